@@ -1,0 +1,190 @@
+/*
+ * tfpose_decode.h -- C-ABI of libtfpose_decode.so: the B200 (sm_100a) heatmap/PAF decode
+ * path of tf-pose-estimation.  Plain pointers and sizes only; no torch / CUDA types.
+ *
+ * What this boundary replaces in the reference (paths relative to the reference root):
+ *
+ *   seam 1  the post-processing half of TfPoseEstimator.inference
+ *           (tf_pose/estimator.py:518-553): the TF1 graph ops built at
+ *           tf_pose/estimator.py:321-337 (channel split, tf.image.resize_area x2,
+ *           Smoother 25x25 depthwise conv -- tf_pose/tensblur/smoother.py:62-95 --,
+ *           3x3 max-pool NMS) followed by PoseEstimator.estimate_paf
+ *           (tf_pose/estimator.py:272-299).
+ *           -> tfpd_decode_device / tfpd_decode_host + tfpd_fetch_humans.
+ *
+ *   seam 2  the swig-bound C++ module tf_pose/pafprocess (prototypes
+ *           tf_pose/pafprocess/pafprocess.h:53-59, body pafprocess.cpp:19-214, binding
+ *           tf_pose/pafprocess/pafprocess.i:1-15).
+ *           -> tfpd_process_paf + tfpd_get_num_humans / tfpd_get_part_cid / tfpd_get_score /
+ *              tfpd_get_part_x / tfpd_get_part_y / tfpd_get_part_score.
+ *
+ * Every function that can fail returns an int status (TFPD_OK == 0); tfpd_last_error()
+ * gives the message.  A context (ctx) owns its device workspace and its results; results
+ * stay valid until the next decode/process call on that ctx.  Calls on different contexts
+ * are independent (the reference keeps its results in module globals,
+ * pafprocess.cpp:12-13, and is not re-entrant).  There is no CPU fallback anywhere: without
+ * a CUDA device tfpd_create fails with TFPD_ERR_CUDA.
+ */
+#ifndef TFPOSE_DECODE_H_
+#define TFPOSE_DECODE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define TFPD_API __attribute__((visibility("default")))
+#else
+#define TFPD_API
+#endif
+
+#define TFPD_NUM_PARTS 18          /* pafprocess.h:11 NUM_PART */
+#define TFPD_NUM_LIMBS 19          /* pafprocess.h:15 COCOPAIRS_SIZE */
+#define TFPD_HEAT_CHANNELS 19      /* estimator.py:321 */
+#define TFPD_PAF_CHANNELS 38       /* estimator.py:322 */
+#define TFPD_NET_CHANNELS 57
+
+enum {
+    TFPD_OK = 0,
+    TFPD_ERR_INVALID = 1,    /* bad argument (shape, alignment, null pointer, batch > max_batch) */
+    TFPD_ERR_CUDA = 2,       /* CUDA runtime error or no device */
+    TFPD_ERR_CAPACITY = 3,   /* a per-frame table overflowed (see frame flags); nothing is silently truncated */
+    TFPD_ERR_STATE = 4       /* fetch/getter without a preceding decode */
+};
+
+/* per-frame flag bits (tfpd_frame_info.flags) */
+enum {
+    TFPD_FLAG_SCORE_TIE = 1,       /* two candidates of one limb have bit-equal scores: the reference's
+                                      order is then decided by libstdc++ introsort internals
+                                      (pafprocess.cpp:97); this library orders (score desc, idx1, idx2) */
+    TFPD_FLAG_FOUND_GT2 = 2,       /* a connection matched >2 subset rows and was dropped (pafprocess.cpp:136-141) */
+    TFPD_FLAG_PEAK_OVERFLOW = 4,
+    TFPD_FLAG_CAND_OVERFLOW = 8,
+    TFPD_FLAG_ROW_OVERFLOW = 16,
+    TFPD_FLAG_HUMAN_OVERFLOW = 32
+};
+
+enum { TFPD_MODE_ASBUILT = 0,     /* pafprocess.cpp:152 as compiled by GCC -O2: found==2 never merges */
+       TFPD_MODE_UPSTREAM = 1 };  /* `int membership = 0;` (ildoonet upstream): merge disjoint rows */
+
+typedef struct tfpd_ctx tfpd_ctx;
+
+typedef struct tfpd_config {
+    int device;               /* CUDA device ordinal */
+    int max_batch;            /* frames per decode call */
+    int max_h, max_w;         /* largest UPSAMPLED map (H, W) the ctx must handle */
+    /* decode constants, pafprocess.h:6-13 */
+    float thresh_heat;            /* 0.05 */
+    float thresh_vector_score;    /* 0.05 */
+    int thresh_vector_cnt1;       /* 6 */
+    int thresh_part_cnt;          /* 4 */
+    float thresh_human_score;     /* 0.3 */
+    int mode;                     /* TFPD_MODE_* */
+    /* smoother parameters, estimator.py:332 */
+    int blur_ksize;               /* 25 */
+    float blur_sigma;             /* 3.0 */
+    /* per-frame table capacities (overflow is reported, never silent) */
+    int max_peaks;                /* <= 4096 */
+    int max_cands;                /* accepted limb candidates per frame */
+    int max_rows;                 /* subset rows alive during assembly */
+    int max_humans;               /* humans per frame after filtering */
+} tfpd_config;
+
+/* One human, as PoseEstimator.estimate_paf reads it through the getters
+ * (estimator.py:277-297): cid < 0 means the part is absent. */
+typedef struct tfpd_human {
+    float score;                        /* get_score: subset[18]/subset[19] (pafprocess.cpp:202-204) */
+    int16_t cid[TFPD_NUM_PARTS];        /* get_part_cid */
+    int16_t x[TFPD_NUM_PARTS];          /* get_part_x(cid), upsampled pixels */
+    int16_t y[TFPD_NUM_PARTS];          /* get_part_y(cid) */
+    float part_score[TFPD_NUM_PARTS];   /* get_part_score(cid): un-blurred heat value */
+} tfpd_human;
+
+typedef struct tfpd_frame_info {
+    int n_humans;
+    int n_peaks;
+    int n_cands;
+    int flags;          /* TFPD_FLAG_* */
+    int near_ties;      /* pixels whose peak / threshold decision is within 2e-5 relative of flipping */
+    int n_rows;         /* subset rows before filtering (pafprocess.cpp:185) */
+} tfpd_frame_info;
+
+/* Optional dense outputs of seam 1, DEVICE pointers (16-byte aligned), NHWC float32,
+ * the three tensors the reference's sess.run returns (estimator.py:536-539).
+ * All three null = minimal mode (nothing dense is written). All three must be set or none. */
+typedef struct tfpd_dense {
+    float *heat_up;     /* [N,H,W,19] */
+    float *paf_up;      /* [N,H,W,38] */
+    float *peaks;       /* [N,H,W,19] */
+} tfpd_dense;
+
+TFPD_API void tfpd_default_config(tfpd_config *cfg);
+TFPD_API int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out);
+TFPD_API void tfpd_destroy(tfpd_ctx *ctx);
+/* Message of the last failing call on ctx (or of the last failed tfpd_create when ctx is null). */
+TFPD_API const char *tfpd_last_error(const tfpd_ctx *ctx);
+
+/* seam 1, device buffers: net_out is a DEVICE pointer to [N,h,w,57] float32 NHWC (the tensor
+ * `Openpose/concat_stage7`, estimator.py:319); (H,W) is upsample_size (estimator.py:325,
+ * 523-525).  Asynchronous on `stream` (a cudaStream_t passed as void*; null = default stream). */
+TFPD_API int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W,
+                       void *stream, const tfpd_dense *dense);
+
+/* seam 1, host buffers: copies net_out host->device, decodes, and (when the pointers are
+ * non-null) copies the dense tensors device->host -- what one persistent_sess.run +
+ * estimate_paf does (estimator.py:536-551).  Synchronous. */
+TFPD_API int tfpd_decode_host(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W,
+                     float *heat_up, float *paf_up, float *peaks);
+
+/* Waits for the decode, copies the per-frame tables to the host.
+ * humans: [N * max_humans] (frame i at humans + i*max_humans), info: [N].  Either may be null.
+ * Returns TFPD_ERR_CAPACITY if any frame overflowed a table (tables are still filled). */
+TFPD_API int tfpd_fetch_humans(tfpd_ctx *ctx, tfpd_human *humans, tfpd_frame_info *info);
+
+/* Peak table of one frame (peak id == index == the reference's Peak.id, pafprocess.cpp:30):
+ * arrays of length >= cap; *count receives the number of peaks.  Any array may be null. */
+TFPD_API int tfpd_fetch_peaks(tfpd_ctx *ctx, int frame, int cap, int *part, int *x, int *y, float *score, int *count);
+
+/* Accepted connections of one frame, limb-major in acceptance order (pafprocess.cpp:96-124):
+ * arrays of length >= cap; *count = number written. */
+TFPD_API int tfpd_fetch_connections(tfpd_ctx *ctx, int frame, int cap, int *limb, int *cid1, int *cid2,
+                           float *score, int *count);
+
+/* seam 2: same prototype as the reference's process_paf (pafprocess.h:53) plus ctx.
+ * peaks [p1,p2,p3], heatmap [h1,h2,h3], pafmap [f1,f2,f3] are HOST float32 C-contiguous arrays
+ * (what swig's IN_ARRAY3 typemap hands over, pafprocess_wrap.cpp:4930-4969); p3 = h3 = 19,
+ * f3 = 38.  Returns 0 like the reference on success. */
+TFPD_API int tfpd_process_paf(tfpd_ctx *ctx, int p1, int p2, int p3, const float *peaks, int h1, int h2, int h3,
+                     const float *heatmap, int f1, int f2, int f3, const float *pafmap);
+/* same, DEVICE pointers, asynchronous on stream */
+TFPD_API int tfpd_process_paf_device(tfpd_ctx *ctx, int p1, int p2, int p3, const float *peaks, int h1, int h2,
+                            int h3, const float *heatmap, int f1, int f2, int f3, const float *pafmap,
+                            void *stream);
+/* getters of pafprocess.h:54-59 (frame 0 of the last call).  Unlike the reference they are
+ * bounds-checked: out-of-range arguments return -1 / 0.0f and set the error string. */
+TFPD_API int tfpd_get_num_humans(tfpd_ctx *ctx);
+TFPD_API int tfpd_get_part_cid(tfpd_ctx *ctx, int human_id, int part_id);
+TFPD_API float tfpd_get_score(tfpd_ctx *ctx, int human_id);
+TFPD_API int tfpd_get_part_x(tfpd_ctx *ctx, int cid);
+TFPD_API int tfpd_get_part_y(tfpd_ctx *ctx, int cid);
+TFPD_API float tfpd_get_part_score(tfpd_ctx *ctx, int cid);
+
+/* Introspection used by the tests and the bench. */
+TFPD_API int tfpd_version(void);
+/* 25-tap separable factor and polyphase weights the kernels use (float64 -> float32):
+ * k2d receives ksize*ksize float32 weights identical to Smoother.gauss_kernel (smoother.py:62-71). */
+TFPD_API int tfpd_gauss_kernel(int ksize, float sigma, float *k2d);
+/* Number of kernel launches issued by the last decode/process call, and the device time of
+ * each stage of the last call in milliseconds (CUDA events on the caller's stream):
+ * stage_ms[0]=K1 maps, [1]=peak sort, [2]=K2 limb scoring, [3]=K3 assembly.  Timing is only
+ * recorded when tfpd_set_profiling(ctx, 1) was called. */
+TFPD_API int tfpd_last_launch_count(const tfpd_ctx *ctx);
+TFPD_API int tfpd_set_profiling(tfpd_ctx *ctx, int on);
+TFPD_API int tfpd_last_stage_ms(tfpd_ctx *ctx, float stage_ms[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TFPOSE_DECODE_H_ */

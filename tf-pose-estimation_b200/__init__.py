@@ -7,5 +7,11 @@ sm_100a CUDA kernels.  There is no CPU fallback: every decode call needs the
 built ``libtfpose_decode.so`` and a CUDA device.
 """
 from .common import CocoPart, CocoPairs, CocoPairsRender, CocoPairsNetwork, CocoColors  # noqa: F401
+from .humans import Human, BodyPart  # noqa: F401
+from .decoder import PoseDecoder, DecodeResult, upsample_size_for, humans_from_table  # noqa: F401
+from .estimator import PoseEstimator, TfPosePostProcessor  # noqa: F401
+from ._lib import DecodeError, CapacityError, DecodeLibraryMissing  # noqa: F401
 
-__all__ = ["CocoPart", "CocoPairs", "CocoPairsRender", "CocoPairsNetwork", "CocoColors"]
+__all__ = ["CocoPart", "CocoPairs", "CocoPairsRender", "CocoPairsNetwork", "CocoColors", "Human", "BodyPart",
+           "PoseDecoder", "DecodeResult", "PoseEstimator", "TfPosePostProcessor", "upsample_size_for",
+           "humans_from_table", "DecodeError", "CapacityError", "DecodeLibraryMissing"]

@@ -1,0 +1,659 @@
+// api.cu -- the C-ABI of include/tfpose_decode.h: context, workspace, stage sequencing.
+// Host-side only; the kernels live in k1_fused.cu / k_generic.cu / k_peaks.cu / k2_limbs.cu /
+// k3_assemble.cu.  There is deliberately no CPU implementation of any stage in this library.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "tfpd_internal.cuh"
+
+using namespace tfpd;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+    cudaError_t reserve(size_t need) {
+        if (need <= bytes) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaMalloc(&p, need);
+        if (e == cudaSuccess) bytes = need;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+};
+
+}  // namespace
+
+struct tfpd_ctx {
+    tfpd_config cfg;
+    int sm_count = 148;
+    Workspace ws{};
+    void *ws_block = nullptr;           // one allocation holding every workspace array
+    tfpd_frame_info *d_info = nullptr;  // contiguous [info | humans] block (one D2H copy)
+    size_t result_bytes = 0;
+    unsigned char *h_result = nullptr;  // pinned mirror of the result block
+    float *d_k1d = nullptr;             // float32 separable factor (generic path)
+    std::vector<double> s1d;
+    DevBuf in_buf, dense_buf, gen_buf;  // lazily sized: host-call input, dense outputs, generic-path scratch
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool profiling = false, have_timing = false;
+    cudaStream_t last_stream = nullptr;
+    int last_N = 0, last_H = 0, last_W = 0;
+    int launches = 0;
+    bool decoded = false, fetched = false;
+    std::string err;
+    // host caches for the seam-2 getters
+    std::vector<tfpd_human> g_humans;
+    std::vector<int> g_px, g_py;
+    std::vector<float> g_ps;
+    bool getters_ready = false;
+};
+
+namespace {
+
+int fail(tfpd_ctx *ctx, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf;
+    else g_create_error = buf;
+    return code;
+}
+
+#define CUDA_TRY(ctx, expr)                                                                        \
+    do {                                                                                           \
+        cudaError_t e__ = (expr);                                                                  \
+        if (e__ != cudaSuccess)                                                                    \
+            return fail(ctx, TFPD_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e__));      \
+    } while (0)
+
+// Phi(x): scipy.stats.norm.cdf, used by Smoother.gauss_kernel (smoother.py:65)
+double std_normal_cdf(double x) { return 0.5 * erfc(-x / sqrt(2.0)); }
+
+// smoother.py:62-71: the 2-D float32 weights and the float64 separable factor s (K = s s^T)
+void gauss_kernel_host(int ks, double nsig, std::vector<float> *k2d, std::vector<double> *s1d) {
+    const double interval = (2.0 * nsig + 1.0) / ks;
+    const double lo = -nsig - interval / 2.0, hi = nsig + interval / 2.0;
+    const double step = (hi - lo) / ks;
+    std::vector<double> cdf(ks + 1), k1(ks);
+    for (int i = 0; i <= ks; ++i) cdf[i] = std_normal_cdf(i == ks ? hi : lo + i * step);
+    for (int i = 0; i < ks; ++i) k1[i] = cdf[i + 1] - cdf[i];
+    double total = 0.0, ssum = 0.0;
+    for (int r = 0; r < ks; ++r)
+        for (int q = 0; q < ks; ++q) total += sqrt(k1[r] * k1[q]);
+    if (k2d) {
+        k2d->resize((size_t)ks * ks);
+        for (int r = 0; r < ks; ++r)
+            for (int q = 0; q < ks; ++q) (*k2d)[(size_t)r * ks + q] = (float)(sqrt(k1[r] * k1[q]) / total);
+    }
+    if (s1d) {
+        s1d->resize(ks);
+        for (int i = 0; i < ks; ++i) ssum += sqrt(k1[i]);
+        for (int i = 0; i < ks; ++i) (*s1d)[i] = sqrt(k1[i]) / ssum;
+    }
+}
+
+int next_pow2(int v) {
+    int p = 32;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+Thresholds thresholds_of(const tfpd_config &c) {
+    Thresholds t;
+    t.heat = c.thresh_heat;
+    t.vector_score = c.thresh_vector_score;
+    t.human_score = c.thresh_human_score;
+    t.vector_cnt1 = c.thresh_vector_cnt1;
+    t.part_cnt = c.thresh_part_cnt;
+    t.mode = c.mode;
+    return t;
+}
+
+// zero the per-frame counters, then stages 2..4 shared by both seams
+int run_tail(tfpd_ctx *ctx, int N, const PafSource &src, size_t frame_stride, cudaStream_t s) {
+    int r;
+    if (ctx->profiling) cudaEventRecord(ctx->ev[1], s);
+    if ((r = launch_sort_peaks(ctx->ws, N, s)) < 0) return fail(ctx, TFPD_ERR_CUDA, "k_sort_peaks launch failed");
+    ctx->launches += r;
+    if (ctx->profiling) cudaEventRecord(ctx->ev[2], s);
+    if ((r = launch_limb_score(ctx->ws, N, src, frame_stride, thresholds_of(ctx->cfg), ctx->sm_count, s)) < 0)
+        return fail(ctx, TFPD_ERR_CUDA, "k_limb_score launch failed");
+    ctx->launches += r;
+    if (ctx->profiling) cudaEventRecord(ctx->ev[3], s);
+    if ((r = launch_assemble(ctx->ws, N, thresholds_of(ctx->cfg), s)) < 0)
+        return fail(ctx, TFPD_ERR_CUDA, "k_assemble launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+    ctx->launches += r;
+    if (ctx->profiling) {
+        cudaEventRecord(ctx->ev[4], s);
+        ctx->have_timing = true;
+    }
+    return TFPD_OK;
+}
+
+void begin_call(tfpd_ctx *ctx, int N, int H, int W, cudaStream_t s) {
+    ctx->launches = 0;
+    ctx->last_stream = s;
+    ctx->last_N = N;
+    ctx->last_H = H;
+    ctx->last_W = W;
+    ctx->decoded = false;
+    ctx->fetched = false;
+    ctx->getters_ready = false;
+    ctx->have_timing = false;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tfpd_version(void) { return 100; }
+
+void tfpd_default_config(tfpd_config *c) {
+    if (!c) return;
+    memset(c, 0, sizeof(*c));
+    c->device = 0;
+    c->max_batch = 64;
+    c->max_h = 368;
+    c->max_w = 656;
+    c->thresh_heat = 0.05f;             // pafprocess.h:6-10
+    c->thresh_vector_score = 0.05f;
+    c->thresh_vector_cnt1 = 6;
+    c->thresh_part_cnt = 4;
+    c->thresh_human_score = 0.3f;
+    c->mode = TFPD_MODE_ASBUILT;
+    c->blur_ksize = 25;                 // estimator.py:332
+    c->blur_sigma = 3.0f;
+    c->max_peaks = 2048;
+    c->max_cands = 4096;
+    c->max_rows = 512;
+    c->max_humans = 64;
+}
+
+const char *tfpd_last_error(const tfpd_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int tfpd_gauss_kernel(int ksize, float sigma, float *k2d) {
+    if (ksize < 1 || (ksize & 1) == 0 || !k2d) return TFPD_ERR_INVALID;
+    std::vector<float> k;
+    gauss_kernel_host(ksize, (double)sigma, &k, nullptr);
+    memcpy(k2d, k.data(), k.size() * sizeof(float));
+    return TFPD_OK;
+}
+
+int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
+    if (!cfg || !out) return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: null argument");
+    *out = nullptr;
+    if (cfg->max_batch < 1 || cfg->max_h < 1 || cfg->max_w < 1 || cfg->max_h > 8191 || cfg->max_w > 16383)
+        return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: bad max_batch/max_h/max_w");
+    if (cfg->blur_ksize < 1 || (cfg->blur_ksize & 1) == 0 || cfg->blur_ksize > 127)
+        return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: blur_ksize must be odd and <= 127");
+    if (cfg->max_peaks < 1 || cfg->max_peaks > kMaxPeaksHard || cfg->max_cands < 1 || cfg->max_cands > 16384 ||
+        cfg->max_rows < 1 || cfg->max_rows > 1024 || cfg->max_humans < 1 || cfg->max_humans > cfg->max_rows)
+        return fail(nullptr, TFPD_ERR_INVALID,
+                    "tfpd_create: capacities out of range (max_peaks<=4096, max_cands<=16384, "
+                    "max_humans<=max_rows<=1024)");
+    if (cfg->mode != TFPD_MODE_ASBUILT && cfg->mode != TFPD_MODE_UPSTREAM)
+        return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: unknown mode %d", cfg->mode);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
+        return fail(nullptr, TFPD_ERR_CUDA, "tfpd_create: no CUDA device (this library has no CPU path)");
+    if (cfg->device < 0 || cfg->device >= ndev)
+        return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: device %d of %d", cfg->device, ndev);
+    cudaError_t e = cudaSetDevice(cfg->device);
+    if (e != cudaSuccess) return fail(nullptr, TFPD_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+
+    tfpd_ctx *ctx = new tfpd_ctx();
+    ctx->cfg = *cfg;
+    ctx->cfg.max_peaks = next_pow2(cfg->max_peaks);     // the in-smem sorts pad to a power of two
+    ctx->cfg.max_cands = next_pow2(cfg->max_cands);
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
+
+    Workspace &w = ctx->ws;
+    w.max_batch = cfg->max_batch;
+    w.max_peaks = ctx->cfg.max_peaks;
+    w.max_cands = ctx->cfg.max_cands;
+    w.max_rows = cfg->max_rows;
+    w.max_humans = cfg->max_humans;
+    const size_t N = (size_t)cfg->max_batch, MP = (size_t)w.max_peaks, MC = (size_t)w.max_cands;
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+        size_t o = off;
+        off = align_up(off + bytes, 256);
+        return o;
+    };
+    const size_t o_cnt = take(N * sizeof(FrameCounters));
+    const size_t o_rk = take(N * MP * 4), o_rv = take(N * MP * 4);
+    const size_t o_px = take(N * MP * 2), o_py = take(N * MP * 2), o_ps = take(N * MP * 4);
+    const size_t o_pf = take(N * 20 * 4);
+    const size_t o_ck = take(N * MC * 8);
+    const size_t o_c1 = take(N * MC * 2), o_c2 = take(N * MC * 2), o_cs = take(N * MC * 4);
+    const size_t o_st = take(N * 20 * 4), o_cc = take(N * 20 * 4);
+    const size_t o_res = take(0);
+    ctx->result_bytes = align_up(N * sizeof(tfpd_frame_info), 16) + N * w.max_humans * sizeof(tfpd_human);
+    take(ctx->result_bytes);
+    e = cudaMalloc(&ctx->ws_block, off);
+    if (e != cudaSuccess) {
+        delete ctx;
+        return fail(nullptr, TFPD_ERR_CUDA, "cudaMalloc(%zu) workspace: %s", off, cudaGetErrorString(e));
+    }
+    cudaMemset(ctx->ws_block, 0, off);
+    unsigned char *b = (unsigned char *)ctx->ws_block;
+    w.counters = (FrameCounters *)(b + o_cnt);
+    w.rec_key = (uint32_t *)(b + o_rk);
+    w.rec_val = (float *)(b + o_rv);
+    w.pk_x = (int16_t *)(b + o_px);
+    w.pk_y = (int16_t *)(b + o_py);
+    w.pk_score = (float *)(b + o_ps);
+    w.part_first = (int *)(b + o_pf);
+    w.cand_key = (unsigned long long *)(b + o_ck);
+    w.conn_cid1 = (int16_t *)(b + o_c1);
+    w.conn_cid2 = (int16_t *)(b + o_c2);
+    w.conn_score = (float *)(b + o_cs);
+    w.conn_start = (int *)(b + o_st);
+    w.conn_count = (int *)(b + o_cc);
+    w.info = (tfpd_frame_info *)(b + o_res);
+    w.humans = (tfpd_human *)(b + o_res + align_up(N * sizeof(tfpd_frame_info), 16));
+    ctx->d_info = w.info;
+
+    e = cudaMallocHost((void **)&ctx->h_result, ctx->result_bytes);
+    if (e != cudaSuccess) {
+        cudaFree(ctx->ws_block);
+        delete ctx;
+        return fail(nullptr, TFPD_ERR_CUDA, "cudaMallocHost: %s", cudaGetErrorString(e));
+    }
+    gauss_kernel_host(cfg->blur_ksize, (double)cfg->blur_sigma, nullptr, &ctx->s1d);
+    std::vector<float> s32(ctx->s1d.size());
+    for (size_t i = 0; i < s32.size(); ++i) s32[i] = (float)ctx->s1d[i];
+    e = cudaMalloc((void **)&ctx->d_k1d, s32.size() * 4);
+    if (e == cudaSuccess) e = cudaMemcpy(ctx->d_k1d, s32.data(), s32.size() * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess || (cfg->blur_ksize == 25 && upload_polyphase_weights(ctx->s1d.data(), 25) != 0)) {
+        tfpd_destroy(ctx);
+        return fail(nullptr, TFPD_ERR_CUDA, "smoother weight upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+    }
+    for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    *out = ctx;
+    return TFPD_OK;
+}
+
+void tfpd_destroy(tfpd_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->cfg.device);
+    if (ctx->decoded) cudaStreamSynchronize(ctx->last_stream);
+    for (auto &ev : ctx->ev)
+        if (ev) cudaEventDestroy(ev);
+    if (ctx->ws_block) cudaFree(ctx->ws_block);
+    if (ctx->h_result) cudaFreeHost(ctx->h_result);
+    if (ctx->d_k1d) cudaFree(ctx->d_k1d);
+    ctx->in_buf.release();
+    ctx->dense_buf.release();
+    ctx->gen_buf.release();
+    delete ctx;
+}
+
+int tfpd_set_profiling(tfpd_ctx *ctx, int on) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    ctx->profiling = on != 0;
+    return TFPD_OK;
+}
+
+int tfpd_last_launch_count(const tfpd_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int tfpd_last_stage_ms(tfpd_ctx *ctx, float stage_ms[4]) {
+    if (!ctx || !stage_ms) return TFPD_ERR_INVALID;
+    if (!ctx->have_timing) return fail(ctx, TFPD_ERR_STATE, "no timing recorded (tfpd_set_profiling + decode first)");
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev[4]));
+    for (int i = 0; i < 4; ++i) CUDA_TRY(ctx, cudaEventElapsedTime(&stage_ms[i], ctx->ev[i], ctx->ev[i + 1]));
+    return TFPD_OK;
+}
+
+int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W, void *stream,
+                       const tfpd_dense *dense) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!net_out) return fail(ctx, TFPD_ERR_INVALID, "decode: net_out is null");
+    if (N < 1 || N > ctx->cfg.max_batch) return fail(ctx, TFPD_ERR_INVALID, "decode: batch %d outside 1..%d", N, ctx->cfg.max_batch);
+    if (h < 1 || w < 1 || H < 1 || W < 1) return fail(ctx, TFPD_ERR_INVALID, "decode: non-positive dimension");
+    if (H > ctx->cfg.max_h || W > ctx->cfg.max_w)
+        return fail(ctx, TFPD_ERR_INVALID, "decode: upsample %dx%d exceeds ctx max %dx%d", H, W, ctx->cfg.max_h, ctx->cfg.max_w);
+    const bool want_dense = dense && (dense->heat_up || dense->paf_up || dense->peaks);
+    if (want_dense && !(dense->heat_up && dense->paf_up && dense->peaks))
+        return fail(ctx, TFPD_ERR_INVALID, "decode: dense outputs must be all set or all null");
+    if (want_dense && ((((uintptr_t)dense->heat_up) | ((uintptr_t)dense->paf_up) | ((uintptr_t)dense->peaks)) & 15))
+        return fail(ctx, TFPD_ERR_INVALID, "decode: dense output pointers must be 16-byte aligned");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    begin_call(ctx, N, H, W, s);
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->ws.counters, 0, (size_t)N * sizeof(FrameCounters), s));
+    if (ctx->profiling) cudaEventRecord(ctx->ev[0], s);
+
+    PafSource src;
+    size_t frame_stride;
+    const bool fast = (H == 4 * h && W == 4 * w && ctx->cfg.blur_ksize == 25);
+    if (fast) {
+        K1Params p;
+        p.X = net_out;
+        p.heat_up = want_dense ? dense->heat_up : nullptr;
+        p.paf_up = want_dense ? dense->paf_up : nullptr;
+        p.peaks = want_dense ? dense->peaks : nullptr;
+        p.rec_key = ctx->ws.rec_key;
+        p.rec_val = ctx->ws.rec_val;
+        p.counters = ctx->ws.counters;
+        p.max_peaks = ctx->ws.max_peaks;
+        p.N = N;
+        p.h = h;
+        p.w = w;
+        p.nchunks = (w + 55) / 56;
+        p.chunk_cells = (w + p.nchunks - 1) / p.nchunks;
+        // bands: enough items for >= ~6 rounds over the SMs, but at least 2 low-res rows each
+        int want_items = ctx->sm_count * 6;
+        int nb = (want_items + N * p.nchunks - 1) / (N * p.nchunks);
+        if (nb < 1) nb = 1;
+        int br = (h + nb - 1) / nb;
+        if (br < 2) br = 2;
+        if (br > h) br = h;
+        p.band_rows = br;
+        p.nbands = (h + br - 1) / br;
+        p.nitems = N * p.nbands * p.nchunks;
+        p.thresh = ctx->cfg.thresh_heat;
+        int r = launch_k1_fused_f4(p, want_dense, ctx->sm_count, s);
+        if (r < 0) return fail(ctx, TFPD_ERR_CUDA, "k1_fused_f4 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
+        ctx->launches += r;
+        src.base = net_out;
+        src.rows = h;
+        src.cols = w;
+        src.chan = kNetC;
+        src.chan_off = kHeatC;
+        src.shift = 2;
+        src.H = H;
+        frame_stride = (size_t)h * w * kNetC;
+    } else {
+        const size_t px = (size_t)N * H * W;
+        float *heat_up, *paf_up, *peaks;
+        size_t need = 2 * px * kHeatC * 4;
+        if (!want_dense) need += px * (kHeatC + kPafC) * 4;
+        CUDA_TRY(ctx, ctx->gen_buf.reserve(need));
+        float *scratch = (float *)ctx->gen_buf.p;
+        if (want_dense) {
+            heat_up = dense->heat_up;
+            paf_up = dense->paf_up;
+            peaks = dense->peaks;
+        } else {
+            heat_up = scratch + 2 * px * kHeatC;
+            paf_up = heat_up + px * kHeatC;
+            peaks = nullptr;
+        }
+        int r = launch_generic_maps(net_out, N, h, w, H, W, ctx->d_k1d, ctx->cfg.blur_ksize, heat_up, paf_up, peaks,
+                                    scratch, ctx->ws, ctx->cfg.thresh_heat, s);
+        if (r < 0) return fail(ctx, TFPD_ERR_CUDA, "generic map kernels failed: %s", cudaGetErrorString(cudaGetLastError()));
+        ctx->launches += r;
+        src.base = paf_up;
+        src.rows = H;
+        src.cols = W;
+        src.chan = kPafC;
+        src.chan_off = 0;
+        src.shift = 0;
+        src.H = H;
+        frame_stride = (size_t)H * W * kPafC;
+    }
+    int rc = run_tail(ctx, N, src, frame_stride, s);
+    if (rc != TFPD_OK) return rc;
+    ctx->decoded = true;
+    return TFPD_OK;
+}
+
+int tfpd_fetch_humans(tfpd_ctx *ctx, tfpd_human *humans, tfpd_frame_info *info) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!ctx->decoded) return fail(ctx, TFPD_ERR_STATE, "fetch: no decode on this ctx yet");
+    const int N = ctx->last_N;
+    const size_t info_bytes = align_up((size_t)ctx->cfg.max_batch * sizeof(tfpd_frame_info), 16);
+    if (!ctx->fetched) {
+        CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+        // info for N frames and humans for N frames: two contiguous ranges of the result block
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_result, ctx->d_info, (size_t)N * sizeof(tfpd_frame_info),
+                                      cudaMemcpyDeviceToHost, ctx->last_stream));
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_result + info_bytes, ctx->ws.humans,
+                                      (size_t)N * ctx->ws.max_humans * sizeof(tfpd_human), cudaMemcpyDeviceToHost,
+                                      ctx->last_stream));
+        CUDA_TRY(ctx, cudaStreamSynchronize(ctx->last_stream));
+        ctx->fetched = true;
+    }
+    const tfpd_frame_info *hi = (const tfpd_frame_info *)ctx->h_result;
+    if (info) memcpy(info, hi, (size_t)N * sizeof(tfpd_frame_info));
+    if (humans) memcpy(humans, ctx->h_result + info_bytes, (size_t)N * ctx->ws.max_humans * sizeof(tfpd_human));
+    const int ovf = TFPD_FLAG_PEAK_OVERFLOW | TFPD_FLAG_CAND_OVERFLOW | TFPD_FLAG_ROW_OVERFLOW | TFPD_FLAG_HUMAN_OVERFLOW;
+    for (int i = 0; i < N; ++i)
+        if (hi[i].flags & ovf)
+            return fail(ctx, TFPD_ERR_CAPACITY,
+                        "frame %d overflowed a table (flags=0x%x: 4=peaks>%d 8=cands>%d 16=rows>%d 32=humans>%d); "
+                        "raise the capacity in tfpd_config",
+                        i, hi[i].flags, ctx->ws.max_peaks, ctx->ws.max_cands, ctx->ws.max_rows, ctx->ws.max_humans);
+    return TFPD_OK;
+}
+
+int tfpd_fetch_peaks(tfpd_ctx *ctx, int frame, int cap, int *part, int *x, int *y, float *score, int *count) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!ctx->decoded) return fail(ctx, TFPD_ERR_STATE, "fetch_peaks: no decode on this ctx yet");
+    if (frame < 0 || frame >= ctx->last_N || cap < 0) return fail(ctx, TFPD_ERR_INVALID, "fetch_peaks: bad frame/cap");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->last_stream));
+    int first[20];
+    CUDA_TRY(ctx, cudaMemcpy(first, ctx->ws.part_first + frame * 20, sizeof(first), cudaMemcpyDeviceToHost));
+    const int n = first[kParts];
+    if (count) *count = n;
+    const int m = n < cap ? n : cap;
+    if (m > 0) {
+        std::vector<int16_t> hx(m), hy(m);
+        const size_t o = (size_t)frame * ctx->ws.max_peaks;
+        CUDA_TRY(ctx, cudaMemcpy(hx.data(), ctx->ws.pk_x + o, (size_t)m * 2, cudaMemcpyDeviceToHost));
+        CUDA_TRY(ctx, cudaMemcpy(hy.data(), ctx->ws.pk_y + o, (size_t)m * 2, cudaMemcpyDeviceToHost));
+        if (score) CUDA_TRY(ctx, cudaMemcpy(score, ctx->ws.pk_score + o, (size_t)m * 4, cudaMemcpyDeviceToHost));
+        int p = 0;
+        for (int i = 0; i < m; ++i) {
+            while (p < kParts - 1 && i >= first[p + 1]) ++p;
+            if (part) part[i] = p;
+            if (x) x[i] = hx[i];
+            if (y) y[i] = hy[i];
+        }
+    }
+    return TFPD_OK;
+}
+
+int tfpd_fetch_connections(tfpd_ctx *ctx, int frame, int cap, int *limb, int *cid1, int *cid2, float *score,
+                           int *count) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!ctx->decoded) return fail(ctx, TFPD_ERR_STATE, "fetch_connections: no decode on this ctx yet");
+    if (frame < 0 || frame >= ctx->last_N || cap < 0) return fail(ctx, TFPD_ERR_INVALID, "fetch_connections: bad frame/cap");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->last_stream));
+    int st[20], cc[20];
+    CUDA_TRY(ctx, cudaMemcpy(st, ctx->ws.conn_start + frame * 20, sizeof(st), cudaMemcpyDeviceToHost));
+    CUDA_TRY(ctx, cudaMemcpy(cc, ctx->ws.conn_count + frame * 20, sizeof(cc), cudaMemcpyDeviceToHost));
+    const size_t MC = (size_t)ctx->ws.max_cands;
+    std::vector<int16_t> h1(MC), h2(MC);
+    std::vector<float> hs(MC);
+    CUDA_TRY(ctx, cudaMemcpy(h1.data(), ctx->ws.conn_cid1 + frame * MC, MC * 2, cudaMemcpyDeviceToHost));
+    CUDA_TRY(ctx, cudaMemcpy(h2.data(), ctx->ws.conn_cid2 + frame * MC, MC * 2, cudaMemcpyDeviceToHost));
+    CUDA_TRY(ctx, cudaMemcpy(hs.data(), ctx->ws.conn_score + frame * MC, MC * 4, cudaMemcpyDeviceToHost));
+    int k = 0;
+    for (int l = 0; l < kLimbs; ++l)
+        for (int i = 0; i < cc[l]; ++i, ++k) {
+            if (k >= cap) continue;
+            if (limb) limb[k] = l;
+            if (cid1) cid1[k] = h1[st[l] + i];
+            if (cid2) cid2[k] = h2[st[l] + i];
+            if (score) score[k] = hs[st[l] + i];
+        }
+    if (count) *count = k;
+    return TFPD_OK;
+}
+
+int tfpd_decode_host(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W, float *heat_up,
+                     float *paf_up, float *peaks) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!net_out) return fail(ctx, TFPD_ERR_INVALID, "decode_host: net_out is null");
+    if (N < 1 || N > ctx->cfg.max_batch || h < 1 || w < 1 || H < 1 || W < 1)
+        return fail(ctx, TFPD_ERR_INVALID, "decode_host: bad batch or dimension");
+    const bool want_dense = heat_up || paf_up || peaks;
+    if (want_dense && !(heat_up && paf_up && peaks))
+        return fail(ctx, TFPD_ERR_INVALID, "decode_host: dense outputs must be all set or all null");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    const size_t in_bytes = (size_t)N * h * w * kNetC * 4;
+    CUDA_TRY(ctx, ctx->in_buf.reserve(in_bytes));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_buf.p, net_out, in_bytes, cudaMemcpyHostToDevice, nullptr));
+    tfpd_dense d = {nullptr, nullptr, nullptr};
+    const size_t px = (size_t)N * H * W;
+    if (want_dense) {
+        CUDA_TRY(ctx, ctx->dense_buf.reserve(px * (2 * kHeatC + kPafC) * 4));
+        d.heat_up = (float *)ctx->dense_buf.p;
+        d.paf_up = d.heat_up + px * kHeatC;
+        d.peaks = d.paf_up + px * kPafC;
+    }
+    int rc = tfpd_decode_device(ctx, (const float *)ctx->in_buf.p, N, h, w, H, W, nullptr, want_dense ? &d : nullptr);
+    if (rc != TFPD_OK) return rc;
+    if (want_dense) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(heat_up, d.heat_up, px * kHeatC * 4, cudaMemcpyDeviceToHost, nullptr));
+        CUDA_TRY(ctx, cudaMemcpyAsync(paf_up, d.paf_up, px * kPafC * 4, cudaMemcpyDeviceToHost, nullptr));
+        CUDA_TRY(ctx, cudaMemcpyAsync(peaks, d.peaks, px * kHeatC * 4, cudaMemcpyDeviceToHost, nullptr));
+    }
+    return tfpd_fetch_humans(ctx, nullptr, nullptr);    // synchronises; reports capacity overflow
+}
+
+int tfpd_process_paf_device(tfpd_ctx *ctx, int p1, int p2, int p3, const float *peaks, int h1, int h2, int h3,
+                            const float *heatmap, int f1, int f2, int f3, const float *pafmap, void *stream) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!peaks || !heatmap || !pafmap) return fail(ctx, TFPD_ERR_INVALID, "process_paf: null array");
+    if (p3 != kHeatC || h3 != kHeatC || f3 != kPafC)
+        return fail(ctx, TFPD_ERR_INVALID, "process_paf: channel counts must be 19/19/38, got %d/%d/%d", p3, h3, f3);
+    if (p1 < 1 || p2 < 1 || h1 != p1 || h2 != p2 || f1 != p1 || f2 != p2)
+        return fail(ctx, TFPD_ERR_INVALID, "process_paf: the three arrays must share their spatial shape");
+    if (p1 > 8191 || p2 > 16383) return fail(ctx, TFPD_ERR_INVALID, "process_paf: map larger than 8191x16383");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    begin_call(ctx, 1, p1, p2, s);
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->ws.counters, 0, sizeof(FrameCounters), s));
+    if (ctx->profiling) cudaEventRecord(ctx->ev[0], s);
+    int r = launch_scan_dense_peaks(peaks, heatmap, 1, p1, p2, ctx->cfg.thresh_heat, ctx->ws, s);
+    if (r < 0) return fail(ctx, TFPD_ERR_CUDA, "k_scan_dense_peaks launch failed");
+    ctx->launches += r;
+    PafSource src;
+    src.base = pafmap;
+    src.rows = p1;
+    src.cols = p2;
+    src.chan = kPafC;
+    src.chan_off = 0;
+    src.shift = 0;
+    src.H = h1;
+    int rc = run_tail(ctx, 1, src, (size_t)p1 * p2 * kPafC, s);
+    if (rc != TFPD_OK) return rc;
+    ctx->decoded = true;
+    return 0;
+}
+
+int tfpd_process_paf(tfpd_ctx *ctx, int p1, int p2, int p3, const float *peaks, int h1, int h2, int h3,
+                     const float *heatmap, int f1, int f2, int f3, const float *pafmap) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!peaks || !heatmap || !pafmap) return fail(ctx, TFPD_ERR_INVALID, "process_paf: null array");
+    if (p1 < 1 || p2 < 1 || p3 < 1 || h1 < 1 || h2 < 1 || h3 < 1 || f1 < 1 || f2 < 1 || f3 < 1)
+        return fail(ctx, TFPD_ERR_INVALID, "process_paf: empty array");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    const size_t np = (size_t)p1 * p2 * p3, nh = (size_t)h1 * h2 * h3, nf = (size_t)f1 * f2 * f3;
+    CUDA_TRY(ctx, ctx->dense_buf.reserve((np + nh + nf) * 4));
+    float *dp = (float *)ctx->dense_buf.p, *dh = dp + np, *df = dh + nh;
+    CUDA_TRY(ctx, cudaMemcpyAsync(dp, peaks, np * 4, cudaMemcpyHostToDevice, nullptr));
+    CUDA_TRY(ctx, cudaMemcpyAsync(dh, heatmap, nh * 4, cudaMemcpyHostToDevice, nullptr));
+    CUDA_TRY(ctx, cudaMemcpyAsync(df, pafmap, nf * 4, cudaMemcpyHostToDevice, nullptr));
+    int rc = tfpd_process_paf_device(ctx, p1, p2, p3, dp, h1, h2, h3, dh, f1, f2, f3, df, nullptr);
+    if (rc != TFPD_OK) return rc;
+    rc = tfpd_fetch_humans(ctx, nullptr, nullptr);
+    return rc == TFPD_OK ? 0 : rc;
+}
+
+static int ensure_getters(tfpd_ctx *ctx) {
+    if (ctx->getters_ready) return TFPD_OK;
+    if (!ctx->decoded) return fail(ctx, TFPD_ERR_STATE, "getter: no process_paf/decode on this ctx yet");
+    int rc = tfpd_fetch_humans(ctx, nullptr, nullptr);
+    if (rc != TFPD_OK && rc != TFPD_ERR_CAPACITY) return rc;
+    const tfpd_frame_info *hi = (const tfpd_frame_info *)ctx->h_result;
+    const size_t info_bytes = align_up((size_t)ctx->cfg.max_batch * sizeof(tfpd_frame_info), 16);
+    const tfpd_human *hh = (const tfpd_human *)(ctx->h_result + info_bytes);
+    ctx->g_humans.assign(hh, hh + hi[0].n_humans);
+    const int np = hi[0].n_peaks;
+    ctx->g_px.resize(np);
+    ctx->g_py.resize(np);
+    ctx->g_ps.resize(np);
+    int cnt = 0;
+    if (np > 0) {
+        rc = tfpd_fetch_peaks(ctx, 0, np, nullptr, ctx->g_px.data(), ctx->g_py.data(), ctx->g_ps.data(), &cnt);
+        if (rc != TFPD_OK) return rc;
+    }
+    ctx->getters_ready = true;
+    return TFPD_OK;
+}
+
+int tfpd_get_num_humans(tfpd_ctx *ctx) {
+    if (!ctx || ensure_getters(ctx) != TFPD_OK) return -1;
+    return (int)ctx->g_humans.size();
+}
+
+int tfpd_get_part_cid(tfpd_ctx *ctx, int human_id, int part_id) {
+    if (!ctx || ensure_getters(ctx) != TFPD_OK) return -1;
+    if (human_id < 0 || human_id >= (int)ctx->g_humans.size() || part_id < 0 || part_id >= kParts) {
+        fail(ctx, TFPD_ERR_INVALID, "get_part_cid(%d,%d) out of range", human_id, part_id);
+        return -1;
+    }
+    return ctx->g_humans[human_id].cid[part_id];
+}
+
+float tfpd_get_score(tfpd_ctx *ctx, int human_id) {
+    if (!ctx || ensure_getters(ctx) != TFPD_OK) return 0.0f;
+    if (human_id < 0 || human_id >= (int)ctx->g_humans.size()) {
+        fail(ctx, TFPD_ERR_INVALID, "get_score(%d) out of range", human_id);
+        return 0.0f;
+    }
+    return ctx->g_humans[human_id].score;
+}
+
+int tfpd_get_part_x(tfpd_ctx *ctx, int cid) {
+    if (!ctx || ensure_getters(ctx) != TFPD_OK) return -1;
+    if (cid < 0 || cid >= (int)ctx->g_px.size()) {
+        fail(ctx, TFPD_ERR_INVALID, "get_part_x(%d) out of range", cid);
+        return -1;
+    }
+    return ctx->g_px[cid];
+}
+
+int tfpd_get_part_y(tfpd_ctx *ctx, int cid) {
+    if (!ctx || ensure_getters(ctx) != TFPD_OK) return -1;
+    if (cid < 0 || cid >= (int)ctx->g_py.size()) {
+        fail(ctx, TFPD_ERR_INVALID, "get_part_y(%d) out of range", cid);
+        return -1;
+    }
+    return ctx->g_py[cid];
+}
+
+float tfpd_get_part_score(tfpd_ctx *ctx, int cid) {
+    if (!ctx || ensure_getters(ctx) != TFPD_OK) return 0.0f;
+    if (cid < 0 || cid >= (int)ctx->g_ps.size()) {
+        fail(ctx, TFPD_ERR_INVALID, "get_part_score(%d) out of range", cid);
+        return 0.0f;
+    }
+    return ctx->g_ps[cid];
+}
+
+}  // extern "C"

@@ -1,0 +1,259 @@
+// k3_assemble.cu -- K3: one block per frame does what pafprocess.cpp:96-189 does after the
+// candidates exist:
+//   1. per-limb ordering of the candidates (std::sort with comp_candidate, :97,:239-241) --
+//      one bitonic sort of the frame's 64-bit keys (limb | ~score | idx1 | idx2), i.e. score
+//      descending with (idx1, idx2) ascending as the tie order (what libstdc++ gives for <= 16
+//      candidates in a-major/b-minor input order when scores differ; bit-equal scores raise
+//      TFPD_FLAG_SCORE_TIE because the reference's order is then introsort-internal),
+//   2. greedy matching (:98-124): one warp per limb walks its sorted segment,
+//   3. subset assembly (:127-183) by warp 0, the row scan spread over the lanes,
+//      in `asbuilt` (found==2 never merges: `int membership;` UB at :152 as compiled by GCC -O2)
+//      or `upstream` (membership = 0) mode,
+//   4. the filter (:185-189) and the getter view (:194-214) -> tfpd_human records.
+#include "tfpd_internal.cuh"
+
+namespace tfpd {
+
+namespace {
+
+constexpr int kK3Threads = 640;             // 20 warps: 19 greedy walkers + sort helpers
+constexpr int kBitmapWords = kMaxPeaksHard / 32;   // 128
+
+__global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Thresholds th) {
+    extern __shared__ __align__(16) unsigned char sm_raw[];
+    unsigned long long *keys = reinterpret_cast<unsigned long long *>(sm_raw);            // [max_cands]
+    float *rows = reinterpret_cast<float *>(keys + ws.max_cands);                        // [20][max_rows] SoA
+    uint32_t *used = reinterpret_cast<uint32_t *>(rows + 20 * (size_t)ws.max_rows);      // [19][2][128]
+    __shared__ int s_lstart[kLimbs + 1];
+    __shared__ int s_ccount[kLimbs];
+    __shared__ int s_first[kHeatC + 1];
+    __shared__ int s_flags;
+
+    const int n = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int MR = ws.max_rows;
+    const int raw = ws.counters[n].n_cand;
+    const int cnt = min(raw, ws.max_cands);
+    int np2 = 32;
+    while (np2 < cnt) np2 <<= 1;
+    for (int i = tid; i < np2; i += kK3Threads)
+        keys[i] = (i < cnt) ? ws.cand_key[(size_t)n * ws.max_cands + i] : ~0ull;
+    for (int i = tid; i < kLimbs * 2 * kBitmapWords; i += kK3Threads) used[i] = 0u;
+    if (tid <= kHeatC) s_first[tid] = ws.part_first[n * 20 + tid];
+    if (tid <= kLimbs) s_lstart[tid] = cnt;
+    if (tid < kLimbs) s_ccount[tid] = 0;
+    if (tid == 0) s_flags = (raw > ws.max_cands) ? TFPD_FLAG_CAND_OVERFLOW : 0;
+    __syncthreads();
+
+    // ---- 1. sort ----
+    for (int k = 2; k <= np2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = tid; i < np2; i += kK3Threads) {
+                int ixj = i ^ j;
+                if (ixj > i) {
+                    bool up = ((i & k) == 0);
+                    unsigned long long a = keys[i], b = keys[ixj];
+                    if ((a > b) == up) {
+                        keys[i] = b;
+                        keys[ixj] = a;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    // limb segments + exact-tie detection
+    for (int i = tid; i < cnt; i += kK3Threads) {
+        int limb = (int)(keys[i] >> 56);
+        int prev = (i == 0) ? -1 : (int)(keys[i - 1] >> 56);
+        for (int q = prev + 1; q <= limb; ++q) s_lstart[q] = i;
+        if (i > 0 && (keys[i] >> 24) == (keys[i - 1] >> 24)) atomicOr(&s_flags, TFPD_FLAG_SCORE_TIE);
+    }
+    __syncthreads();
+
+    // ---- 2. greedy matching, one warp per limb (lane 0 walks; the walk is inherently serial) ----
+    int16_t *c1 = ws.conn_cid1 + (size_t)n * ws.max_cands;
+    int16_t *c2 = ws.conn_cid2 + (size_t)n * ws.max_cands;
+    float *cs = ws.conn_score + (size_t)n * ws.max_cands;
+    if (warp < kLimbs && lane == 0) {
+        const int limb = warp;
+        const int beg = s_lstart[limb], end = s_lstart[limb + 1];
+        uint32_t *ua = used + (size_t)limb * 2 * kBitmapWords, *ub = ua + kBitmapWords;
+        const int fa = s_first[c_limb_part[limb][0]], fb = s_first[c_limb_part[limb][1]];
+        int nconn = 0;
+        for (int i = beg; i < end; ++i) {
+            const unsigned long long key = keys[i];
+            const int a = (int)((key >> 12) & 0xfff), b = (int)(key & 0xfff);
+            if ((ua[a >> 5] >> (a & 31)) & 1u) continue;        // peak_id1 already assigned (:104-108)
+            if ((ub[b >> 5] >> (b & 31)) & 1u) continue;        // peak_id2 already assigned (:110-114)
+            ua[a >> 5] |= 1u << (a & 31);
+            ub[b >> 5] |= 1u << (b & 31);
+            c1[beg + nconn] = (int16_t)(fa + a);                // conn.cid1 = peak_a_list[idx1].id (:122)
+            c2[beg + nconn] = (int16_t)(fb + b);
+            cs[beg + nconn] = __uint_as_float(0xffffffffu - (uint32_t)((key >> 24) & 0xffffffffu));
+            ++nconn;
+        }
+        s_ccount[limb] = nconn;
+    }
+    __syncthreads();
+    if (tid < kLimbs) {
+        ws.conn_start[n * 20 + tid] = s_lstart[tid];
+        ws.conn_count[n * 20 + tid] = s_ccount[tid];
+    }
+    if (warp != 0) return;
+
+    // ---- 3. subset assembly (warp 0) ----
+    const float *pscore = ws.pk_score + (size_t)n * ws.max_peaks;
+    int nrows = 0;
+    bool row_overflow = false;
+    for (int limb = 0; limb < kLimbs; ++limb) {
+        const int pa = c_limb_part[limb][0], pb = c_limb_part[limb][1];
+        float *colA = rows + (size_t)pa * MR, *colB = rows + (size_t)pb * MR;
+        float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
+        const int beg = s_lstart[limb], nconn = s_ccount[limb];
+        for (int k = 0; k < nconn; ++k) {
+            const int cid1 = c1[beg + k], cid2 = c2[beg + k];
+            const float cscore = cs[beg + k];
+            const float f1 = (float)cid1, f2 = (float)cid2;
+            int found = 0, r1 = 0, r2 = 0;
+            for (int base = 0; base < nrows; base += 32) {
+                const int r = base + lane;
+                const bool hit = (r < nrows) && (colA[r] == f1 || colB[r] == f2);       // :137
+                unsigned bits = __ballot_sync(0xffffffffu, hit);
+                if (bits) {
+                    if (found == 0) {
+                        r1 = base + __ffs(bits) - 1;
+                        unsigned rest = bits & (bits - 1);
+                        if (rest) r2 = base + __ffs(rest) - 1;
+                    } else if (found == 1) {
+                        r2 = base + __ffs(bits) - 1;
+                    }
+                    found += __popc(bits);
+                }
+            }
+            if (found == 1) {
+                if (lane == 0 && colB[r1] != f2) {                                      // :144-149
+                    colB[r1] = f2;
+                    col19[r1] = __fadd_rn(col19[r1], 1.0f);
+                    col18[r1] = __fadd_rn(col18[r1], __fadd_rn(pscore[cid2], cscore));
+                }
+            } else if (found == 2) {
+                bool merge = false;
+                if (th.mode == TFPD_MODE_UPSTREAM) {
+                    // membership stays 0 iff no part k has both rows > 0 (:153-157)
+                    bool both = (lane < kParts) && (rows[(size_t)lane * MR + r1] > 0.0f) &&
+                                (rows[(size_t)lane * MR + r2] > 0.0f);
+                    merge = (__ballot_sync(0xffffffffu, both) == 0u);
+                }
+                if (merge) {                                                           // :159-165
+                    if (lane < kParts) {
+                        float *cc = rows + (size_t)lane * MR;
+                        cc[r1] = __fadd_rn(cc[r1], __fadd_rn(cc[r2], 1.0f));
+                    } else if (lane == 18) {
+                        col18[r1] = __fadd_rn(__fadd_rn(col18[r1], col18[r2]), cscore);
+                    } else if (lane == 19) {
+                        col19[r1] = __fadd_rn(col19[r1], col19[r2]);
+                    }
+                    __syncwarp();
+                    // subset.erase(begin + r2): shift the later rows up by one, column by column
+                    for (int c = 0; c < 20; ++c) {
+                        float *cc = rows + (size_t)c * MR;
+                        for (int base = r2; base < nrows - 1; base += 32) {
+                            const int r = base + lane;
+                            float v = 0.f;
+                            if (r < nrows - 1) v = cc[r + 1];
+                            __syncwarp();
+                            if (r < nrows - 1) cc[r] = v;
+                            __syncwarp();
+                        }
+                    }
+                    --nrows;
+                } else if (lane == 0) {                                                // :166-170
+                    colB[r1] = f2;
+                    col19[r1] = __fadd_rn(col19[r1], 1.0f);
+                    col18[r1] = __fadd_rn(col18[r1], __fadd_rn(pscore[cid2], cscore));
+                }
+            } else if (found == 0 && limb < 17) {                                      // :171-181
+                if (nrows < MR) {
+                    if (lane < 20) {
+                        float v = -1.0f;
+                        if (lane == pa) v = f1;
+                        if (lane == pb) v = f2;
+                        if (lane == 19) v = 2.0f;
+                        if (lane == 18) v = __fadd_rn(__fadd_rn(pscore[cid1], pscore[cid2]), cscore);
+                        rows[(size_t)lane * MR + nrows] = v;
+                    }
+                    ++nrows;
+                } else {
+                    row_overflow = true;
+                }
+            } else if (found > 2) {
+                if (lane == 0) atomicOr(&s_flags, TFPD_FLAG_FOUND_GT2);
+            }
+            __syncwarp();
+        }
+    }
+
+    // ---- 4. filter (:185-189) + getter view ----
+    const float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
+    const int16_t *pkx = ws.pk_x + (size_t)n * ws.max_peaks, *pky = ws.pk_y + (size_t)n * ws.max_peaks;
+    tfpd_human *out = ws.humans + (size_t)n * ws.max_humans;
+    int nh = 0;
+    bool human_overflow = false;
+    for (int base = 0; base < nrows; base += 32) {
+        const int r = base + lane;
+        bool keep = false;
+        if (r < nrows) {
+            const float cntf = col19[r], sc = col18[r];
+            keep = !(cntf < (float)th.part_cnt || __fdiv_rn(sc, cntf) < th.human_score);
+        }
+        const unsigned bits = __ballot_sync(0xffffffffu, keep);
+        const int slot = nh + __popc(bits & ((1u << lane) - 1u));
+        if (keep) {
+            if (slot < ws.max_humans) {
+                tfpd_human *hm = out + slot;
+                hm->score = __fdiv_rn(col18[r], col19[r]);                             // get_score (:202-204)
+#pragma unroll 1
+                for (int p = 0; p < kParts; ++p) {
+                    const int cid = (int)rows[(size_t)p * MR + r];                     // get_part_cid (:198-200)
+                    hm->cid[p] = (int16_t)cid;
+                    hm->x[p] = (cid >= 0) ? pkx[cid] : (int16_t)-1;
+                    hm->y[p] = (cid >= 0) ? pky[cid] : (int16_t)-1;
+                    hm->part_score[p] = (cid >= 0) ? pscore[cid] : 0.0f;
+                }
+            } else {
+                human_overflow = true;
+            }
+        }
+        nh += __popc(bits);
+    }
+    human_overflow = __any_sync(0xffffffffu, human_overflow);
+    if (lane == 0) {
+        int flags = s_flags | ws.counters[n].flags;
+        if (row_overflow) flags |= TFPD_FLAG_ROW_OVERFLOW;
+        if (human_overflow) flags |= TFPD_FLAG_HUMAN_OVERFLOW;
+        ws.info[n].n_humans = min(nh, ws.max_humans);
+        ws.info[n].n_cands = cnt;
+        ws.info[n].n_rows = nrows;
+        ws.info[n].flags = flags;
+    }
+}
+
+}  // namespace
+
+size_t assemble_smem_bytes(const Workspace &ws) {
+    return (size_t)ws.max_cands * 8 + (size_t)20 * ws.max_rows * 4 + (size_t)kLimbs * 2 * kBitmapWords * 4;
+}
+
+int launch_assemble(const Workspace &ws, int N, const Thresholds &th, cudaStream_t s) {
+    size_t smem = assemble_smem_bytes(ws);
+    static size_t attr_smem = 0;
+    if (smem > 48 * 1024 && smem > attr_smem) {
+        if (cudaFuncSetAttribute(k_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return -1;
+        attr_smem = smem;
+    }
+    k_assemble<<<N, kK3Threads, smem, s>>>(ws, th);
+    return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+}  // namespace tfpd

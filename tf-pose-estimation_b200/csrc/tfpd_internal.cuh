@@ -1,0 +1,108 @@
+// tfpd_internal.cuh -- shared declarations of the decode kernels (not part of the C-ABI).
+//
+// Data layout in HBM (all per ctx, sized for max_batch frames):
+//   net_out   X[N,h,w,57]  f32 NHWC   caller-owned   heat = ch 0..18, PAF = ch 19..56 (estimator.py:321-322)
+//   dense     heat_up[N,H,W,19], paf_up[N,H,W,38], peaks[N,H,W,19]   caller-owned, optional
+//   rec_key/rec_val [N,max_peaks]   unsorted peak records appended by K1 (key = part|y|x)
+//   pk_x/pk_y/pk_score [N,max_peaks], part_first[N,20]   peak table, id = index (pafprocess.cpp:24-44)
+//   cand_key [N,max_cands] u64      accepted limb candidates (limb|~score|a|b)
+//   conn_* [N,max_cands]            accepted connections, limb-major (pafprocess.cpp:96-124)
+//   humans [N,max_humans] tfpd_human, info[N] tfpd_frame_info
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "tfpose_decode.h"
+
+namespace tfpd {
+
+constexpr int kParts = TFPD_NUM_PARTS;
+constexpr int kLimbs = TFPD_NUM_LIMBS;
+constexpr int kHeatC = TFPD_HEAT_CHANNELS;
+constexpr int kPafC = TFPD_PAF_CHANNELS;
+constexpr int kNetC = TFPD_NET_CHANNELS;
+constexpr int kStepPaf = 10;               // pafprocess.h:13
+constexpr int kMaxPeaksHard = 4096;        // 12-bit per-part indices inside the candidate key
+
+// limb tables, pafprocess.h:16-24 (one copy per translation unit; no relocatable device code)
+static __constant__ int c_limb_part[kLimbs][2] = {{1, 2},  {1, 5},   {2, 3},   {3, 4},  {5, 6},   {6, 7},  {1, 8},
+                                                  {8, 9},  {9, 10},  {1, 11},  {11, 12}, {12, 13}, {1, 0},  {0, 14},
+                                                  {14, 16}, {0, 15}, {15, 17}, {2, 16}, {5, 17}};
+static __constant__ int c_limb_chan[kLimbs][2] = {{12, 13}, {20, 21}, {14, 15}, {16, 17}, {22, 23}, {24, 25}, {0, 1},
+                                                  {2, 3},   {4, 5},   {6, 7},   {8, 9},   {10, 11}, {28, 29}, {30, 31},
+                                                  {34, 35}, {32, 33}, {36, 37}, {18, 19}, {26, 27}};
+
+// peak record key: part(5) | y(13) | x(14)  -> ascending key order == (part, y, x) order
+__host__ __device__ inline uint32_t peak_key(int part, int y, int x) {
+    return ((uint32_t)part << 27) | ((uint32_t)y << 14) | (uint32_t)x;
+}
+__host__ __device__ inline int key_part(uint32_t k) { return (int)(k >> 27); }
+__host__ __device__ inline int key_y(uint32_t k) { return (int)((k >> 14) & 0x1FFF); }
+__host__ __device__ inline int key_x(uint32_t k) { return (int)(k & 0x3FFF); }
+
+struct Thresholds {
+    float heat, vector_score, human_score;
+    int vector_cnt1, part_cnt;
+    int mode;
+};
+
+// per-frame counters zeroed before every call (one cudaMemsetAsync)
+struct FrameCounters {
+    int n_peak_rec;     // records appended by K1 / the dense scan (may exceed max_peaks)
+    int near_ties;
+    int n_cand;         // candidates appended by K2 (may exceed max_cands)
+    int flags;
+};
+
+struct Workspace {
+    int max_batch, max_peaks, max_cands, max_rows, max_humans;
+    FrameCounters *counters;    // [N]
+    uint32_t *rec_key;          // [N,max_peaks]
+    float *rec_val;             // [N,max_peaks]
+    int16_t *pk_x, *pk_y;       // [N,max_peaks]
+    float *pk_score;            // [N,max_peaks]
+    int *part_first;            // [N,20]  first[part], first[18] = n_peaks (19 = pad)
+    unsigned long long *cand_key;   // [N,max_cands]
+    int16_t *conn_cid1, *conn_cid2; // [N,max_cands]
+    float *conn_score;          // [N,max_cands]
+    int *conn_start;            // [N,20]  segment start per limb inside conn_* ; [19] = unused
+    int *conn_count;            // [N,20]
+    tfpd_human *humans;         // [N,max_humans]
+    tfpd_frame_info *info;      // [N]
+};
+
+// Where limb scoring reads PAF vectors from.
+struct PafSource {
+    const float *base;      // X (lowres, 57 ch) or paf_up (dense, 38 ch)
+    int rows, cols;         // spatial dims of `base`
+    int chan, chan_off;     // channels per pixel, offset of PAF channel 0
+    int shift;              // lowres: log2(upsample factor) applied to sample coords; dense: 0
+    int H;                  // upsampled height h1 used in the length penalty (pafprocess.cpp:83)
+};
+
+struct K1Params {
+    const float *X;
+    float *heat_up, *paf_up, *peaks;    // dense outputs or null
+    uint32_t *rec_key;
+    float *rec_val;
+    FrameCounters *counters;
+    int max_peaks;
+    int N, h, w;                        // low-res dims; H = 4h, W = 4w
+    int band_rows, nbands, chunk_cells, nchunks, nitems;
+    float thresh;
+};
+
+// launchers (each returns the number of kernel launches it issued, <0 on launch error)
+int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t s);
+int upload_polyphase_weights(const double *s1d, int ksize);     // F=4, ksize=25 fast path
+int launch_generic_maps(const float *X, int N, int h, int w, int H, int W, const float *d_k1d, int ksize,
+                        float *heat_up, float *paf_up, float *peaks, float *scratch, const Workspace &ws, float thr,
+                        cudaStream_t s);
+int launch_scan_dense_peaks(const float *peaks, const float *heat, int N, int H, int W, float thresh,
+                            const Workspace &ws, cudaStream_t s);
+int launch_sort_peaks(const Workspace &ws, int N, cudaStream_t s);
+int launch_limb_score(const Workspace &ws, int N, const PafSource &src, size_t frame_stride,
+                      const Thresholds &th, int sm_count, cudaStream_t s);
+int launch_assemble(const Workspace &ws, int N, const Thresholds &th, cudaStream_t s);
+size_t assemble_smem_bytes(const Workspace &ws);
+
+}  // namespace tfpd

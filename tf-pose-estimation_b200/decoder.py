@@ -1,0 +1,241 @@
+"""Host side of seam 1: network output -> humans, over the C-ABI.
+
+``PoseDecoder`` owns one ``tfpd_ctx`` (one GPU, one thread at a time).  It replaces what
+``TfPoseEstimator.inference`` does after the network forward (tf_pose/estimator.py:536-551):
+the resize_area / smoother / NMS graph ops and ``PoseEstimator.estimate_paf``.
+
+PyTorch tensors are used only as device buffers (``data_ptr()``); NumPy arrays go through
+``tfpd_decode_host`` which does the host<->device copies itself.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .humans import BodyPart, Human
+
+
+def upsample_size_for(target_w, target_h, ratio=4.0):
+    """[H, W] exactly as inference() computes it (estimator.py:522-523) for
+    ``resize_to_default=True``: ``int(target / 8 * ratio)``."""
+    return [int(target_h / 8 * ratio), int(target_w / 8 * ratio)]
+
+
+def humans_from_table(table_row, n_humans, H, W):
+    """Build ``Human``/``BodyPart`` objects from one frame's tfpd_human records the way
+    PoseEstimator.estimate_paf does from the getters (estimator.py:277-297)."""
+    humans = []
+    for human_id in range(int(n_humans)):
+        rec = table_row[human_id]
+        human = Human([])
+        is_added = False
+        cids, xs, ys, ps = rec["cid"], rec["x"], rec["y"], rec["part_score"]
+        for part_idx in range(18):
+            if int(cids[part_idx]) < 0:
+                continue
+            is_added = True
+            human.body_parts[part_idx] = BodyPart(
+                '%d-%d' % (human_id, part_idx), part_idx,
+                float(int(xs[part_idx])) / W, float(int(ys[part_idx])) / H, float(ps[part_idx]))
+        if is_added:
+            human.score = float(rec["score"])
+            humans.append(human)
+    return humans
+
+
+class DecodeResult(object):
+    """Per-frame tables of one decode call, already on the host.  ``Human`` objects are built
+    lazily: the tables are the transport format (also what the multi-GPU gather moves)."""
+
+    def __init__(self, info, table, H, W):
+        self.info = info        # structured [N]: n_humans, n_peaks, n_cands, flags, near_ties, n_rows
+        self.table = table      # structured [N, max_humans] (tfpd_human)
+        self.H, self.W = H, W
+
+    def __len__(self):
+        return len(self.info)
+
+    def humans(self, frame=0):
+        return humans_from_table(self.table[frame], self.info["n_humans"][frame], self.H, self.W)
+
+    def all_humans(self):
+        return [self.humans(i) for i in range(len(self.info))]
+
+    def compact(self):
+        """(counts[N] int32, records[sum(counts)] tfpd_human) -- what the gather ships."""
+        counts = self.info["n_humans"].astype(np.int32)
+        recs = np.concatenate([self.table[i, :counts[i]] for i in range(len(counts))]) if len(counts) else \
+            np.empty(0, _lib.HUMAN_DTYPE)
+        return counts, recs
+
+
+class PoseDecoder(object):
+    def __init__(self, max_batch=1, max_upsample=(368, 656), device=0, mode="asbuilt", **overrides):
+        """max_upsample = (H, W) of the largest upsampled map.  ``overrides`` are further
+        ``tfpd_config`` fields (thresholds, blur_ksize/blur_sigma, max_peaks, max_cands, ...)."""
+        L = _lib.lib()
+        cfg = _lib.default_config(device=int(device), max_batch=int(max_batch), max_h=int(max_upsample[0]),
+                                  max_w=int(max_upsample[1]),
+                                  mode={"asbuilt": _lib.MODE_ASBUILT, "upstream": _lib.MODE_UPSTREAM}[mode],
+                                  **overrides)
+        self._L = L
+        self._ctx = C.c_void_p()
+        rc = L.tfpd_create(C.byref(cfg), C.byref(self._ctx))
+        if rc != _lib.OK:
+            msg = L.tfpd_last_error(None).decode()
+            self._ctx = None
+            raise _lib.DecodeError(rc, msg)
+        self.cfg = cfg
+        self.max_batch = int(max_batch)
+        self.max_humans = int(cfg.max_humans)
+        self.device = int(device)
+        self._shape = None      # (N, H, W) of the last call
+        self._keep = None       # buffers borrowed by the in-flight call
+
+    # -- lifetime ------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._L.tfpd_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc):
+        if rc != _lib.OK:
+            msg = self._L.tfpd_last_error(self._ctx).decode()
+            raise (_lib.CapacityError if rc == _lib.ERR_CAPACITY else _lib.DecodeError)(rc, msg)
+
+    # -- seam 1 --------------------------------------------------------------------------
+    def decode_async(self, net_out, upsample_size, dense=None, stream=None):
+        """Enqueue the decode of a CUDA tensor ``net_out[N,h,w,57]`` (float32, contiguous) on
+        ``stream`` (default: torch's current stream).  ``dense`` = (heat_up, paf_up, peaks) CUDA
+        tensors to fill ([N,H,W,19], [N,H,W,38], [N,H,W,19]) or None for minimal mode."""
+        import torch
+        if not (isinstance(net_out, torch.Tensor) and net_out.is_cuda):
+            raise TypeError("decode_async wants a CUDA torch.Tensor; use decode_host for NumPy arrays")
+        if net_out.dtype != torch.float32 or not net_out.is_contiguous() or net_out.dim() != 4:
+            raise ValueError("net_out must be a contiguous float32 [N,h,w,57] tensor")
+        N, h, w, c = net_out.shape
+        if c != 57:
+            raise ValueError("net_out must have 57 channels (19 heat + 38 PAF), got %d" % c)
+        if net_out.device.index != self.device:
+            raise ValueError("net_out is on cuda:%s, decoder on cuda:%d" % (net_out.device.index, self.device))
+        H, W = int(upsample_size[0]), int(upsample_size[1])
+        dptr = None
+        if dense is not None:
+            hu, pu, pk = dense
+            for t, ch in ((hu, 19), (pu, 38), (pk, 19)):
+                if tuple(t.shape) != (N, H, W, ch) or t.dtype != torch.float32 or not t.is_contiguous() \
+                        or not t.is_cuda:
+                    raise ValueError("dense outputs must be contiguous float32 CUDA [N,H,W,19|38|19]")
+            dptr = _lib.Dense(hu.data_ptr(), pu.data_ptr(), pk.data_ptr())
+        if stream is None:
+            stream = torch.cuda.current_stream(net_out.device)
+        sptr = C.c_void_p(stream.cuda_stream)
+        self._keep = (net_out, dense)
+        self._check(self._L.tfpd_decode_device(self._ctx, net_out.data_ptr(), N, h, w, H, W, sptr,
+                                               C.byref(dptr) if dptr is not None else None))
+        self._shape = (N, H, W)
+
+    def fetch(self):
+        """Wait for the enqueued decode and return its tables (``DecodeResult``)."""
+        if self._shape is None:
+            raise _lib.DecodeError(_lib.ERR_STATE, "fetch() before decode")
+        N, H, W = self._shape
+        info = np.empty(N, _lib.INFO_DTYPE)
+        table = np.empty((N, self.max_humans), _lib.HUMAN_DTYPE)
+        self._check(self._L.tfpd_fetch_humans(self._ctx, table.ctypes.data, info.ctypes.data))
+        self._keep = None
+        return DecodeResult(info, table, H, W)
+
+    def decode(self, net_out, upsample_size, dense=None, stream=None):
+        """CUDA tensor in -> DecodeResult (synchronous)."""
+        self.decode_async(net_out, upsample_size, dense=dense, stream=stream)
+        return self.fetch()
+
+    def decode_host(self, net_out, upsample_size, want_dense=False):
+        """NumPy ``net_out[N,h,w,57]`` (or [h,w,57]) in host memory -> DecodeResult; with
+        ``want_dense`` also returns (heat_up, paf_up, peaks) NumPy arrays, i.e. everything one
+        ``sess.run`` + ``estimate_paf`` of the reference yields (estimator.py:536-551)."""
+        x = np.ascontiguousarray(net_out, np.float32)
+        if x.ndim == 3:
+            x = x[None]
+        if x.ndim != 4 or x.shape[3] != 57:
+            raise ValueError("net_out must be [N,h,w,57]")
+        N, h, w, _ = x.shape
+        H, W = int(upsample_size[0]), int(upsample_size[1])
+        hu = pu = pk = None
+        if want_dense:
+            hu = np.empty((N, H, W, 19), np.float32)
+            pu = np.empty((N, H, W, 38), np.float32)
+            pk = np.empty((N, H, W, 19), np.float32)
+        self._shape = None
+        self._check(self._L.tfpd_decode_host(self._ctx, x.ctypes.data, N, h, w, H, W,
+                                             hu.ctypes.data if want_dense else None,
+                                             pu.ctypes.data if want_dense else None,
+                                             pk.ctypes.data if want_dense else None))
+        self._shape = (N, H, W)
+        res = self.fetch()
+        return (res, (hu, pu, pk)) if want_dense else res
+
+    # -- introspection -------------------------------------------------------------------
+    def peaks(self, frame=0):
+        """dict(part, x, y, score) of int32/float32 arrays: the peak table of a frame."""
+        cap = int(self.cfg.max_peaks) * 2
+        part, x, y = (np.empty(cap, np.int32) for _ in range(3))
+        score = np.empty(cap, np.float32)
+        n = C.c_int(0)
+        self._check(self._L.tfpd_fetch_peaks(self._ctx, frame, cap, part.ctypes.data, x.ctypes.data,
+                                             y.ctypes.data, score.ctypes.data, C.byref(n)))
+        k = min(n.value, cap)
+        return {"part": part[:k].copy(), "x": x[:k].copy(), "y": y[:k].copy(), "score": score[:k].copy()}
+
+    def connections(self, frame=0):
+        """dict(limb, cid1, cid2, score): accepted connections, limb-major, acceptance order."""
+        cap = int(self.cfg.max_cands) * 4
+        limb, c1, c2 = (np.empty(cap, np.int32) for _ in range(3))
+        score = np.empty(cap, np.float32)
+        n = C.c_int(0)
+        self._check(self._L.tfpd_fetch_connections(self._ctx, frame, cap, limb.ctypes.data, c1.ctypes.data,
+                                                   c2.ctypes.data, score.ctypes.data, C.byref(n)))
+        k = min(n.value, cap)
+        return {"limb": limb[:k].copy(), "cid1": c1[:k].copy(), "cid2": c2[:k].copy(), "score": score[:k].copy()}
+
+    def set_profiling(self, on=True):
+        self._check(self._L.tfpd_set_profiling(self._ctx, 1 if on else 0))
+
+    def stage_ms(self):
+        """[K1 maps, peak sort, K2 limb scoring, K3 assembly] device ms of the last call."""
+        out = (C.c_float * 4)()
+        self._check(self._L.tfpd_last_stage_ms(self._ctx, C.byref(out)))
+        return [float(v) for v in out]
+
+    def launch_count(self):
+        return int(self._L.tfpd_last_launch_count(self._ctx))
+
+    # -- seam 2 (used by the pafprocess module) ------------------------------------------
+    def process_paf(self, peaks, heat_mat, paf_mat):
+        arrs = []
+        for a in (peaks, heat_mat, paf_mat):
+            a = np.ascontiguousarray(a, np.float32)   # swig IN_ARRAY3 semantics (pafprocess_wrap.cpp:4935-4968)
+            if a.ndim != 3:
+                raise ValueError("Array must have 3 dimensions.  Given array has %d dimensions" % a.ndim)
+            arrs.append(a)
+        p, h, f = arrs
+        self._shape = None
+        rc = self._L.tfpd_process_paf(self._ctx, p.shape[0], p.shape[1], p.shape[2], p.ctypes.data,
+                                      h.shape[0], h.shape[1], h.shape[2], h.ctypes.data,
+                                      f.shape[0], f.shape[1], f.shape[2], f.ctypes.data)
+        self._check(rc)
+        self._shape = (1, p.shape[0], p.shape[1])
+        return 0

@@ -1,0 +1,100 @@
+"""The reference-facing operator interface of the decode path.
+
+* ``PoseEstimator.estimate_paf(peaks, heat_mat, paf_mat)`` -- same name, arguments and result as
+  tf_pose/estimator.py:272-299, running on the GPU through the ``pafprocess`` drop-in (seam 2).
+* ``TfPosePostProcessor`` -- the part of ``TfPoseEstimator`` after the network forward
+  (tf_pose/estimator.py:321-337 graph ops + :536-551): give it the tensor the frozen graph
+  calls ``Openpose/concat_stage7`` and get ``inference()``'s return value, with the same
+  ``heatMat`` / ``pafMat`` side effects (:545-546).  Seam 1.
+
+The network forward itself (TF1 frozen graphs) is outside this repository's scope.
+"""
+import numpy as np
+
+from . import pafprocess
+from .decoder import PoseDecoder, upsample_size_for
+from .humans import BodyPart, Human
+
+
+class PoseEstimator(object):
+    def __init__(self):
+        pass
+
+    @staticmethod
+    def estimate_paf(peaks, heat_mat, paf_mat):
+        pafprocess.process_paf(peaks, heat_mat, paf_mat)
+        humans = []
+        H, W = heat_mat.shape[0], heat_mat.shape[1]
+        for human_id in range(pafprocess.get_num_humans()):
+            human = Human([])
+            is_added = False
+            for part_idx in range(18):
+                c_idx = int(pafprocess.get_part_cid(human_id, part_idx))
+                if c_idx < 0:
+                    continue
+                is_added = True
+                human.body_parts[part_idx] = BodyPart(
+                    '%d-%d' % (human_id, part_idx), part_idx,
+                    float(pafprocess.get_part_x(c_idx)) / W,
+                    float(pafprocess.get_part_y(c_idx)) / H,
+                    pafprocess.get_part_score(c_idx))
+            if is_added:
+                human.score = pafprocess.get_score(human_id)
+                humans.append(human)
+        return humans
+
+
+class TfPosePostProcessor(object):
+    """``TfPoseEstimator`` minus the TensorFlow session.
+
+    target_size = (w, h) of the network input like the reference ctor (estimator.py:305-306).
+    ``inference_from_output(net_out, upsample_size=4.0)`` mirrors
+    ``inference(npimg, resize_to_default=True, upsample_size=...)`` from the point where the
+    session returns: it sets ``self.heatMat`` / ``self.pafMat`` (when ``keep_maps``) and returns
+    ``list[Human]``.
+    """
+
+    def __init__(self, target_size=(432, 368), device=0, mode="asbuilt", keep_maps=True, max_ratio=8.0,
+                 **overrides):
+        self.target_size = target_size
+        self.keep_maps = keep_maps
+        H, W = upsample_size_for(target_size[0], target_size[1], max_ratio)
+        self._decoder = PoseDecoder(max_batch=1, max_upsample=(H, W), device=device, mode=mode, **overrides)
+        self.heatMat = self.pafMat = None
+        self.peaks = None
+        self.last_info = None
+
+    def inference_from_output(self, net_out, upsample_size=1.0, input_hw=None):
+        """net_out: [1,h,w,57] or [h,w,57] NumPy array or CUDA tensor.  ``input_hw`` plays the
+        role of ``npimg.shape[:2]`` when ``resize_to_default`` is False (estimator.py:524-525)."""
+        if net_out is None:
+            raise Exception('The network output is not valid.')
+        if input_hw is None:
+            size = upsample_size_for(self.target_size[0], self.target_size[1], upsample_size)
+        else:
+            size = [int(input_hw[0] / 8 * upsample_size), int(input_hw[1] / 8 * upsample_size)]
+        is_numpy = isinstance(net_out, np.ndarray)
+        if is_numpy:
+            out = self._decoder.decode_host(net_out, size, want_dense=self.keep_maps)
+            if self.keep_maps:
+                res, (hu, pu, pk) = out
+                self.peaks, self.heatMat, self.pafMat = pk[0], hu[0], pu[0]
+            else:
+                res = out
+        else:
+            import torch
+            x = net_out if net_out.dim() == 4 else net_out.unsqueeze(0)
+            dense = None
+            if self.keep_maps:
+                n = x.shape[0]
+                dense = (torch.empty((n, size[0], size[1], 19), device=x.device),
+                         torch.empty((n, size[0], size[1], 38), device=x.device),
+                         torch.empty((n, size[0], size[1], 19), device=x.device))
+            res = self._decoder.decode(x.contiguous(), size, dense=dense)
+            if self.keep_maps:
+                self.heatMat, self.pafMat, self.peaks = dense[0][0], dense[1][0], dense[2][0]
+        self.last_info = res.info[0]
+        return res.humans(0)
+
+    def close(self):
+        self._decoder.close()
