@@ -1,0 +1,374 @@
+#!/usr/bin/env python
+"""bench.py -- decoded frames/s of the heatmap/PAF decode path (BASELINE.json metric).
+
+Workload (BASELINE.json configs[1]): mobilenet_thin 432x368 network outputs, i.e. X[64,46,54,57]
+float32 per GPU, upsample x4 -> 184x216, synthetic skeleton maps (tf-pose-estimation_b200/synth.py),
+full decode to humans.  One "step" = one batch of 64 frames through the hot path:
+  K1 fused upsample+smoother+NMS (dense outputs written: heat_up, paf_up, peaks -- the three
+  tensors the reference's sess.run returns) -> peak sort -> K2 limb scoring -> K3 assembly ->
+  human tables copied to the host.
+
+  value      frames/s with the inputs resident in HBM (dense mode), CUDA-event timed.
+  e2e        frames/s through the host-buffer C-ABI call (tfpd_decode_host): pinned host input,
+             H2D inside the timed region, human tables D2H.  Dense maps stay on the device
+             (inference() returns humans; e2e_dense_maps also ships the three maps back).
+  roofline   fused K1 kernel: algorithmic bytes 4*(57hw + 76HW) per frame / its CUDA-event time,
+             against MEASURED_PEAKS.json hbm_gbs.
+  cpu_baseline / --impl reference: the same decode on the host cores: the C restatement of the
+             TF ops (TensorFlow itself is not available) + the reference's own pafprocess.cpp
+             (oracle/_ref), one process per core.
+
+Multi-GPU: frames are independent, the batch is sharded by image (each rank decodes its own 64
+frames: weak scaling); no collective on the data path, only the timing reduction and a final
+gather of the human counts.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+H_LOW, W_LOW, FACTOR = 46, 54, 4          # mobilenet_thin @432x368: 368/8 x 432/8
+BATCH = 64
+CONFIG_ID = 2
+N_INPUT_SETS = 4                          # rotate inputs: 4 x 36 MB > L2 together with 773 MB of outputs/step
+WORKLOAD = ("mobilenet_thin 432x368 decode, batch %d per GPU, 46x54x57 -> 184x216 (upsample x4), "
+            "dense maps (heat_up+paf_up+peaks) produced, humans to host")
+
+
+def dense_bytes_per_frame(h, w, f):
+    return 4 * (57 * h * w + 76 * (f * h) * (f * w))
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        threading.Thread.__init__(self, daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def result(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------ CPU arm
+_CPU_X = None
+
+
+def _cpu_decode_one(i):
+    """One frame on one core: restated TF ops (C oracle) + the reference's pafprocess.cpp."""
+    from oracle import oracle as O
+    global _CPU_REF
+    x = _CPU_X[i % len(_CPU_X)]
+    H, W = FACTOR * x.shape[0], FACTOR * x.shape[1]
+    peaks, heat_up, paf_up, _ = O.dense_maps(x, H, W)
+    ref = globals().get("_CPU_REF")
+    if ref is None:
+        try:
+            ref = O.ReferencePafprocess("asbuilt")
+        except Exception:
+            ref = False
+        globals()["_CPU_REF"] = ref
+    if ref:
+        ref.process_paf(peaks, heat_up, paf_up)
+        return len(ref.humans_as_tuples())
+    return len(O.process_paf(peaks, heat_up, paf_up).humans_as_tuples())
+
+
+def cpu_decode_rate(x, frames_per_step, steps, warmup, cores):
+    """frames/s of the CPU decode with `cores` worker processes."""
+    import multiprocessing as mp
+    from oracle import oracle as O
+    O.build()
+    global _CPU_X
+    _CPU_X = x
+    kind = "reference+port" if os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libpafprocess_asbuilt.so")) else "port"
+    ctx = mp.get_context("fork")
+    with ctx.Pool(cores) as pool:
+        for _ in range(warmup):
+            pool.map(_cpu_decode_one, range(frames_per_step), chunksize=1)
+        t0 = time.perf_counter()
+        humans = 0
+        for s in range(steps):
+            humans += sum(pool.map(_cpu_decode_one, range(s * frames_per_step, (s + 1) * frames_per_step), chunksize=1))
+        dt = time.perf_counter() - t0
+    return frames_per_step * steps / dt, dt, humans, kind
+
+
+def host_cores():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    from tfpose_b200 import synth
+    cores = host_cores()
+    x = synth.synth_batch(min(BATCH, 32), H_LOW, W_LOW, config_id=CONFIG_ID)
+    # bounded sample per step: ~0.45 s per frame per core -> keep the whole run within minutes
+    per_step = max(cores, 8)
+    budget_s = 150.0
+    est = 0.5 * per_step * (args.steps + args.warmup) / cores
+    if est > budget_s:
+        per_step = max(1, int(per_step * budget_s / est))
+    rate, dt, humans, kind = cpu_decode_rate(x, per_step, args.steps, args.warmup, cores)
+    sample = "%d synthetic 46x54x57 frames per step (of the 64-frame batch), %d worker processes" % (per_step, cores)
+    line = {
+        "impl": "reference", "metric": "decoded_frames_per_s", "value": rate, "unit": "frames/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD % BATCH, "batch_per_gpu": BATCH, "global_batch": BATCH * world,
+                   "sharding": "by image, no collective", "mode": "asbuilt",
+                   "reference_sample_frames_per_step": per_step},
+        "cpu_baseline": {"value": rate, "unit": "frames/s", "cores": cores, "kind": "reference" if kind != "port" else "port",
+                         "sample": sample + "; maps = C restatement of the TF ops (TensorFlow unavailable on this box), "
+                                            "pafprocess = reference's own pafprocess.cpp (oracle/_ref)"},
+        "e2e": {"value": rate, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "humans_decoded": humans,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import tfpose_b200 as tp
+    from tfpose_b200 import synth, _lib
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    h, w, f = H_LOW, W_LOW, FACTOR
+    H, W = f * h, f * w
+    B = args.batch
+
+    # synthetic inputs: N_INPUT_SETS different batches per rank (frame seeds never repeat across ranks)
+    sets_host = []
+    for sidx in range(N_INPUT_SETS):
+        base = synth.synth_batch(min(B, 16), h, w, config_id=CONFIG_ID, first_frame=(rank * N_INPUT_SETS + sidx) * 16)
+        reps = (B + len(base) - 1) // len(base)
+        sets_host.append(np.concatenate([base] * reps)[:B].copy())
+    x_dev = [torch.from_numpy(s).to(dev) for s in sets_host]
+    x_pin = [torch.from_numpy(s).pin_memory() for s in sets_host]
+    dense = (torch.empty((B, H, W, 19), device=dev), torch.empty((B, H, W, 38), device=dev),
+             torch.empty((B, H, W, 19), device=dev))
+
+    dec = tp.PoseDecoder(max_batch=B, max_upsample=(H, W), device=local_rank)
+    dec.set_profiling(True)
+    stream = torch.cuda.current_stream(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return ms
+
+    # ---- device-resident: value ----
+    humans_total = 0
+    near_ties = 0
+    for i in range(args.warmup):
+        dec.decode(x_dev[i % N_INPUT_SETS], (H, W), dense=dense)
+    k1_ms, stage_acc = [], np.zeros(4)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    launches = 0
+    for i in range(args.steps):
+        res = dec.decode(x_dev[i % N_INPUT_SETS], (H, W), dense=dense)
+        st = dec.stage_ms()
+        k1_ms.append(st[0])
+        stage_acc += np.array(st)
+        launches += dec.launch_count()
+        humans_total += int(res.info["n_humans"].sum())
+        near_ties += int(res.info["near_ties"].sum())
+    ev1.record(stream)
+    barrier()
+    sampler.stop_flag = True
+    sampler.join()
+    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+    ms_per_step = ms_total / args.steps
+    value = world * B * args.steps / (ms_total * 1e-3)
+
+    # ---- minimal mode (no dense tensors written), device-resident ----
+    for i in range(args.warmup):
+        dec.decode(x_dev[i % N_INPUT_SETS], (H, W))
+    barrier()
+    ev0.record(stream)
+    for i in range(args.steps):
+        dec.decode(x_dev[i % N_INPUT_SETS], (H, W))
+    ev1.record(stream)
+    barrier()
+    ms_min = max_over_ranks(ev0.elapsed_time(ev1))
+    value_min = world * B * args.steps / (ms_min * 1e-3)
+
+    # ---- end to end through the host-buffer C-ABI call ----
+    h2d = B * h * w * 57 * 4
+    d2h = B * _lib.INFO_DTYPE.itemsize + B * dec.max_humans * _lib.HUMAN_DTYPE.itemsize
+    xs_np = [t.numpy() for t in x_pin]
+    legacy = torch.cuda.default_stream(dev)
+    for i in range(args.warmup):
+        dec.decode_host(xs_np[i % N_INPUT_SETS], (H, W))
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        r = dec.decode_host(xs_np[i % N_INPUT_SETS], (H, W))
+    torch.cuda.synchronize(dev)
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+    barrier()
+    e2e_value = world * B * args.steps / (e2e_ms * 1e-3)
+    e2e_humans = int(r.info["n_humans"].sum())
+
+    # ---- end to end including the three dense maps back on the host (what sess.run returns) ----
+    e2e_dense_value = None
+    if args.e2e_dense:
+        ksteps = max(2, min(args.steps, 5))
+        dec.decode_host(xs_np[0], (H, W), want_dense=True)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(ksteps):
+            dec.decode_host(xs_np[i % N_INPUT_SETS], (H, W), want_dense=True)
+        torch.cuda.synchronize(dev)
+        e2e_dense_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+        e2e_dense_value = world * B * ksteps / (e2e_dense_ms * 1e-3)
+
+    # final host gather of the per-rank human counts (not timed; KBs)
+    if world > 1:
+        t = torch.tensor([humans_total], device=dev, dtype=torch.int64)
+        gathered = [torch.zeros_like(t) for _ in range(world)] if rank == 0 else None
+        dist.gather(t, gathered, dst=0)
+        if rank == 0:
+            humans_total = int(sum(int(g.item()) for g in gathered))
+
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = host_cores()
+        per = max(cores, 8)
+        steps_cpu = max(1, int(round(12.0 * cores / (0.5 * per))))      # ~12 s of wall time
+        steps_cpu = min(steps_cpu, 8)
+        rate, dt, _, kind = cpu_decode_rate(sets_host[0][:32], per, steps_cpu, 1, cores)
+        cpu_base = {"value": rate, "unit": "frames/s", "cores": cores, "kind": "reference" if kind != "port" else "port",
+                    "sample": "%d frames of the same synthetic batch in %.1f s on %d worker processes; maps = C "
+                              "restatement of the TF ops (TensorFlow unavailable), pafprocess = reference's own "
+                              "pafprocess.cpp (oracle/_ref)" % (per * steps_cpu, dt, cores)}
+
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        k1 = float(np.mean(k1_ms))
+        alg = dense_bytes_per_frame(h, w, f) * B
+        achieved = alg / (k1 * 1e-3) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "k1_traffic.json")
+        if os.path.exists(tpath):
+            try:
+                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        line = {
+            "metric": "decoded_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD % B,
+                       "batch_per_gpu": B, "global_batch": B * world, "sharding": "by image, no collective",
+                       "l2": "outputs 773 MB/step exceed the 126 MB L2; %d rotating input batches" % N_INPUT_SETS,
+                       "mode": "asbuilt"},
+            "roofline": {"bound": "hbm", "kernel": "k1_fused_f4 (upsample+smoother+NMS, dense)", "achieved": achieved,
+                         "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "algorithmic_bytes_per_launch": alg, "kernel_ms": k1},
+            "stage_ms": {"k1_maps": stage_acc[0] / args.steps, "peak_sort": stage_acc[1] / args.steps,
+                         "k2_limbs": stage_acc[2] / args.steps, "k3_assemble": stage_acc[3] / args.steps},
+            "value_minimal_mode": value_min,
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "call": "tfpd_decode_host (pinned host input -> human tables on host), dense maps left on device"},
+            "e2e_dense_maps": e2e_dense_value,
+            "gpu_launches": launches, "clocks": sampler.result(), "humans_decoded": humans_total,
+            "near_tie_pixels": near_ties, "e2e_humans_last_step": e2e_humans,
+        }
+        if cpu_base is not None:
+            line["cpu_baseline"] = cpu_base
+        print(json.dumps(line))
+    dec.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e-dense", dest="e2e_dense", action="store_false", default=True)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -22,6 +22,14 @@
  * --impl reference legs may load this library.
  */
 #include <math.h>
+/* Runtime-dispatched AVX2 clone of the hot loops: the inner channel loop vectorises across the 19
+ * channels, so each channel keeps its own tap-by-tap float32 accumulation order and (with
+ * -ffp-contract=off) the results are bit-identical to the scalar build. */
+#if defined(__x86_64__) && defined(__GNUC__)
+#define TARGET_CLONES __attribute__((target_clones("avx2", "default")))
+#else
+#define TARGET_CLONES
+#endif
 #include <stdlib.h>
 #include <string.h>
 
@@ -122,7 +130,7 @@ void oracle_resize_area(const float *in, int ih, int iw, int c, float *out, int 
  * accumulation in r-major / q-minor tap order (TF's own order is build
  * dependent; hence the 1e-5 tolerance on g, never bit-exactness).
  */
-void oracle_blur_f32(const float *up, int H, int W, int C, const float *k2d, int ks, float *g)
+TARGET_CLONES void oracle_blur_f32(const float *up, int H, int W, int C, const float *k2d, int ks, float *g)
 {
     int pad = ks / 2;
     float *acc = (float *)malloc(sizeof(float) * (size_t)C);

@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -327,6 +328,7 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
                        const tfpd_dense *dense) {
     if (!ctx) return TFPD_ERR_INVALID;
     if (!net_out) return fail(ctx, TFPD_ERR_INVALID, "decode: net_out is null");
+    if (((uintptr_t)net_out) & 15) return fail(ctx, TFPD_ERR_INVALID, "decode: net_out must be 16-byte aligned");
     if (N < 1 || N > ctx->cfg.max_batch) return fail(ctx, TFPD_ERR_INVALID, "decode: batch %d outside 1..%d", N, ctx->cfg.max_batch);
     if (h < 1 || w < 1 || H < 1 || W < 1) return fail(ctx, TFPD_ERR_INVALID, "decode: non-positive dimension");
     if (H > ctx->cfg.max_h || W > ctx->cfg.max_w)
@@ -360,12 +362,15 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
         p.w = w;
         p.nchunks = (w + 55) / 56;
         p.chunk_cells = (w + p.nchunks - 1) / p.nchunks;
+        p.copy_nchunks = (w + 27) / 28;                     // <= 28 cells (24.6 KB staged) per copy item
+        p.copy_chunk = (w + p.copy_nchunks - 1) / p.copy_nchunks;
         // bands: enough items for >= ~6 rounds over the SMs, but at least 2 low-res rows each
         int want_items = ctx->sm_count * 6;
         int nb = (want_items + N * p.nchunks - 1) / (N * p.nchunks);
         if (nb < 1) nb = 1;
         int br = (h + nb - 1) / nb;
         if (br < 2) br = 2;
+        if (const char *e = getenv("TFPD_K1_BAND")) br = atoi(e) > 0 ? atoi(e) : br;   // tuning knob
         if (br > h) br = h;
         p.band_rows = br;
         p.nbands = (h + br - 1) / br;

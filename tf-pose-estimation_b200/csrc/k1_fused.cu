@@ -30,10 +30,10 @@ namespace {
 
 constexpr int CPL = 2;                      // low-res cells per lane
 constexpr int kBlurWarps = kHeatC;          // 19
-constexpr int kCopyWarps = 5;
+constexpr int kCopyWarps = 1;
 constexpr int kBlurThreads = kBlurWarps * 32;
 constexpr int kCopyThreads = kCopyWarps * 32;
-constexpr int kThreads = kBlurThreads + kCopyThreads;   // 768
+constexpr int kThreads = kBlurThreads + kCopyThreads;   // 640 -> 96 registers per thread
 // a warp pass owns at most 32*CPL-8 = 56 cells (see launch_k1_fused_f4: chunk_cells <= 56)
 constexpr int NPX = 4 * CPL;                // output pixels per lane per row
 
@@ -49,15 +49,39 @@ __device__ __forceinline__ void bulk_store(void *gdst, const void *ssrc, uint32_
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n .reg .pred p;\n WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra DONE_%=;\n"
+        " bra WAIT_%=;\n DONE_%=:\n}\n" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+// TMA bulk load global -> shared, completion counted in bytes on an mbarrier (16-byte aligned src/dst/size)
+__device__ __forceinline__ void bulk_load(void *sdst, const void *gsrc, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(sdst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 __device__ __forceinline__ void named_bar(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 __host__ __device__ constexpr int floordiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
 
+// bytes of one raw input chunk buffer: the 16-byte aligned superset of copy_chunk cells, 128-byte padded
+__host__ __device__ constexpr int k1_raw_bytes(int copy_chunk) { return ((copy_chunk * kNetC * 4 + 32) + 127) / 128 * 128; }
+
 struct Item {
     int n, iy0, nrows, c0, tc;
 };
+// blur items: (frame, band of low-res rows, chunk of cells)
 __device__ __forceinline__ Item decode_item(const K1Params &p, int item) {
     Item it;
     int per_frame = p.nbands * p.nchunks;
@@ -73,51 +97,97 @@ __device__ __forceinline__ Item decode_item(const K1Params &p, int item) {
 }
 
 // ------------------------------------------------------------------------------------------
-// copy role: heat_up / paf_up rows of one item.  One low-res row chunk -> smem (already in the
-// NHWC order of an upsampled row) -> 4 + 4 bulk stores.  Two staging slots: while slot A drains
-// through the TMA engine, slot B is being filled.
+// copy role (one warp): heat_up / paf_up.  Item = one low-res row chunk (frame, iy, chunk of
+// <= copy_chunk cells).  Its tc*57 floats come in by ONE TMA bulk load (the 16-byte aligned
+// superset of the chunk; the next item's load is in flight while this one is expanded), are
+// expanded x4 along X into a staging slot that already has the NHWC layout of an upsampled row,
+// and the slot goes out as 4 + 4 TMA bulk stores (x4 along Y).  Two raw buffers, two slots.
 // ------------------------------------------------------------------------------------------
-__device__ void copy_role(const K1Params &p, const Item &it, float *cslots, int slot_floats, int ctid,
-                          unsigned &phase) {
+struct CopyItem {
+    int n, iy, c0, tc;
+    size_t src_off;     // byte offset of the chunk inside X
+};
+__device__ __forceinline__ CopyItem copy_item(const K1Params &p, int R) {
+    CopyItem ci;
+    const int chunk = R % p.copy_nchunks, grow = R / p.copy_nchunks;   // grow = n*h + iy
+    ci.c0 = chunk * p.copy_chunk;
+    ci.tc = min(p.copy_chunk, p.w - ci.c0);
+    ci.n = grow / p.h;
+    ci.iy = grow - ci.n * p.h;
+    ci.src_off = ((size_t)grow * p.w + ci.c0) * (kNetC * 4);
+    return ci;
+}
+// lane 0: start the bulk load of item R into raw; returns nothing (bytes are re-derived by the waiter)
+__device__ __forceinline__ void copy_prefetch(const K1Params &p, int R, unsigned char *raw, uint64_t *bar) {
+    const CopyItem ci = copy_item(p, R);
+    const size_t total = (size_t)p.N * p.h * p.w * (kNetC * 4);
+    const size_t a0 = ci.src_off & ~(size_t)15;
+    size_t a1 = (ci.src_off + (size_t)ci.tc * (kNetC * 4) + 15) & ~(size_t)15;
+    if (a1 > total) a1 = total & ~(size_t)15;      // never read past the tensor; the tail comes by LDG
+    const uint32_t bytes = (uint32_t)(a1 - a0);
+    fence_proxy_async();                           // earlier generic reads of `raw` precede the async write
+    mbar_expect_tx(bar, bytes);
+    bulk_load(raw, reinterpret_cast<const unsigned char *>(p.X) + a0, bytes, bar);
+}
+
+__device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, unsigned char *raws, int raw_bytes,
+                          uint64_t *bars, int lane) {
     const int H = 4 * p.h, W = 4 * p.w;
-    const int tc = it.tc;
-    for (int r = 0; r < it.nrows; ++r) {
-        const int iy = it.iy0 + r;
-        float *sh = cslots + (size_t)(phase & 1u) * slot_floats;   // heat part: tc*76 floats
-        float *sp = sh + tc * 4 * kHeatC;                          // paf part:  tc*152 floats
-        ++phase;
-        const float *src = p.X + ((size_t)(it.n * p.h + iy) * p.w + it.c0) * kNetC;
+    const int total_items = p.N * p.h * p.copy_nchunks;
+    const size_t total_bytes = (size_t)p.N * p.h * p.w * (kNetC * 4);
+    if (lane == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    int R = blockIdx.x;
+    if (R < total_items && lane == 0) copy_prefetch(p, R, raws, &bars[0]);
+    unsigned k = 0;
+    for (; R < total_items; R += gridDim.x, ++k) {
+        const unsigned b = k & 1u;
+        const int Rn = R + gridDim.x;
+        if (Rn < total_items && lane == 0) copy_prefetch(p, Rn, raws + (size_t)(b ^ 1u) * raw_bytes, &bars[b ^ 1u]);
+        const CopyItem ci = copy_item(p, R);
+        float *sh = cslots + (size_t)b * slot_floats;      // heat part: tc*76 floats
+        float *sp = sh + ci.tc * 4 * kHeatC;               // paf part:  tc*152 floats
+        if (lane == 0) bulk_wait_read1();                  // the stores that last used THIS slot have drained
+        mbar_wait(&bars[b], (k >> 1) & 1u);                // the chunk has landed in raw[b]
+        __syncwarp();
+        const unsigned char *rawb = raws + (size_t)b * raw_bytes;
+        const float *src = reinterpret_cast<const float *>(rawb + (ci.src_off & 15));
+        const int ne = ci.tc * kNetC;
+        // the few floats a clamped load left out (only at the very end of a tensor whose size is not
+        // a multiple of 16 bytes)
+        const size_t a0 = ci.src_off & ~(size_t)15;
+        const size_t got = ((total_bytes & ~(size_t)15) - a0);
+        const int ne_loaded = (int)min((size_t)ne, (got - (ci.src_off & 15)) / 4);
         // a cell of the upsampled row is its 19 (38) channel values repeated 4 times
-        for (int q = ctid; q < tc * kHeatC; q += kCopyThreads) {
-            int cell = q / kHeatC, m = q - cell * kHeatC;
-            const float *b = src + cell * kNetC;
-            int ch = 4 * m;
-            float4 v;
-            v.x = __ldg(b + (ch % kHeatC));
-            v.y = __ldg(b + ((ch + 1) % kHeatC));
-            v.z = __ldg(b + ((ch + 2) % kHeatC));
-            v.w = __ldg(b + ((ch + 3) % kHeatC));
-            reinterpret_cast<float4 *>(sh)[q] = v;
-        }
-        for (int q = ctid; q < tc * kPafC; q += kCopyThreads) {
-            int cell = q / kPafC, m = q - cell * kPafC;
-            const float *b = src + cell * kNetC + kHeatC;
-            int ch = 4 * m;
-            float4 v;
-            v.x = __ldg(b + (ch % kPafC));
-            v.y = __ldg(b + ((ch + 1) % kPafC));
-            v.z = __ldg(b + ((ch + 2) % kPafC));
-            v.w = __ldg(b + ((ch + 3) % kPafC));
-            reinterpret_cast<float4 *>(sp)[q] = v;
+#pragma unroll 2
+        for (int cellb = 0; cellb < ci.tc; ++cellb) {
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const int ch = lane + 32 * half;
+                if (ch < kNetC) {
+                    const int e = cellb * kNetC + ch;
+                    const float v = (e < ne_loaded) ? src[e] : __ldg(p.X + ci.src_off / 4 + e);
+                    if (ch < kHeatC) {
+                        float *d = sh + cellb * (4 * kHeatC) + ch;
+                        d[0] = v; d[kHeatC] = v; d[2 * kHeatC] = v; d[3 * kHeatC] = v;
+                    } else {
+                        float *d = sp + cellb * (4 * kPafC) + (ch - kHeatC);
+                        d[0] = v; d[kPafC] = v; d[2 * kPafC] = v; d[3 * kPafC] = v;
+                    }
+                }
+            }
         }
         fence_proxy_async();
-        if (ctid == 0) bulk_wait_read0();    // the OTHER slot has drained -> it may be refilled after the barrier
-        named_bar(2, kCopyThreads);
-        if (ctid == 0) {
-            const uint32_t hb = (uint32_t)tc * 4 * kHeatC * 4, pb = (uint32_t)tc * 4 * kPafC * 4;
+        __syncwarp();
+        if (lane == 0) {
+            const uint32_t hb = (uint32_t)ci.tc * 4 * kHeatC * 4, pb = (uint32_t)ci.tc * 4 * kPafC * 4;
 #pragma unroll
             for (int rr = 0; rr < 4; ++rr) {
-                size_t pix = ((size_t)it.n * H + (4 * iy + rr)) * W + 4 * it.c0;
+                size_t pix = ((size_t)ci.n * H + (4 * ci.iy + rr)) * W + 4 * ci.c0;
                 bulk_store(p.heat_up + pix * kHeatC, sh, hb);
                 bulk_store(p.paf_up + pix * kPafC, sp, pb);
             }
@@ -129,9 +199,29 @@ __device__ void copy_role(const K1Params &p, const Item &it, float *cslots, int 
 // ------------------------------------------------------------------------------------------
 // blur role: warp = heat channel c, lane l owns low-res cells cb + 2l, cb + 2l + 1 (cb = c0-4).
 // ------------------------------------------------------------------------------------------
+// A local maximum was found (rare: ~0.5 % of the pixels): dense poke + peak record + flags.
+// nb = largest of the 8 neighbours (near-tie test from the winner's side).
+__device__ __forceinline__ void emit_peak(const K1Params &p, int n, int c, int Yc, int X, float gc, float hc, float nb,
+                                       float *slot_addr) {
+    if (slot_addr) *slot_addr = gc;
+    if (c < kParts) {
+        const float thr = p.thresh;
+        if (gc > thr) {                                   // PEAKS(y,x,part) > THRESH_HEAT, pafprocess.cpp:27
+            int idx = atomicAdd(&p.counters[n].n_peak_rec, 1);
+            if (idx < p.max_peaks) {
+                p.rec_key[(size_t)n * p.max_peaks + idx] = peak_key(c, Yc, X);
+                p.rec_val[(size_t)n * p.max_peaks + idx] = hc;     // score = un-blurred HEAT(y,x,part), :32
+            }
+        }
+        const bool near_thr = fabsf(gc - thr) <= 2e-5f * thr;
+        const bool near_nb = gc > thr * (1.0f - 4e-5f) && (gc - nb) <= 2e-5f * fabsf(gc);
+        if (near_thr || near_nb) atomicAdd(&p.counters[n].near_ties, 1);
+    }
+}
+
 template <int PR, bool DENSE>
 __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int pslot_floats, int c, int lane,
-                          unsigned &pgroup, uint32_t (&wmask)[2]) {
+                          unsigned &pgroup, uint32_t &wmask0, uint32_t &wmask1) {
     const int h = p.h, w = p.w, H = 4 * h, W = 4 * w;
     const int tc = it.tc, c0 = it.c0, n = it.n;
     const int pitch_px = 4 * p.chunk_cells;     // slot row pitch: independent of the item's width
@@ -139,13 +229,15 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
     const unsigned FULL = 0xffffffffu;
 
     int cell[CPL];
-    bool cin[CPL], own[CPL];
+    bool cin[CPL];
+    uint32_t ownmask = 0;
 #pragma unroll
     for (int k = 0; k < CPL; ++k) {
         cell[k] = c0 - 4 + lane * CPL + k;
         cin[k] = (cell[k] >= 0) && (cell[k] < w);
-        own[k] = (cell[k] >= c0) && (cell[k] < c0 + tc);
+        if ((cell[k] >= c0) && (cell[k] < c0 + tc)) ownmask |= 0xfu << (4 * k);
     }
+    const int lx0 = 4 * (lane * CPL - 4);        // slot column of this lane's first pixel
     const float *Xn = p.X + (size_t)n * h * w * kNetC + c;
     auto hv = [&](int r, int k) -> float {
         return (cin[k] && r >= 0 && r < h) ? __ldg(Xn + ((size_t)r * w + cell[k]) * kNetC) : 0.0f;
@@ -160,144 +252,167 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
         for (int t = 0; t < 7; ++t) win[k][t] = hv(iy - 3 + t, k);
         nxt[k] = hv(iy + 4, k);
     }
-    float gp2[NPX], gp1[NPX], hc1[CPL];
+    // NMS state: ga/gb ping-pong hold g of the previous / current row, vm = max(g[Y-2], g[Y-1])
+    float ga[NPX], gb[NPX], vm[NPX];
 #pragma unroll
-    for (int i = 0; i < NPX; ++i) gp2[i] = gp1[i] = NEG;
-#pragma unroll
-    for (int k = 0; k < CPL; ++k) hc1[k] = 0.0f;
+    for (int i = 0; i < NPX; ++i) ga[i] = gb[i] = vm[i] = NEG;
 
-    const int Ys = 4 * it.iy0 - 1, Ye = 4 * (it.iy0 + it.nrows);   // rows whose g is needed
-    const float thr = p.thresh;
-    const float thr_lo = thr * (1.0f - 4e-5f);
+    const int Ys = 4 * it.iy0 - 1;                       // first row whose g is needed; last = 4*(iy0+nrows)
+    const float thr_lo = p.thresh * (1.0f - 4e-5f);
+    const bool is_part = c < kParts;
 
-    for (int grp = 0; grp < it.nrows + 2; ++grp, ++iy) {
+    // one output row: g(Y) -> cur ; NMS decision for row Y-1 whose g is in prev
+    auto do_row = [&](const int Y, float (&cur)[NPX], float (&prev)[NPX]) {
+        const int py = Y & 3;
+        if (Y >= 0 && Y < H) {
+            // vertical polyphase: gv[cell] = sum_t wp[py][t] * X[iy-3+t, cell, c]
+            float wv[7];
 #pragma unroll
-        for (int py = 0; py < 4; ++py) {
-            const int Y = 4 * iy + py;
-            if (Y < Ys || Y > Ye) continue;     // warp-uniform: only the first/last group are partial
-            float g[NPX];
-            if (Y >= 0 && Y < H) {
-                // vertical polyphase: gv[cell] = sum_t wp[py][t] * X[iy-3+t, cell, c]
-                float gv[CPL];
+            for (int t = 0; t < 7; ++t) wv[t] = c_wp[py][t];
+            float gv[CPL];
 #pragma unroll
-                for (int k = 0; k < CPL; ++k) {
-                    float a = c_wp[py][0] * win[k][0];
+            for (int k = 0; k < CPL; ++k) {
+                float a = wv[0] * win[k][0];
 #pragma unroll
-                    for (int t = 1; t < 7; ++t) a = fmaf(c_wp[py][t], win[k][t], a);
-                    gv[k] = a;
-                }
-                // window of gv over cells (own first cell - 3 .. own last cell + 3) via shuffles
-                float Wn[CPL + 6];
-#pragma unroll
-                for (int j = 0; j < CPL + 6; ++j) {
-                    const int d = j - 3;
-                    const int dl = floordiv(d, CPL);
-                    const int kk = d - dl * CPL;
-                    if (dl == 0) Wn[j] = gv[kk];
-                    else if (dl < 0) Wn[j] = __shfl_up_sync(FULL, gv[kk], -dl);
-                    else Wn[j] = __shfl_down_sync(FULL, gv[kk], dl);
-                }
-                // horizontal polyphase: g[cell,px] = sum_t wp[px][t] * gv[cell-3+t]
-#pragma unroll
-                for (int k = 0; k < CPL; ++k) {
-#pragma unroll
-                    for (int px = 0; px < 4; ++px) {
-                        float a = c_wp[px][0] * Wn[k];
-#pragma unroll
-                        for (int t = 1; t < 7; ++t) a = fmaf(c_wp[px][t], Wn[k + t], a);
-                        g[k * 4 + px] = cin[k] ? a : NEG;
-                    }
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < NPX; ++i) g[i] = NEG;
+                for (int t = 1; t < 7; ++t) a = fmaf(wv[t], win[k][t], a);
+                gv[k] = a;
             }
-
-            // 3x3 NMS of row Yc = Y-1: vertical max in registers, horizontal neighbours by shuffle
-            const int Yc = Y - 1;
-            const int j = Yc - 4 * it.iy0;     // candidate row inside the band
-            if (j >= 0 && j < 4 * it.nrows) {  // warp-uniform
-                float v[NPX + 2];
+            // window of gv over cells (own first cell - 3 .. own last cell + 3) via shuffles
+            float Wn[CPL + 6];
 #pragma unroll
-                for (int i = 0; i < NPX; ++i) v[i + 1] = fmaxf(fmaxf(gp2[i], gp1[i]), g[i]);
-                v[0] = __shfl_up_sync(FULL, v[NPX], 1);
-                v[NPX + 1] = __shfl_down_sync(FULL, v[1], 1);
-
-                float *slot = nullptr;
-                int jr = 0;
-                if (DENSE) {
-                    jr = j % PR;
-                    const int sidx = (int)((pgroup + (unsigned)(j / PR)) & 1u);
-                    slot = pslots + (size_t)sidx * pslot_floats;
-                    if (jr == 0 && wmask[sidx]) {
-                        // lazily clear what this lane poked into the slot two groups ago
-                        uint32_t mk = wmask[sidx];
-                        while (mk) {
-                            int b = __ffs(mk) - 1;
-                            mk &= mk - 1;
-                            int rr = b / NPX, i = b - rr * NPX;
-                            int X = 4 * cell[i >> 2] + (i & 3);
-                            slot[((size_t)rr * pitch_px + (X - 4 * c0)) * kHeatC + c] = 0.0f;
-                        }
-                        wmask[sidx] = 0;
-                    }
-                }
+            for (int j = 0; j < CPL + 6; ++j) {
+                const int d = j - 3;
+                const int dl = floordiv(d, CPL);
+                const int kk = d - dl * CPL;
+                if (dl == 0) Wn[j] = gv[kk];
+                else if (dl < 0) Wn[j] = __shfl_up_sync(FULL, gv[kk], -dl);
+                else Wn[j] = __shfl_down_sync(FULL, gv[kk], dl);
+            }
+            // horizontal polyphase: g[cell,px] = sum_t wp[px][t] * gv[cell-3+t]
 #pragma unroll
-                for (int i = 0; i < NPX; ++i) {
-                    const int k = i >> 2;
-                    if (!own[k]) continue;
-                    const float m = fmaxf(fmaxf(v[i], v[i + 1]), v[i + 2]);
-                    const float gc = gp1[i];
-                    const int X = 4 * cell[k] + (i & 3);
-                    if (gc == m) {
-                        if (DENSE) {
-                            slot[((size_t)jr * pitch_px + (X - 4 * c0)) * kHeatC + c] = gc;
-                            wmask[(pgroup + (unsigned)(j / PR)) & 1u] |= 1u << (jr * NPX + i);
-                        }
-                        if (c < kParts && gc > thr) {
-                            int idx = atomicAdd(&p.counters[n].n_peak_rec, 1);
-                            if (idx < p.max_peaks) {
-                                p.rec_key[(size_t)n * p.max_peaks + idx] = peak_key(c, Yc, X);
-                                p.rec_val[(size_t)n * p.max_peaks + idx] = hc1[k];
-                            }
-                        }
-                        if (c < kParts && fabsf(gc - thr) <= 2e-5f * thr) atomicAdd(&p.counters[n].near_ties, 1);
-                    } else if (c < kParts && gc > thr_lo && (m - gc) <= 2e-5f * fabsf(m)) {
-                        atomicAdd(&p.counters[n].near_ties, 1);     // lost the 3x3 max by a hair
-                    }
-                }
-                if (DENSE && (jr == PR - 1 || j == 4 * it.nrows - 1)) {
-                    // the slot's rows are complete: hand them to the TMA engine
-                    fence_proxy_async();
-                    if (c == 0 && lane == 0) bulk_wait_read0();     // previous slot drained
-                    named_bar(1, kBlurThreads);
-                    if (c == 0 && lane == 0) {
-                        const int jfirst = j - jr;
-                        const uint32_t bytes = (uint32_t)tc * 4 * kHeatC * 4;
-                        for (int rr = 0; rr <= jr; ++rr) {
-                            size_t pix = ((size_t)n * H + (4 * it.iy0 + jfirst + rr)) * W + 4 * c0;
-                            bulk_store(p.peaks + pix * kHeatC, slot + (size_t)rr * pitch_px * kHeatC, bytes);
-                        }
-                        bulk_commit();
-                    }
+            for (int k = 0; k < CPL; ++k) {
+#pragma unroll
+                for (int px = 0; px < 4; ++px) {
+                    float a = c_wp[px][0] * Wn[k];
+#pragma unroll
+                    for (int t = 1; t < 7; ++t) a = fmaf(c_wp[px][t], Wn[k + t], a);
+                    cur[k * 4 + px] = cin[k] ? a : NEG;
                 }
             }
+        } else {
+#pragma unroll
+            for (int i = 0; i < NPX; ++i) cur[i] = NEG;
+        }
+
+        // 3x3 NMS of row Yc = Y-1: vertical max in registers, horizontal neighbours by shuffle
+        const int Yc = Y - 1;
+        const int j = Yc - 4 * it.iy0;     // candidate row inside the band
+        if (j >= 0 && j < 4 * it.nrows) {  // warp-uniform
+            float v[NPX + 2];
+#pragma unroll
+            for (int i = 0; i < NPX; ++i) v[i + 1] = fmaxf(vm[i], cur[i]);
+            v[0] = __shfl_up_sync(FULL, v[NPX], 1);
+            v[NPX + 1] = __shfl_down_sync(FULL, v[1], 1);
+            uint32_t pm = 0;
+            float hot = NEG;
 #pragma unroll
             for (int i = 0; i < NPX; ++i) {
-                gp2[i] = gp1[i];
-                gp1[i] = g[i];
+                const float m = fmaxf(fmaxf(v[i], v[i + 1]), v[i + 2]);
+                pm |= (prev[i] == m) ? (1u << i) : 0u;
+                hot = fmaxf(hot, prev[i]);
             }
+            pm &= ownmask;
+            if (is_part && hot > thr_lo) {
+                // a pixel above the heat threshold that lost its 3x3 max by a hair: near-tie (loser side)
+                uint32_t nm = 0;
 #pragma unroll
-            for (int k = 0; k < CPL; ++k) hc1[k] = win[k][3];
+                for (int i = 0; i < NPX; ++i) {
+                    const float m = fmaxf(fmaxf(v[i], v[i + 1]), v[i + 2]);
+                    const bool nr = (prev[i] > thr_lo) & (prev[i] != m) & ((m - prev[i]) <= 2e-5f * fabsf(m));
+                    nm |= nr ? (1u << i) : 0u;
+                }
+                nm &= ownmask;
+                if (nm) atomicAdd(&p.counters[n].near_ties, __popc(nm));
+            }
+
+            float *slot = nullptr;
+            int jr = 0;
+            if (DENSE) {
+                jr = j % PR;
+                const unsigned sidx = (pgroup + (unsigned)(j / PR)) & 1u;
+                slot = pslots + (size_t)sidx * pslot_floats;
+                uint32_t &wm = sidx ? wmask1 : wmask0;
+                if (jr == 0 && wm) {
+                    // lazily clear what this lane poked into the slot two groups ago
+                    uint32_t mk = wm;
+                    while (mk) {
+                        const int b = __ffs(mk) - 1;
+                        mk &= mk - 1;
+                        const int rr = b / NPX, i = b - rr * NPX;
+                        slot[((size_t)rr * pitch_px + lx0 + i) * kHeatC + c] = 0.0f;
+                    }
+                    wm = 0;
+                }
+                wm |= pm << (jr * NPX);
+            }
+            // rare path (~0.5 % of the pixels are local maxima): one compact loop over the set bits,
+            // operands picked out of the register arrays by predicated moves (no local memory, no call)
+            for (uint32_t mk = pm; mk;) {
+                const int i = __ffs(mk) - 1;
+                mk &= mk - 1;
+                float gc = 0.f, nb = 0.f, hc = 0.f;
+                int cx = 0;
+#pragma unroll
+                for (int q = 0; q < NPX; ++q)
+                    if (i == q) {
+                        gc = prev[q];
+                        // largest neighbour except the one above (that pixel tests this one as its "below")
+                        nb = fmaxf(fmaxf(v[q], v[q + 2]), cur[q]);
+                        // heat score of row Yc: its low-res row is the window centre, or the one above it
+                        // when Y just crossed into the next low-res row
+                        hc = (py == 0) ? win[q >> 2][2] : win[q >> 2][3];
+                        cx = cell[q >> 2];
+                    }
+                emit_peak(p, n, c, Yc, 4 * cx + (i & 3), gc, hc, nb,
+                          DENSE ? slot + ((size_t)jr * pitch_px + lx0 + i) * kHeatC + c : nullptr);
+            }
+            if (DENSE && (jr == PR - 1 || j == 4 * it.nrows - 1)) {
+                // the slot's rows are complete: hand them to the TMA engine
+                fence_proxy_async();
+                if (c == 0 && lane == 0) bulk_wait_read0();     // previous slot drained
+                named_bar(1, kBlurThreads);
+                if (c == 0 && lane == 0) {
+                    const int jfirst = j - jr;
+                    const uint32_t bytes = (uint32_t)tc * 4 * kHeatC * 4;
+                    for (int rr = 0; rr <= jr; ++rr) {
+                        size_t pix = ((size_t)n * H + (4 * it.iy0 + jfirst + rr)) * W + 4 * c0;
+                        bulk_store(p.peaks + pix * kHeatC, slot + (size_t)rr * pitch_px * kHeatC, bytes);
+                    }
+                    bulk_commit();
+                }
+            }
         }
-        // slide the low-res window down one row; prefetch the row after next
+        // vm for the next row = max(g[Y-1], g[Y])
 #pragma unroll
-        for (int k = 0; k < CPL; ++k) {
+        for (int i = 0; i < NPX; ++i) vm[i] = fmaxf(prev[i], cur[i]);
+        if (py == 3) {
+            // slide the low-res window down one row; prefetch the row after next
+            ++iy;
 #pragma unroll
-            for (int t = 0; t < 6; ++t) win[k][t] = win[k][t + 1];
-            win[k][6] = nxt[k];
-            nxt[k] = hv(iy + 5, k);
+            for (int k = 0; k < CPL; ++k) {
+#pragma unroll
+                for (int t = 0; t < 6; ++t) win[k][t] = win[k][t + 1];
+                win[k][6] = nxt[k];
+                nxt[k] = hv(iy + 4, k);
+            }
         }
+    };
+
+    // rows Ys .. Ys + 4*nrows + 1 (an even count), two per iteration so ga/gb swap roles without moves
+#pragma unroll 1
+    for (int r = 0; r < 4 * it.nrows + 2; r += 2) {
+        do_row(Ys + r, ga, gb);
+        do_row(Ys + r + 1, gb, ga);
     }
     if (DENSE) pgroup += (unsigned)((4 * it.nrows + PR - 1) / PR);
 }
@@ -308,9 +423,12 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const int pslot_floats = PR * p.chunk_cells * 4 * kHeatC;
-    const int cslot_floats = p.chunk_cells * 4 * kNetC;
+    const int cslot_floats = p.copy_chunk * 4 * kNetC;
+    const int raw_bytes = k1_raw_bytes(p.copy_chunk);
     float *pslots = smem;                                 // 2 peak-row slots (blur role)
     float *cslots = smem + 2 * (size_t)pslot_floats;      // 2 replication slots (copy role)
+    unsigned char *raws = reinterpret_cast<unsigned char *>(cslots + 2 * (size_t)cslot_floats);   // 2 raw chunks
+    uint64_t *bars = reinterpret_cast<uint64_t *>(raws + 2 * (size_t)raw_bytes);
 
     if (warp < kBlurWarps) {
         if (DENSE) {
@@ -319,21 +437,16 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
             named_bar(1, kBlurThreads);
         }
         unsigned pgroup = 0;
-        uint32_t wmask[2] = {0u, 0u};
+        uint32_t wmask0 = 0u, wmask1 = 0u;
         for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
             Item it = decode_item(p, item);
-            blur_role<PR, DENSE>(p, it, pslots, pslot_floats, warp, lane, pgroup, wmask);
+            blur_role<PR, DENSE>(p, it, pslots, pslot_floats, warp, lane, pgroup, wmask0, wmask1);
         }
         if (DENSE && tid == 0) bulk_wait_all();
     } else {
         if (DENSE) {
-            const int ctid = tid - kBlurThreads;
-            unsigned phase = 0;
-            for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
-                Item it = decode_item(p, item);
-                copy_role(p, it, cslots, cslot_floats, ctid, phase);
-            }
-            if (ctid == 0) bulk_wait_all();
+            copy_role(p, cslots, cslot_floats, raws, raw_bytes, bars, lane);
+            if (lane == 0) bulk_wait_all();
         }
     }
 }
@@ -357,14 +470,17 @@ int upload_polyphase_weights(const double *s1d, int ksize) {
 }
 
 int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t s) {
-    const int grid = min(p.nitems, sm_count);
+    const int copy_items = dense ? p.N * p.h * p.copy_nchunks : 0;
+    const int grid = min(max(p.nitems, copy_items), sm_count);
     if (grid <= 0) return 0;
     if (!dense) {
         k1_fused_f4<4, false><<<grid, kBlurThreads, 0, s>>>(p);
         return cudaGetLastError() == cudaSuccess ? 1 : -1;
     }
-    const size_t cslot = (size_t)p.chunk_cells * 4 * kNetC * 4;
+    const size_t cslot = (size_t)p.copy_chunk * 4 * kNetC * 4;
+    const size_t raw = (size_t)k1_raw_bytes(p.copy_chunk);
     const size_t pslot4 = (size_t)4 * p.chunk_cells * 4 * kHeatC * 4;
+    const size_t fixed = 2 * cslot + 2 * raw + 64;
     const size_t limit = 227 * 1024 - 1024;
     static bool attr_set = false;
     if (!attr_set) {
@@ -372,10 +488,10 @@ int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t
         cudaFuncSetAttribute(k1_fused_f4<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
         attr_set = true;
     }
-    if (2 * pslot4 + 2 * cslot <= limit) {
-        k1_fused_f4<4, true><<<grid, kThreads, 2 * pslot4 + 2 * cslot, s>>>(p);
+    if (2 * pslot4 + fixed <= limit) {
+        k1_fused_f4<4, true><<<grid, kThreads, 2 * pslot4 + fixed, s>>>(p);
     } else {
-        k1_fused_f4<2, true><<<grid, kThreads, pslot4 + 2 * cslot, s>>>(p);
+        k1_fused_f4<2, true><<<grid, kThreads, pslot4 + fixed, s>>>(p);
     }
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }

@@ -87,7 +87,8 @@ struct K1Params {
     FrameCounters *counters;
     int max_peaks;
     int N, h, w;                        // low-res dims; H = 4h, W = 4w
-    int band_rows, nbands, chunk_cells, nchunks, nitems;
+    int band_rows, nbands, chunk_cells, nchunks, nitems;   // blur role decomposition
+    int copy_chunk, copy_nchunks;                          // copy role decomposition (cells per row chunk)
     float thresh;
 };
 
