@@ -1,0 +1,180 @@
+"""Generates the committed golden vectors.  Run in the BUILD container (needs /root/reference,
+scipy and oracle/_ref built from the reference sources); the vectors then travel with the repo.
+
+  gauss_kernel_25_3.npy   the literal reference Smoother.gauss_kernel(25, 3.0, 1)
+                          (tf_pose/tensblur/smoother.py:62-71, executed from the reference file with
+                          a stub `tensorflow` module -- the function itself is pure numpy/scipy).
+  toy_dense.npz           a small dense (peaks, heat, paf) triple with two hand-placed skeletons and
+                          the humans the reference's own PoseEstimator.estimate_paf
+                          (tf_pose/estimator.py:272-299, executed from the reference file) returns for
+                          it on top of the reference's own compiled pafprocess.cpp (oracle/_ref).
+  synth_humans.json       for seeded synthetic frames: the humans the same reference code returns when
+                          fed the oracle's dense maps, plus a sha256 of those maps so a test can tell
+                          "inputs differ" from "decode differs".
+"""
+import hashlib
+import importlib.util
+import json
+import os
+import sys
+import types
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = "/root/reference"
+sys.path.insert(0, ROOT)
+
+from oracle import oracle as O          # noqa: E402
+import tfpose_b200                      # noqa: E402,F401
+from tfpose_b200 import synth           # noqa: E402
+
+
+class _Stub(types.ModuleType):
+    """Stand-in for an absent third-party module (tensorflow, cv2, slidingwindow): any attribute is
+    another stub, calling one returns a stub.  The decode code paths exercised here never touch it."""
+
+    def __init__(self, name="stub"):
+        types.ModuleType.__init__(self, name)
+
+    def __getattr__(self, item):
+        if item.startswith("__"):
+            raise AttributeError(item)
+        return _Stub(self.__name__ + "." + item)
+
+    def __call__(self, *a, **k):
+        return _Stub(self.__name__ + "()")
+
+
+def load_reference_module(path, name, stubs):
+    saved = {}
+    for k, v in stubs.items():
+        saved[k] = sys.modules.get(k)
+        sys.modules[k] = v
+    try:
+        spec = importlib.util.spec_from_file_location(name, path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return mod
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+
+
+def reference_gauss_kernel():
+    tf = _Stub("tensorflow")
+    sm = load_reference_module(os.path.join(REF, "tf_pose/tensblur/smoother.py"), "ref_smoother", {"tensorflow": tf})
+    k = sm.Smoother.gauss_kernel(None, 25, 3.0, 1)      # `self` is unused by the reference function
+    return np.ascontiguousarray(k[:, :, 0, 0])
+
+
+def reference_estimator(variant="asbuilt"):
+    """The reference's estimator module with its compiled pafprocess bound through ctypes."""
+    ref = O.ReferencePafprocess(variant)
+    paf_mod = types.ModuleType("tf_pose.pafprocess.pafprocess")
+    for name in ("process_paf", "get_num_humans", "get_part_cid", "get_score", "get_part_x", "get_part_y",
+                 "get_part_score"):
+        setattr(paf_mod, name, getattr(ref, name))
+    pkg = types.ModuleType("tf_pose")
+    pkg.__path__ = []
+    pafpkg = types.ModuleType("tf_pose.pafprocess")
+    pafpkg.pafprocess = paf_mod
+    pafpkg.__path__ = []
+    tf = _Stub("tensorflow")
+    sw = _Stub("slidingwindow")
+    cv2 = _Stub("cv2")
+    common = load_reference_module(os.path.join(REF, "tf_pose/common.py"), "tf_pose.common",
+                                   {"tensorflow": tf, "cv2": cv2})
+    pkg.common = common
+    tens = types.ModuleType("tf_pose.tensblur")
+    tens.__path__ = []
+    smo = types.ModuleType("tf_pose.tensblur.smoother")
+    smo.Smoother = object
+    stubs = {"tensorflow": tf, "slidingwindow": sw, "cv2": cv2, "tf_pose": pkg, "tf_pose.common": common,
+             "tf_pose.pafprocess": pafpkg, "tf_pose.pafprocess.pafprocess": paf_mod, "tf_pose.tensblur": tens,
+             "tf_pose.tensblur.smoother": smo}
+    return load_reference_module(os.path.join(REF, "tf_pose/estimator.py"), "ref_estimator", stubs)
+
+
+def humans_to_json(humans):
+    out = []
+    for h in humans:
+        parts = {str(k): [bp.uidx, bp.x, bp.y, float(np.float32(bp.score))] for k, bp in h.body_parts.items()}
+        out.append({"score": float(np.float32(h.score)), "parts": parts, "str": str(h)})
+    return out
+
+
+def toy_dense():
+    """Two skeletons drawn directly at 'upsampled' resolution 48x40 (no TF ops involved)."""
+    H, W = 48, 40
+    heat = np.zeros((H, W, 19), np.float32)
+    peaks = np.zeros((H, W, 19), np.float32)
+    paf = np.zeros((H, W, 38), np.float32)
+    rng = np.random.default_rng(7)
+    from tfpose_b200.common import CocoPairs, CocoPairsNetwork
+    people = [(10.0, 6.0, 30.0), (28.0, 8.0, 34.0)]
+    tmpl = synth._TEMPLATE
+    for (nx, ny, size) in people:
+        joints = np.round(tmpl * size + np.array([nx, ny])).astype(int)
+        joints[:, 0] = np.clip(joints[:, 0], 0, W - 1)
+        joints[:, 1] = np.clip(joints[:, 1], 0, H - 1)
+        for k in range(18):
+            x, y = joints[k]
+            v = np.float32(0.6 + 0.4 * rng.random())
+            heat[y, x, k] = v
+            peaks[y, x, k] = v
+        for limb, (pa, pb) in enumerate(CocoPairs):
+            ax, ay = joints[pa]
+            bx, by = joints[pb]
+            d = np.hypot(bx - ax, by - ay)
+            if d < 1e-6:
+                continue
+            ux, uy = (bx - ax) / d, (by - ay) / d
+            chx, chy = CocoPairsNetwork[limb]
+            for t in np.linspace(0, 1, int(4 * d) + 2):
+                px, py = int(round(ax + t * (bx - ax))), int(round(ay + t * (by - ay)))
+                for dy in (-1, 0, 1):
+                    for dx in (-1, 0, 1):
+                        yy, xx = min(max(py + dy, 0), H - 1), min(max(px + dx, 0), W - 1)
+                        paf[yy, xx, chx] = ux
+                        paf[yy, xx, chy] = uy
+    return peaks, heat, paf
+
+
+def main():
+    k = reference_gauss_kernel()
+    np.save(os.path.join(HERE, "gauss_kernel_25_3.npy"), k)
+    print("gauss kernel", k.shape, k.dtype, k[12, 12], k[0, 0])
+
+    est = {v: reference_estimator(v) for v in ("asbuilt", "upstream")}
+    peaks, heat, paf = toy_dense()
+    toy = {}
+    for v in est:
+        toy[v] = humans_to_json(est[v].PoseEstimator.estimate_paf(peaks, heat, paf))
+    np.savez_compressed(os.path.join(HERE, "toy_dense.npz"), peaks=peaks, heat=heat, paf=paf)
+    print("toy humans", {v: len(t) for v, t in toy.items()})
+
+    cases = []
+    for (cfg, frame, h, w, people) in [(2, 0, 46, 54, None), (2, 1, 46, 54, None), (2, 2, 46, 54, None),
+                                       (2, 5, 46, 54, None), (3, 0, 46, 82, 5), (4, 0, 46, 54, 30),
+                                       (4, 1, 46, 54, 30), (5, 0, 92, 164, 12)]:
+        x = synth.synth_frame(h, w, synth.frame_seed(cfg, frame), people=people)
+        H, W = 4 * h, 4 * w
+        pk, hu, pu, g = O.dense_maps(x, H, W)
+        sha = hashlib.sha256(pk.tobytes() + hu.tobytes() + pu.tobytes()).hexdigest()
+        rec = {"config": cfg, "frame": frame, "h": h, "w": w, "people": people, "maps_sha256": sha,
+               "x_sha256": hashlib.sha256(x.tobytes()).hexdigest(), "fragile_pixels": int(O.fragile_pixels(g).sum())}
+        for v in est:
+            rec[v] = humans_to_json(est[v].PoseEstimator.estimate_paf(pk, hu, pu))
+        cases.append(rec)
+        print(cfg, frame, h, w, people, {v: len(rec[v]) for v in est}, "fragile", rec["fragile_pixels"])
+    with open(os.path.join(HERE, "synth_humans.json"), "w") as fh:
+        json.dump({"toy": toy, "cases": cases}, fh)
+
+
+if __name__ == "__main__":
+    main()

@@ -376,6 +376,8 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
         p.nbands = (h + br - 1) / br;
         p.nitems = N * p.nbands * p.nchunks;
         p.thresh = ctx->cfg.thresh_heat;
+        p.debug_roles = 3;
+        if (const char *e = getenv("TFPD_K1_ROLES")) p.debug_roles = atoi(e);   // profiling knob
         int r = launch_k1_fused_f4(p, want_dense, ctx->sm_count, s);
         if (r < 0) return fail(ctx, TFPD_ERR_CUDA, "k1_fused_f4 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
         ctx->launches += r;

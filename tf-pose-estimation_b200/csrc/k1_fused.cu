@@ -431,6 +431,7 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
     uint64_t *bars = reinterpret_cast<uint64_t *>(raws + 2 * (size_t)raw_bytes);
 
     if (warp < kBlurWarps) {
+        if (!(p.debug_roles & 1)) return;
         if (DENSE) {
             float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int q = tid; q < 2 * pslot_floats / 4; q += kBlurThreads) reinterpret_cast<float4 *>(pslots)[q] = z;
@@ -444,7 +445,7 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
         }
         if (DENSE && tid == 0) bulk_wait_all();
     } else {
-        if (DENSE) {
+        if (DENSE && (p.debug_roles & 2)) {
             copy_role(p, cslots, cslot_floats, raws, raw_bytes, bars, lane);
             if (lane == 0) bulk_wait_all();
         }

@@ -90,6 +90,7 @@ struct K1Params {
     int band_rows, nbands, chunk_cells, nchunks, nitems;   // blur role decomposition
     int copy_chunk, copy_nchunks;                          // copy role decomposition (cells per row chunk)
     float thresh;
+    int debug_roles;                    // bit0 blur role, bit1 copy role (3 = normal; tuning/profiling only)
 };
 
 // launchers (each returns the number of kernel launches it issued, <0 on launch error)
