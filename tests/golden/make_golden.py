@@ -8,6 +8,9 @@ scipy and oracle/_ref built from the reference sources); the vectors then travel
                           the humans the reference's own PoseEstimator.estimate_paf
                           (tf_pose/estimator.py:272-299, executed from the reference file) returns for
                           it on top of the reference's own compiled pafprocess.cpp (oracle/_ref).
+  human_boxes.json        what the reference's Human helpers (part_count, get_max_score, get_face_box,
+                          get_upper_body_box, __str__; tf_pose/estimator.py:73-241) return for random humans
+                          built with the reference's own Human / BodyPart classes.
   synth_humans.json       for seeded synthetic frames: the humans the same reference code returns when
                           fed the oracle's dense maps, plus a sha256 of those maps so a test can tell
                           "inputs differ" from "decode differs".
@@ -145,7 +148,49 @@ def toy_dense():
     return peaks, heat, paf
 
 
+def random_humans(est_mod, n=60, seed=11):
+    """Humans with random subsets of parts, built with the REFERENCE's Human/BodyPart classes."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for i in range(n):
+        hm = est_mod.Human([])
+        keep = rng.random(18) < rng.uniform(0.3, 1.0)
+        cx, cy, size = rng.uniform(0.2, 0.8), rng.uniform(0.1, 0.5), rng.uniform(0.2, 0.9)
+        for k in range(18):
+            if not keep[k]:
+                continue
+            px = float(np.clip(cx + synth._TEMPLATE[k, 0] * size + rng.normal(0, 0.01), 0, 1))
+            py = float(np.clip(cy + synth._TEMPLATE[k, 1] * size + rng.normal(0, 0.01), 0, 1))
+            hm.body_parts[k] = est_mod.BodyPart('%d-%d' % (i, k), k, px, py, float(np.float32(rng.uniform(0.05, 1.0))))
+        hm.score = float(rng.uniform(0.3, 2.0))
+        out.append(hm)
+    return out
+
+
+def boxes_golden(est_mod):
+    """Results of the reference's Human helpers (estimator.py:73-241) for random humans."""
+    recs = []
+    for hm in random_humans(est_mod):
+        if not hm.body_parts:
+            continue
+        rec = {"parts": {str(k): [bp.uidx, bp.x, bp.y, bp.score] for k, bp in hm.body_parts.items()},
+               "score": hm.score, "part_count": hm.part_count(), "max_score": hm.get_max_score(), "str": str(hm),
+               "names": [str(bp.get_part_name()) for bp in hm.body_parts.values()], "boxes": []}
+        for (iw, ih) in ((432, 368), (656, 368), (1312, 736), (100, 37)):
+            rec["boxes"].append({"w": iw, "h": ih, "face0": hm.get_face_box(iw, ih, mode=0),
+                                 "face1": hm.get_face_box(iw, ih, mode=1), "upper": hm.get_upper_body_box(iw, ih)})
+        recs.append(rec)
+    with open(os.path.join(HERE, "human_boxes.json"), "w") as fh:
+        json.dump(recs, fh)
+    print("human boxes:", len(recs), "humans;",
+          sum(1 for r in recs for b in r["boxes"] if b["face0"]), "face boxes,",
+          sum(1 for r in recs for b in r["boxes"] if b["upper"]), "upper-body boxes")
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "boxes":
+        boxes_golden(reference_estimator("asbuilt"))
+        return
     k = reference_gauss_kernel()
     np.save(os.path.join(HERE, "gauss_kernel_25_3.npy"), k)
     print("gauss kernel", k.shape, k.dtype, k[12, 12], k[0, 0])
@@ -174,6 +219,7 @@ def main():
         print(cfg, frame, h, w, people, {v: len(rec[v]) for v in est}, "fragile", rec["fragile_pixels"])
     with open(os.path.join(HERE, "synth_humans.json"), "w") as fh:
         json.dump({"toy": toy, "cases": cases}, fh)
+    boxes_golden(est["asbuilt"])
 
 
 if __name__ == "__main__":

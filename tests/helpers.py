@@ -1,0 +1,52 @@
+"""Shared comparison helpers of the parity tests (CUDA path vs oracle).  The oracle is the checker
+here, never the thing under test."""
+import numpy as np
+
+
+def humans_equal(got, want, H, W):
+    """got: list[Human] from the CUDA path; want: oracle/reference tuples [(score, {part: (x, y, s)})].
+    Bit-exact: float32 scores, integer pixel coordinates (through x/W, y/H like estimate_paf)."""
+    if len(got) != len(want):
+        return False, "human count %d != %d" % (len(got), len(want))
+    for i, (hg, (score, parts)) in enumerate(zip(got, want)):
+        if np.float32(hg.score) != np.float32(score):
+            return False, "human %d score %r != %r" % (i, hg.score, score)
+        if list(hg.body_parts) != sorted(parts):
+            return False, "human %d parts %r != %r" % (i, list(hg.body_parts), sorted(parts))
+        for k, (px, py, ps) in parts.items():
+            bp = hg.body_parts[k]
+            if bp.x != px / W or bp.y != py / H or np.float32(bp.score) != np.float32(ps):
+                return False, "human %d part %d (%r,%r,%r) != (%r,%r,%r)" % (i, k, bp.x, bp.y, bp.score, px / W,
+                                                                            py / H, ps)
+            if bp.uidx != "%d-%d" % (i, k) or bp.part_idx != k:
+                return False, "human %d part %d uidx %r" % (i, k, bp.uidx)
+    return True, ""
+
+
+def peaks_equal(pk, R):
+    """pk: PoseDecoder.peaks() dict; R: oracle PafResult."""
+    return (len(pk["x"]) == len(R.peaks["x"]) and np.array_equal(pk["part"], R.peaks["part"])
+            and np.array_equal(pk["x"], R.peaks["x"]) and np.array_equal(pk["y"], R.peaks["y"])
+            and np.array_equal(pk["score"], R.peaks["score"]))
+
+
+def conns_equal(conns, R):
+    """conns: PoseDecoder.connections() dict; R: oracle PafResult (limb-major acceptance order)."""
+    want = [(l, int(a), int(b), np.float32(s)) for l in range(19) for a, b, s in zip(*R.conns[l])]
+    got = list(zip(conns["limb"].tolist(), conns["cid1"].tolist(), conns["cid2"].tolist(),
+                   [np.float32(s) for s in conns["score"]]))
+    return got == want
+
+
+def rel_err(a, b, scale):
+    return float(np.abs(a.astype(np.float64) - b.astype(np.float64)).max() / max(float(np.abs(scale).max()), 1e-30))
+
+
+def table_tuples(res, frame):
+    """The raw tfpd_human records of a frame as comparable tuples."""
+    n = int(res.info["n_humans"][frame])
+    out = []
+    for r in res.table[frame][:n]:
+        out.append((np.float32(r["score"]).tobytes(), r["cid"].tobytes(), r["x"].tobytes(), r["y"].tobytes(),
+                    r["part_score"].tobytes()))
+    return out

@@ -1,0 +1,225 @@
+"""GPU tests of the two drop-in seams as a reference user sees them:
+
+  seam 2  ``pafprocess.process_paf`` + getters, ``PoseEstimator.estimate_paf``  (dense maps in)
+  seam 1  ``TfPosePostProcessor.inference_from_output`` / ``PoseDecoder.decode_host`` (network output in),
+          including the general ``resize_area`` path for the ratios the reference's CLIs allow
+          (run.py:30 default 4.0, eval.py:50 default 8.0, 1.0 / 2.0 / non-integer sizes).
+The CUDA path is always reached through the ctypes C-ABI."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import tfpose_b200 as tp
+from tfpose_b200 import pafprocess, synth
+
+from helpers import humans_equal, rel_err
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+HAVE_REF = os.path.exists(os.path.join(os.path.dirname(GOLD), "..", "oracle", "_ref", "libpafprocess_asbuilt.so"))
+
+
+def _module_humans():
+    out = []
+    for hid in range(pafprocess.get_num_humans()):
+        parts = {}
+        for k in range(18):
+            cid = pafprocess.get_part_cid(hid, k)
+            if cid < 0:
+                continue
+            parts[k] = (pafprocess.get_part_x(cid), pafprocess.get_part_y(cid), pafprocess.get_part_score(cid))
+        out.append((pafprocess.get_score(hid), parts))
+    return out
+
+
+@pytest.mark.parametrize("mode", ["asbuilt", "upstream"])
+def test_pafprocess_module_on_golden_toy(cuda, mode):
+    """The toy dense triple and the humans the reference's own estimate_paf returned for it."""
+    from test_oracle import tuples_from_json
+    gold = json.load(open(os.path.join(GOLD, "synth_humans.json")))["toy"]
+    d = np.load(os.path.join(GOLD, "toy_dense.npz"))
+    pafprocess.configure(mode=mode)
+    humans = tp.PoseEstimator.estimate_paf(d["peaks"], d["heat"], d["paf"])
+    got = [(np.float32(h.score), {k: (bp.x, bp.y, np.float32(bp.score)) for k, bp in h.body_parts.items()})
+           for h in humans]
+    assert got == tuples_from_json(gold[mode])
+    assert [bp.uidx for bp in humans[0].body_parts.values()][:2] == ["0-%d" % k for k in list(humans[0].body_parts)[:2]]
+    pafprocess.configure(mode="asbuilt")
+
+
+@pytest.mark.parametrize("mode", ["asbuilt", "upstream"])
+def test_pafprocess_module_vs_reference_binary_on_dense_maps(cuda, oracle, mode):
+    """Dense maps of seeded synthetic frames: module getters == the reference's compiled
+    pafprocess.cpp (oracle/_ref) getter for getter; falls back to the pinned restatement if the
+    reference binary did not travel."""
+    pafprocess.configure(mode=mode)
+    ref = oracle.ReferencePafprocess(mode) if HAVE_REF else None
+    for cfg, frame, h, w, people in [(2, 0, 46, 54, None), (2, 3, 46, 54, None), (4, 0, 46, 54, 30), (3, 1, 46, 82, 6)]:
+        x = synth.synth_frame(h, w, synth.frame_seed(cfg, frame), people=people)
+        pk, hu, pu, _ = oracle.dense_maps(x, 4 * h, 4 * w)
+        assert pafprocess.process_paf(pk, hu, pu) == 0
+        R = oracle.process_paf(pk, hu, pu, mode=mode, sort="std")
+        if ref is not None:
+            ref.process_paf(pk, hu, pu)
+            want = ref.humans_as_tuples()
+            assert want == R.humans_as_tuples()
+        else:
+            want = R.humans_as_tuples()
+        if R.flags & 1:
+            want = oracle.process_paf(pk, hu, pu, mode=mode, sort="total").humans_as_tuples()
+        got = _module_humans()
+        assert [(np.float32(s), p) for s, p in got] == \
+               [(np.float32(s), {k: (x_, y_, float(np.float32(v))) for k, (x_, y_, v) in p.items()}) for s, p in want]
+    pafprocess.configure(mode="asbuilt")
+
+
+@pytest.mark.parametrize("mode", ["asbuilt", "upstream"])
+def test_pafprocess_random_dense_with_exact_ties(cuda, oracle, mode):
+    """Quantised random dense maps: exact score ties, > 16 candidates per limb, found == 2 and
+    found > 2.  With ties the reference's order is libstdc++-internal; the library documents
+    (score desc, idx1, idx2) and must raise TFPD_FLAG_SCORE_TIE -- compare with the oracle run in
+    that total order, and with the std::sort order whenever no tie is flagged."""
+    pafprocess.configure(mode=mode)
+    seen_tie = seen_gt2 = 0
+    for seed in range(12):
+        rng = np.random.default_rng(100 + seed)
+        H, W = 40, 48
+        peaks = np.zeros((H, W, 19), np.float32)
+        n = int(rng.integers(20, 160))
+        ys, xs, cs = rng.integers(0, H, n), rng.integers(0, W, n), rng.integers(0, 18, n)
+        peaks[ys, xs, cs] = (rng.integers(1, 5, n) / 4.0).astype(np.float32)
+        heat = peaks + np.float32(0.125)
+        paf = (rng.integers(-2, 3, (H, W, 38)) / 2.0).astype(np.float32)
+        pafprocess.process_paf(peaks, heat, paf)
+        d = pafprocess._ctx()
+        info = d.fetch().info[0]
+        Rt = oracle.process_paf(peaks, heat, paf, mode=mode, sort="total")
+        assert bool(info["flags"] & 1) == bool(Rt.flags & 1)
+        assert bool(info["flags"] & 2) == bool(Rt.flags & 2)
+        seen_tie += int(info["flags"] & 1)
+        seen_gt2 += int(bool(info["flags"] & 2))
+        got = [(np.float32(s), p) for s, p in _module_humans()]
+        want = [(np.float32(s), {k: (a, b, float(np.float32(v))) for k, (a, b, v) in p.items()})
+                for s, p in Rt.humans_as_tuples()]
+        assert got == want, (mode, seed)
+        if not (Rt.flags & 1):
+            Rs = oracle.process_paf(peaks, heat, paf, mode=mode, sort="std")
+            assert Rs.humans_as_tuples() == Rt.humans_as_tuples()
+    assert seen_tie > 0
+    pafprocess.configure(mode="asbuilt")
+
+
+def test_pafprocess_argument_errors(cuda):
+    """swig raises ValueError for ndim != 3 (pafprocess_wrap.cpp:4937); channel-count and shape
+    mismatches (unchecked UB in the reference) are rejected with an error here."""
+    ok = np.zeros((8, 8, 19), np.float32)
+    with pytest.raises(ValueError):
+        pafprocess.process_paf(np.zeros((8, 8), np.float32), ok, np.zeros((8, 8, 38), np.float32))
+    with pytest.raises(tp.DecodeError):
+        pafprocess.process_paf(ok, ok, np.zeros((8, 8, 37), np.float32))
+    with pytest.raises(tp.DecodeError):
+        pafprocess.process_paf(ok, np.zeros((9, 8, 19), np.float32), np.zeros((8, 8, 38), np.float32))
+    # float64 / non-contiguous inputs are converted like swig's IN_ARRAY3 typemap does
+    assert pafprocess.process_paf(ok.astype(np.float64), ok[:, ::1], np.zeros((8, 8, 38))) == 0
+    assert pafprocess.get_num_humans() == 0
+    assert pafprocess.get_part_cid(0, 0) == -1      # bounds-checked (the reference indexes unchecked)
+
+
+def test_post_processor_numpy_and_cuda_inputs(cuda, oracle):
+    """TfPosePostProcessor.inference_from_output == inference() after the session returns:
+    humans + heatMat / pafMat side effects (estimator.py:544-551), NumPy (host) and CUDA inputs."""
+    import torch
+    x = synth.synth_batch(1, 46, 54, config_id=2, first_frame=2)
+    R, (peaks, heat_up, paf_up, g) = oracle.decode_frame(x[0], 184, 216, sort="total")
+    assert int(oracle.fragile_pixels(g).sum()) == 0
+    pp = tp.TfPosePostProcessor(target_size=(432, 368))
+    humans = pp.inference_from_output(x, upsample_size=4.0)
+    ok, why = humans_equal(humans, R.humans_as_tuples(), 184, 216)
+    assert ok, why
+    assert pp.heatMat.shape == (184, 216, 19) and pp.pafMat.shape == (184, 216, 38)
+    assert np.array_equal(pp.heatMat, heat_up) and np.array_equal(pp.pafMat, paf_up)
+    assert rel_err(pp.peaks, peaks, g) <= 1e-5
+    humans2 = pp.inference_from_output(torch.from_numpy(x).cuda(), upsample_size=4.0)
+    ok, why = humans_equal(humans2, R.humans_as_tuples(), 184, 216)
+    assert ok, why
+    assert np.array_equal(pp.heatMat.cpu().numpy(), heat_up)
+    with pytest.raises(Exception):
+        pp.inference_from_output(None)
+    pp.close()
+
+
+@pytest.mark.parametrize("ratio", [1.0, 2.0, 3.0, 8.0, 2.5])
+def test_general_resize_area_ratios(cuda, oracle, ratio):
+    """Every --resize-out-ratio other than 4: the general area-resize + separable smoother + NMS
+    kernels.  Maps within 1e-5 relative; humans exact when the frame has no near-tie."""
+    import torch
+    x = synth.synth_batch(2, 46, 54, config_id=2, first_frame=20)
+    H, W = tp.upsample_size_for(432, 368, ratio)
+    dec = tp.PoseDecoder(max_batch=2, max_upsample=(H, W), max_peaks=4096, max_cands=8192)
+    dense = (torch.empty((2, H, W, 19), device="cuda"), torch.empty((2, H, W, 38), device="cuda"),
+             torch.empty((2, H, W, 19), device="cuda"))
+    res = dec.decode(torch.from_numpy(x).cuda(), (H, W), dense=dense)
+    res_min = dec.decode(torch.from_numpy(x).cuda(), (H, W))
+    assert np.array_equal(res.info, res_min.info)
+    for i in range(2):
+        R, (peaks, heat_up, paf_up, g) = oracle.decode_frame(x[i], H, W, sort="total")
+        assert rel_err(dense[0][i].cpu().numpy(), heat_up, heat_up) <= 1e-5
+        assert rel_err(dense[1][i].cpu().numpy(), paf_up, paf_up) <= 1e-5
+        gp = dense[2][i].cpu().numpy()
+        both = (gp != 0) & (peaks != 0)
+        assert rel_err(np.where(both, gp, 0), np.where(both, peaks, 0), g) <= 1e-5
+        # exactness of the discrete results needs bit-equal heat scores: true when the resize is exact
+        exact_maps = np.array_equal(dense[0][i].cpu().numpy(), heat_up) and np.array_equal(dense[1][i].cpu().numpy(), paf_up)
+        if int(oracle.fragile_pixels(g).sum()) == 0 and exact_maps:
+            assert np.array_equal(gp != 0, peaks != 0)
+            ok, why = humans_equal(res.humans(i), R.humans_as_tuples(), H, W)
+            assert ok, (ratio, i, why)
+        else:
+            assert abs(len(res.humans(i)) - len(R.humans_as_tuples())) <= 1
+    dec.close()
+
+
+def test_decode_host_matches_device_call(cuda):
+    """tfpd_decode_host (host buffers, copies inside) == tfpd_decode_device on the same data."""
+    import torch
+    from helpers import table_tuples
+    x = synth.synth_batch(5, 46, 54, config_id=2, first_frame=40)
+    dec = tp.PoseDecoder(max_batch=8, max_upsample=(184, 216))
+    r_host, (hu, pu, pk) = dec.decode_host(x, (184, 216), want_dense=True)
+    dense = (torch.empty((5, 184, 216, 19), device="cuda"), torch.empty((5, 184, 216, 38), device="cuda"),
+             torch.empty((5, 184, 216, 19), device="cuda"))
+    r_dev = dec.decode(torch.from_numpy(x).cuda(), (184, 216), dense=dense)
+    for i in range(5):
+        assert table_tuples(r_host, i) == table_tuples(r_dev, i)
+    assert np.array_equal(hu, dense[0].cpu().numpy()) and np.array_equal(pu, dense[1].cpu().numpy())
+    assert np.array_equal(pk, dense[2].cpu().numpy())
+    r3 = dec.decode_host(x[0], (184, 216))          # [h,w,57] is accepted like the unbatched session output
+    assert table_tuples(r3, 0) == table_tuples(r_dev, 0)
+    dec.close()
+
+
+def test_argument_validation(cuda):
+    import torch
+    dec = tp.PoseDecoder(max_batch=2, max_upsample=(184, 216))
+    x = torch.zeros((3, 46, 54, 57), device="cuda")
+    with pytest.raises(tp.DecodeError):
+        dec.decode(x, (184, 216))                                   # batch > max_batch
+    with pytest.raises(tp.DecodeError):
+        dec.decode(x[:1], (368, 432))                               # upsample larger than the ctx allows
+    with pytest.raises(ValueError):
+        dec.decode(torch.zeros((1, 46, 54, 56), device="cuda"), (184, 216))
+    with pytest.raises(ValueError):
+        dec.decode(x[:1].double(), (184, 216))
+    with pytest.raises(TypeError):
+        dec.decode(np.zeros((1, 46, 54, 57), np.float32), (184, 216))
+    with pytest.raises(tp.DecodeError):
+        tp.PoseDecoder(max_batch=0)
+    with pytest.raises(tp.DecodeError):
+        tp.PoseDecoder(max_batch=1, max_cands=16384, max_rows=1024)     # would not fit K3's shared memory
+    d2 = tp.PoseDecoder(max_batch=1)
+    with pytest.raises(tp.DecodeError):
+        d2.fetch()                                                  # fetch before decode
+    d2.close()
+    dec.close()

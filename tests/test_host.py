@@ -1,0 +1,251 @@
+"""CPU tests of the host side: the C-ABI library loads and exports every symbol the header
+declares (no compute calls: there is no GPU here), the result objects honour the reference's
+contract (checked against golden vectors made by the reference's own classes), table -> Human
+conversion, and the by-image sharding helpers over a 2-rank gloo group."""
+import ctypes as C
+import json
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import tfpose_b200 as tp
+from tfpose_b200 import _lib, shard
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+# ------------------------------------------------------------------------------------ C-ABI
+def header_symbols():
+    src = open(os.path.join(ROOT, "include", "tfpose_decode.h")).read()
+    return re.findall(r"TFPD_API\s+[\w\s\*]+?\b(tfpd_\w+)\s*\(", src)
+
+
+def test_library_exports_every_declared_symbol():
+    names = header_symbols()
+    assert len(names) >= 22 and len(set(names)) == len(names)
+    L = C.CDLL(_lib.LIB_PATH)
+    for n in names:
+        assert hasattr(L, n), "libtfpose_decode.so does not export %s" % n
+    assert sorted(names) == sorted(_lib.SIGNATURES), "ctypes prototypes out of step with the header"
+    # nothing but the C-ABI is visible
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    exported = [l.split()[-1] for l in out.splitlines() if " T " in l]
+    assert sorted(e for e in exported if not e.startswith("_")) == sorted(names)
+
+
+def test_struct_layouts_match_the_header():
+    assert C.sizeof(_lib.Config) == 16 * 4
+    assert C.sizeof(_lib.HumanRec) == 4 + 3 * 18 * 2 + 18 * 4 and _lib.HUMAN_DTYPE.itemsize == C.sizeof(_lib.HumanRec)
+    assert C.sizeof(_lib.FrameInfo) == 24
+    cfg = _lib.default_config()
+    # decode constants of pafprocess.h:6-13 and estimator.py:332
+    assert (round(cfg.thresh_heat, 6), round(cfg.thresh_vector_score, 6), cfg.thresh_vector_cnt1, cfg.thresh_part_cnt,
+            round(cfg.thresh_human_score, 6), cfg.blur_ksize, cfg.blur_sigma) == (0.05, 0.05, 6, 4, 0.3, 25, 3.0)
+    with pytest.raises(TypeError):
+        _lib.default_config(no_such_field=1)
+
+
+def test_smoother_weights_are_the_reference_kernel():
+    """tfpd_gauss_kernel is host code: the 25x25 float32 weights must be bit-identical to what the
+    reference's Smoother.gauss_kernel produced (golden made by executing smoother.py:62-71)."""
+    gold = np.load(os.path.join(GOLD, "gauss_kernel_25_3.npy"))
+    k = _lib.gauss_kernel(25, 3.0)
+    assert np.array_equal(k, gold)
+    k7 = _lib.gauss_kernel(7, 1.5)
+    assert abs(float(k7.astype(np.float64).sum()) - 1.0) < 1e-6 and np.allclose(k7, k7.T)
+    with pytest.raises(tp.DecodeError):
+        _lib.gauss_kernel(24, 3.0)
+
+
+def test_no_cpu_fallback_without_a_device():
+    """On a box without CUDA the product must fail loudly, not compute on the CPU."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA device present")
+    with pytest.raises(tp.DecodeError) as ei:
+        tp.PoseDecoder(max_batch=1)
+    assert ei.value.code == _lib.ERR_CUDA and "no CPU path" in str(ei.value)
+    from tfpose_b200 import pafprocess
+    with pytest.raises(tp.DecodeError):
+        pafprocess.process_paf(np.zeros((4, 4, 19), np.float32), np.zeros((4, 4, 19), np.float32),
+                               np.zeros((4, 4, 38), np.float32))
+
+
+def test_product_does_not_import_the_oracle():
+    pkg = os.path.join(ROOT, "tf-pose-estimation_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), f
+                assert "liboracle" not in src and "/root/reference" not in src, f
+
+
+def test_missing_library_raises(tmp_path, monkeypatch):
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "libtfpose_decode.so"))
+    with pytest.raises(tp.DecodeLibraryMissing):
+        _lib.lib()
+
+
+# ------------------------------------------------------------------------------------ result objects
+def _human_from_json(rec):
+    hm = tp.Human([])
+    for k, (uidx, x, y, s) in rec["parts"].items():
+        hm.body_parts[int(k)] = tp.BodyPart(uidx, int(k), x, y, s)
+    hm.score = rec["score"]
+    return hm
+
+
+def test_human_helpers_match_reference_golden():
+    recs = json.load(open(os.path.join(GOLD, "human_boxes.json")))
+    n_face = n_upper = 0
+    for rec in recs:
+        hm = _human_from_json(rec)
+        assert hm.part_count() == rec["part_count"] and hm.get_max_score() == rec["max_score"]
+        assert str(hm) == rec["str"]
+        assert [str(bp.get_part_name()) for bp in hm.body_parts.values()] == rec["names"]
+        for b in rec["boxes"]:
+            assert hm.get_face_box(b["w"], b["h"], mode=0) == b["face0"]
+            assert hm.get_face_box(b["w"], b["h"], mode=1) == b["face1"]
+            assert hm.get_upper_body_box(b["w"], b["h"]) == b["upper"]
+            n_face += b["face0"] is not None
+            n_upper += b["upper"] is not None
+    assert n_face > 20 and n_upper > 20
+
+
+def test_result_object_contract():
+    assert tp.Human.__slots__ == ('body_parts', 'pairs', 'uidx_list', 'score')
+    assert tp.BodyPart.__slots__ == ('uidx', 'part_idx', 'x', 'y', 'score')
+    bp = tp.BodyPart('3-7', 7, 0.25, 0.5, 0.875)
+    assert str(bp) == 'BodyPart:7-(0.25, 0.50) score=0.88' and repr(bp) == str(bp)
+    assert bp.get_part_name() == tp.CocoPart.LWrist
+    hm = tp.Human([])
+    assert hm.pairs == [] and hm.uidx_list == set() and hm.body_parts == {} and hm.score == 0.0
+    with pytest.raises(Exception):
+        hm.get_upper_body_box(0, 10)
+    assert len(tp.CocoPairs) == 19 and len(tp.CocoPairsRender) == 17 and len(tp.CocoPairsNetwork) == 19
+    assert [p.value for p in tp.CocoPart] == list(range(19))
+
+
+def test_humans_from_table_follows_estimate_paf():
+    """Golden humans -> tfpd_human records -> Human objects must reproduce the reference's objects
+    (uidx '%d-%d' % (human_id, part), x = px / W as Python floats, ascending part order)."""
+    gold = json.load(open(os.path.join(GOLD, "synth_humans.json")))
+    case = gold["cases"][0]
+    H, W = 4 * case["h"], 4 * case["w"]
+    want = case["asbuilt"]
+    table = np.zeros(8, _lib.HUMAN_DTYPE)
+    table["cid"] = -1
+    for i, hm in enumerate(want):
+        table[i]["score"] = hm["score"]
+        for k, (uidx, x, y, s) in hm["parts"].items():
+            k = int(k)
+            table[i]["cid"][k] = k
+            table[i]["x"][k] = int(round(x * W))
+            table[i]["y"][k] = int(round(y * H))
+            table[i]["part_score"][k] = s
+    humans = tp.humans_from_table(table, len(want), H, W)
+    assert len(humans) == len(want)
+    for hm, w_ in zip(humans, want):
+        assert str(hm) == w_["str"]
+        assert {str(k): [bp.uidx, bp.x, bp.y, bp.score] for k, bp in hm.body_parts.items()} == w_["parts"]
+        assert hm.score == w_["score"]
+
+
+def test_upsample_size_rule():
+    # estimator.py:522-523 with the CLI defaults (run.py:30: 4.0 ; eval.py:50: 8.0)
+    assert tp.upsample_size_for(432, 368, 4.0) == [184, 216]
+    assert tp.upsample_size_for(656, 368, 4.0) == [184, 328]
+    assert tp.upsample_size_for(1312, 736, 4.0) == [368, 656]
+    assert tp.upsample_size_for(432, 368, 8.0) == [368, 432]
+    assert tp.upsample_size_for(432, 368, 2.5) == [115, 135]
+
+
+# ------------------------------------------------------------------------------------ sharding
+def test_shard_bounds_cover_the_batch():
+    for n in (0, 1, 7, 64, 128, 512, 513):
+        for world in (1, 2, 3, 4, 8):
+            spans = [shard.shard_bounds(n, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = [hi - lo for lo, hi in spans]
+            assert max(sizes) - min(sizes) <= 1
+    assert shard.shard_bounds(128, 1, 2) == (64, 128) and shard.shard_bounds(512, 7, 8) == (448, 512)
+    with pytest.raises(ValueError):
+        shard.shard_bounds(8, 2, 2)
+
+
+def test_pack_unpack_roundtrip():
+    rng = np.random.default_rng(3)
+    counts = np.array([2, 0, 3], np.int32)
+    recs = np.zeros(5, _lib.HUMAN_DTYPE)
+    recs["score"] = rng.random(5).astype(np.float32)
+    recs["cid"] = rng.integers(-1, 50, (5, 18))
+    c2, r2 = shard.unpack_result(shard.pack_result(counts, recs))
+    assert np.array_equal(c2, counts) and r2.tobytes() == recs.tobytes()
+    parts = shard.split_records(c2, r2)
+    assert [len(p) for p in parts] == [2, 0, 3]
+    c0, r0 = shard.unpack_result(shard.pack_result(np.zeros(0, np.int32), np.zeros(0, _lib.HUMAN_DTYPE)))
+    assert len(c0) == 0 and len(r0) == 0
+
+
+_GLOO_WORKER = r'''
+import os, sys
+sys.path.insert(0, %(root)r)
+import numpy as np, torch, torch.distributed as dist
+import tfpose_b200
+from tfpose_b200 import shard, _lib
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%(port)d", rank=rank, world_size=world)
+N = 13
+lo, hi = shard.shard_bounds(N, rank, world)
+# frame f "decodes" to (f %% 3) humans whose score encodes (frame, human)
+counts = np.array([f %% 3 for f in range(lo, hi)], np.int32)
+recs = np.zeros(int(counts.sum()), _lib.HUMAN_DTYPE)
+k = 0
+for f in range(lo, hi):
+    for j in range(f %% 3):
+        recs[k]["score"] = f + j / 8.0
+        recs[k]["cid"][:] = f
+        k += 1
+out = shard.gather_results(counts, recs, dst=0)
+if rank == 0:
+    c, r = out
+    assert c.tolist() == [f %% 3 for f in range(N)], c
+    per = shard.split_records(c, r)
+    for f in range(N):
+        assert [float(x) for x in per[f]["score"]] == [f + j / 8.0 for j in range(f %% 3)]
+        assert all((row["cid"] == f).all() for row in per[f])
+    print("GATHER_OK")
+else:
+    assert out is None
+dist.barrier()
+dist.destroy_process_group()
+'''
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_gather_results_over_gloo(world, tmp_path):
+    """The N>1 path on CPU: every rank 'decodes' its contiguous shard, rank 0 receives the tables in
+    frame order (the only communication the multi-GPU path has)."""
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER % {"root": ROOT, "port": port})
+    procs = []
+    for r in range(world):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=180)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), "\n".join(outs)
+    assert "GATHER_OK" in outs[0]

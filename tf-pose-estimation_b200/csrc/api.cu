@@ -212,6 +212,17 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
                     "max_humans<=max_rows<=1024)");
     if (cfg->mode != TFPD_MODE_ASBUILT && cfg->mode != TFPD_MODE_UPSTREAM)
         return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: unknown mode %d", cfg->mode);
+    {
+        // K3 keeps a frame's candidate keys, subset rows and greedy bitmaps in shared memory
+        Workspace probe{};
+        probe.max_cands = next_pow2(cfg->max_cands);
+        probe.max_rows = cfg->max_rows;
+        if (assemble_smem_bytes(probe) + 1024 > 227 * 1024)
+            return fail(nullptr, TFPD_ERR_INVALID,
+                        "tfpd_create: max_cands=%d with max_rows=%d needs %zu bytes of shared memory in the assembly "
+                        "kernel (limit 227 KB): lower one of them",
+                        probe.max_cands, cfg->max_rows, assemble_smem_bytes(probe));
+    }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
         return fail(nullptr, TFPD_ERR_CUDA, "tfpd_create: no CUDA device (this library has no CPU path)");

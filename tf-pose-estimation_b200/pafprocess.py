@@ -10,7 +10,7 @@ from . import _lib
 from .decoder import PoseDecoder
 
 _decoder = None
-_settings = {"device": 0, "mode": "asbuilt", "max_peaks": 4096, "max_cands": 16384, "max_rows": 1024,
+_settings = {"device": 0, "mode": "asbuilt", "max_peaks": 4096, "max_cands": 8192, "max_rows": 1024,
              "max_humans": 256}
 
 
