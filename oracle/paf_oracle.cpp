@@ -12,7 +12,7 @@
  *                       found==2 always takes the else arm (:166-170).
  *   mode 1 "upstream" : membership starts at 0 (ildoonet upstream) -> merge.
  *
- * PINNED: tests/test_oracle_vs_reference.py runs this restatement against the
+ * PINNED: tests/test_oracle.py runs this restatement against the
  * reference's own pafprocess.cpp compiled from /root/reference into
  * oracle/_ref/ (both modes) on seeded dense inputs, and against the committed
  * golden vectors in tests/golden/ that were produced by the reference's

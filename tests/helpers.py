@@ -2,6 +2,8 @@
 here, never the thing under test."""
 import numpy as np
 
+MAP_TOL = 1e-5      # north_star: upsampled/blurred maps within 1e-5 relative error
+
 
 def humans_equal(got, want, H, W):
     """got: list[Human] from the CUDA path; want: oracle/reference tuples [(score, {part: (x, y, s)})].
@@ -50,3 +52,20 @@ def table_tuples(res, frame):
         out.append((np.float32(r["score"]).tobytes(), r["cid"].tobytes(), r["x"].tobytes(), r["y"].tobytes(),
                     r["part_score"].tobytes()))
     return out
+
+
+def check_peaks_tensor(oracle, gp, peaks, g, fragile, what):
+    """Dense peaks tensor vs oracle: values within MAP_TOL on the common support; a pixel may be a local
+    maximum on one side only where the oracle's own NMS decision is a near-tie at the map tolerance
+    (flat noise floor, the never-read background channel, x4-replication plateaus) -- and never on a
+    pixel that matters downstream unless the frame is flagged fragile."""
+    both = (gp != 0) & (peaks != 0)
+    assert rel_err(np.where(both, gp, 0), np.where(both, peaks, 0), g) <= MAP_TOL, what
+    mism = (gp != 0) != (peaks != 0)
+    if mism.any():
+        _, margin = oracle.nms(g, want_margin=True)
+        assert (np.abs(margin[mism]) <= 2 * MAP_TOL * float(np.abs(g).max())).all(), \
+            "%s: peaks-tensor support differs at a pixel that is not a near-tie" % what
+        if fragile == 0:
+            assert not (mism[..., :18] & (g[..., :18] > 0.05 * (1 - 4e-5))).any(), \
+                "%s: support differs above the heat threshold" % what

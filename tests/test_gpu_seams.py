@@ -14,7 +14,7 @@ import pytest
 import tfpose_b200 as tp
 from tfpose_b200 import pafprocess, synth
 
-from helpers import humans_equal, rel_err
+from helpers import check_peaks_tensor, humans_equal, rel_err
 
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
@@ -168,16 +168,17 @@ def test_general_resize_area_ratios(cuda, oracle, ratio):
         assert rel_err(dense[0][i].cpu().numpy(), heat_up, heat_up) <= 1e-5
         assert rel_err(dense[1][i].cpu().numpy(), paf_up, paf_up) <= 1e-5
         gp = dense[2][i].cpu().numpy()
-        both = (gp != 0) & (peaks != 0)
-        assert rel_err(np.where(both, gp, 0), np.where(both, peaks, 0), g) <= 1e-5
-        # exactness of the discrete results needs bit-equal heat scores: true when the resize is exact
-        exact_maps = np.array_equal(dense[0][i].cpu().numpy(), heat_up) and np.array_equal(dense[1][i].cpu().numpy(), paf_up)
-        if int(oracle.fragile_pixels(g).sum()) == 0 and exact_maps:
-            assert np.array_equal(gp != 0, peaks != 0)
+        fragile = int(oracle.fragile_pixels(g).sum())
+        check_peaks_tensor(oracle, gp, peaks, g, fragile, "ratio %s frame %d" % (ratio, i))
+        # the discrete stages must be bit-exact GIVEN the maps: the oracle's process_paf fed with the
+        # GPU's own dense tensors reproduces the GPU's humans (covers inexact ratios and near-ties)
+        hu_g, pu_g = dense[0][i].cpu().numpy(), dense[1][i].cpu().numpy()
+        R2 = oracle.process_paf(gp, hu_g, pu_g, sort="total")
+        ok, why = humans_equal(res.humans(i), R2.humans_as_tuples(), H, W)
+        assert ok, (ratio, i, why)
+        if fragile == 0 and np.array_equal(hu_g, heat_up) and np.array_equal(pu_g, paf_up):
             ok, why = humans_equal(res.humans(i), R.humans_as_tuples(), H, W)
             assert ok, (ratio, i, why)
-        else:
-            assert abs(len(res.humans(i)) - len(R.humans_as_tuples())) <= 1
     dec.close()
 
 
