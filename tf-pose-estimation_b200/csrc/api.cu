@@ -373,20 +373,11 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
         p.w = w;
         p.nchunks = (w + 55) / 56;
         p.chunk_cells = (w + p.nchunks - 1) / p.nchunks;
-        p.copy_nchunks = (w + 27) / 28;                     // <= 28 cells (24.6 KB staged) per copy item
+        p.copy_nchunks = (w + 31) / 32;                     // <= 32 cells (29 KB staged) per copy item
         p.copy_chunk = (w + p.copy_nchunks - 1) / p.copy_nchunks;
-        // bands: enough items for >= ~6 rounds over the SMs, but at least 2 low-res rows each
-        int want_items = ctx->sm_count * 6;
-        int nb = (want_items + N * p.nchunks - 1) / (N * p.nchunks);
-        if (nb < 1) nb = 1;
-        int br = (h + nb - 1) / nb;
-        if (br < 2) br = 2;
-        if (const char *e = getenv("TFPD_K1_BAND")) br = atoi(e) > 0 ? atoi(e) : br;   // tuning knob
-        if (br > h) br = h;
-        p.band_rows = br;
-        p.nbands = (h + br - 1) / br;
-        p.nitems = N * p.nbands * p.nchunks;
         p.thresh = ctx->cfg.thresh_heat;
+        p.l2_knobs = 0;
+        if (const char *e = getenv("TFPD_K1_L2")) p.l2_knobs = atoi(e);         // tuning knob
         p.debug_roles = 3;
         if (const char *e = getenv("TFPD_K1_ROLES")) p.debug_roles = atoi(e);   // profiling knob
         int r = launch_k1_fused_f4(p, want_dense, ctx->sm_count, s);

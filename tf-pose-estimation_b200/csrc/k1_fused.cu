@@ -19,10 +19,14 @@
 //                                                    ordered afterwards by k_sort_peaks
 //
 // CTA = 19 "blur" warps (one heat channel each, lanes = low-res cells, marching down the
-// output rows with a 7-row register window) + 5 "copy" warps (replication + staging).  The
-// two roles never synchronise with each other; each has its own smem ring and named barrier.
-// Work item = (frame, band of low-res rows, chunk of <=56 cells); grid = SM count, static
-// stride over items.  Nothing here is a dense contraction: no tensor cores (north_star).
+// output rows with a 7-row register window) + 1 "copy" warp (replication + staging).  The
+// two roles never synchronise with each other; each has its own smem buffers.
+// Scheduling: the (frame, chunk of <=56 cells, low-res row) space is flattened and cut into
+// gridDim.x equal contiguous spans, one per CTA (grid = SM count): every SM gets the same
+// number of rows (+-1) and pays the 8-row window prologue once per span / frame boundary.
+// Nothing here is a dense contraction: no tensor cores (north_star).
+#include <type_traits>
+
 #include "tfpd_internal.cuh"
 
 namespace tfpd {
@@ -44,6 +48,29 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 __device__ __forceinline__ void bulk_store(void *gdst, const void *ssrc, uint32_t bytes) {
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)),
                  "r"(bytes)
+                 : "memory");
+}
+// same with an L2 eviction-priority hint (the dense outputs are written once and never re-read here)
+__device__ __forceinline__ void bulk_store_hint(void *gdst, const void *ssrc, uint32_t bytes, uint64_t policy) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gdst),
+                 "r"(smem_u32(ssrc)), "r"(bytes), "l"(policy)
+                 : "memory");
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint64_t policy_evict_last() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void prefetch_l2(const void *gsrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gsrc), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void prefetch_l2_hint(const void *gsrc, uint32_t bytes, uint64_t policy) {
+    asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;" ::"l"(gsrc), "r"(bytes), "l"(policy)
                  : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
@@ -81,44 +108,38 @@ __host__ __device__ constexpr int k1_raw_bytes(int copy_chunk) { return ((copy_c
 struct Item {
     int n, iy0, nrows, c0, tc;
 };
-// blur items: (frame, band of low-res rows, chunk of cells)
-__device__ __forceinline__ Item decode_item(const K1Params &p, int item) {
-    Item it;
-    int per_frame = p.nbands * p.nchunks;
-    it.n = item / per_frame;
-    int rem = item - it.n * per_frame;
-    int band = rem / p.nchunks;
-    int chunk = rem - band * p.nchunks;
-    it.iy0 = band * p.band_rows;
-    it.nrows = min(p.band_rows, p.h - it.iy0);
-    it.c0 = chunk * p.chunk_cells;
-    it.tc = min(p.chunk_cells, p.w - it.c0);
-    return it;
+// contiguous share [lo, hi) of `total` units for CTA b of g
+__device__ __forceinline__ void span_of(long long total, int b, int g, long long &lo, long long &hi) {
+    lo = total * b / g;
+    hi = total * (b + 1) / g;
 }
 
 // ------------------------------------------------------------------------------------------
 // copy role (one warp): heat_up / paf_up.  Item = one low-res row chunk (frame, iy, chunk of
-// <= copy_chunk cells).  Its tc*57 floats come in by ONE TMA bulk load (the 16-byte aligned
-// superset of the chunk; the next item's load is in flight while this one is expanded), are
-// expanded x4 along X into a staging slot that already has the NHWC layout of an upsampled row,
-// and the slot goes out as 4 + 4 TMA bulk stores (x4 along Y).  Two raw buffers, two slots.
+// <= 32 cells).  Its tc*57 floats come in by ONE TMA bulk load (the 16-byte aligned superset of
+// the chunk; the next item's load is in flight while this one is expanded).  Lane l owns cell l:
+// it reads its 57 values (stride 57 words: conflict-free) and writes the cell's x4 replicated
+// blocks -- 19 float4 of heat, 38 float4 of PAF, all register indices static -- into a staging
+// slot that already has the NHWC layout of an upsampled row; the slot then goes out as 4 + 4 TMA
+// bulk stores (x4 along Y).  Two raw buffers, two slots.
 // ------------------------------------------------------------------------------------------
 struct CopyItem {
     int n, iy, c0, tc;
     size_t src_off;     // byte offset of the chunk inside X
 };
-__device__ __forceinline__ CopyItem copy_item(const K1Params &p, int R) {
+__device__ __forceinline__ CopyItem copy_item(const K1Params &p, long long R) {
     CopyItem ci;
-    const int chunk = R % p.copy_nchunks, grow = R / p.copy_nchunks;   // grow = n*h + iy
+    const long long grow = R / p.copy_nchunks;                       // grow = n*h + iy
+    const int chunk = (int)(R - grow * p.copy_nchunks);
     ci.c0 = chunk * p.copy_chunk;
     ci.tc = min(p.copy_chunk, p.w - ci.c0);
-    ci.n = grow / p.h;
-    ci.iy = grow - ci.n * p.h;
+    ci.n = (int)(grow / p.h);
+    ci.iy = (int)(grow - (long long)ci.n * p.h);
     ci.src_off = ((size_t)grow * p.w + ci.c0) * (kNetC * 4);
     return ci;
 }
-// lane 0: start the bulk load of item R into raw; returns nothing (bytes are re-derived by the waiter)
-__device__ __forceinline__ void copy_prefetch(const K1Params &p, int R, unsigned char *raw, uint64_t *bar) {
+// lane 0: start the bulk load of item R into raw (bytes are re-derived by the waiter)
+__device__ __forceinline__ void copy_prefetch(const K1Params &p, long long R, unsigned char *raw, uint64_t *bar) {
     const CopyItem ci = copy_item(p, R);
     const size_t total = (size_t)p.N * p.h * p.w * (kNetC * 4);
     const size_t a0 = ci.src_off & ~(size_t)15;
@@ -133,21 +154,34 @@ __device__ __forceinline__ void copy_prefetch(const K1Params &p, int R, unsigned
 __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, unsigned char *raws, int raw_bytes,
                           uint64_t *bars, int lane) {
     const int H = 4 * p.h, W = 4 * p.w;
-    const int total_items = p.N * p.h * p.copy_nchunks;
     const size_t total_bytes = (size_t)p.N * p.h * p.w * (kNetC * 4);
+    long long R, Rend;
+    span_of((long long)p.N * p.h * p.copy_nchunks, blockIdx.x, gridDim.x, R, Rend);
     if (lane == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    int R = blockIdx.x;
-    if (R < total_items && lane == 0) copy_prefetch(p, R, raws, &bars[0]);
+    const uint64_t pol_first = policy_evict_first();
+    if ((p.l2_knobs & 1) && lane == 0) {
+        // Pull this CTA's 1/gridDim share of X into L2 up front: DRAM then sees one read burst followed
+        // by an (almost) pure write stream instead of reads sprinkled into the writes.
+        const size_t lo = (total_bytes * blockIdx.x / gridDim.x) & ~(size_t)15;
+        const size_t hi = (blockIdx.x + 1 == gridDim.x) ? (total_bytes & ~(size_t)15)
+                                                        : ((total_bytes * (blockIdx.x + 1) / gridDim.x) & ~(size_t)15);
+        const uint64_t pol_last = policy_evict_last();
+        for (size_t o = lo; o < hi; o += 32768) {
+            const uint32_t nb = (uint32_t)min((size_t)32768, hi - o);
+            if (p.l2_knobs & 4) prefetch_l2_hint(reinterpret_cast<const unsigned char *>(p.X) + o, nb, pol_last);
+            else prefetch_l2(reinterpret_cast<const unsigned char *>(p.X) + o, nb);
+        }
+    }
+    if (R < Rend && lane == 0) copy_prefetch(p, R, raws, &bars[0]);
     unsigned k = 0;
-    for (; R < total_items; R += gridDim.x, ++k) {
+    for (; R < Rend; ++R, ++k) {
         const unsigned b = k & 1u;
-        const int Rn = R + gridDim.x;
-        if (Rn < total_items && lane == 0) copy_prefetch(p, Rn, raws + (size_t)(b ^ 1u) * raw_bytes, &bars[b ^ 1u]);
+        if (R + 1 < Rend && lane == 0) copy_prefetch(p, R + 1, raws + (size_t)(b ^ 1u) * raw_bytes, &bars[b ^ 1u]);
         const CopyItem ci = copy_item(p, R);
         float *sh = cslots + (size_t)b * slot_floats;      // heat part: tc*76 floats
         float *sp = sh + ci.tc * 4 * kHeatC;               // paf part:  tc*152 floats
@@ -157,28 +191,41 @@ __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, uns
         const unsigned char *rawb = raws + (size_t)b * raw_bytes;
         const float *src = reinterpret_cast<const float *>(rawb + (ci.src_off & 15));
         const int ne = ci.tc * kNetC;
-        // the few floats a clamped load left out (only at the very end of a tensor whose size is not
-        // a multiple of 16 bytes)
+        // floats a clamped load left out (only at the very end of a tensor whose size is not a multiple of 16 B)
         const size_t a0 = ci.src_off & ~(size_t)15;
         const size_t got = ((total_bytes & ~(size_t)15) - a0);
         const int ne_loaded = (int)min((size_t)ne, (got - (ci.src_off & 15)) / 4);
-        // a cell of the upsampled row is its 19 (38) channel values repeated 4 times
-#pragma unroll 2
-        for (int cellb = 0; cellb < ci.tc; ++cellb) {
+        if (lane < ci.tc) {
+            const float *sc = src + lane * kNetC;
+            const bool whole = (lane + 1) * kNetC <= ne_loaded;
+            const float *gc = p.X + ci.src_off / 4 + lane * kNetC;
+            {
+                float v[kHeatC];
 #pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                const int ch = lane + 32 * half;
-                if (ch < kNetC) {
-                    const int e = cellb * kNetC + ch;
-                    const float v = (e < ne_loaded) ? src[e] : __ldg(p.X + ci.src_off / 4 + e);
-                    if (ch < kHeatC) {
-                        float *d = sh + cellb * (4 * kHeatC) + ch;
-                        d[0] = v; d[kHeatC] = v; d[2 * kHeatC] = v; d[3 * kHeatC] = v;
-                    } else {
-                        float *d = sp + cellb * (4 * kPafC) + (ch - kHeatC);
-                        d[0] = v; d[kPafC] = v; d[2 * kPafC] = v; d[3 * kPafC] = v;
-                    }
+                for (int c = 0; c < kHeatC; ++c) v[c] = sc[c];
+                if (!whole) {      // rare: the clamped load left part of this cell out
+#pragma unroll
+                    for (int c = 0; c < kHeatC; ++c) v[c] = __ldg(gc + c);
                 }
+                float4 *d = reinterpret_cast<float4 *>(sh + lane * (4 * kHeatC));
+#pragma unroll
+                for (int j = 0; j < kHeatC; ++j)
+                    d[j] = make_float4(v[(4 * j) % kHeatC], v[(4 * j + 1) % kHeatC], v[(4 * j + 2) % kHeatC],
+                                       v[(4 * j + 3) % kHeatC]);
+            }
+            {
+                float u[kPafC];
+#pragma unroll
+                for (int c = 0; c < kPafC; ++c) u[c] = sc[kHeatC + c];
+                if (!whole) {
+#pragma unroll
+                    for (int c = 0; c < kPafC; ++c) u[c] = __ldg(gc + kHeatC + c);
+                }
+                float4 *d = reinterpret_cast<float4 *>(sp + lane * (4 * kPafC));
+#pragma unroll
+                for (int j = 0; j < kPafC; ++j)
+                    d[j] = make_float4(u[(4 * j) % kPafC], u[(4 * j + 1) % kPafC], u[(4 * j + 2) % kPafC],
+                                       u[(4 * j + 3) % kPafC]);
             }
         }
         fence_proxy_async();
@@ -188,8 +235,13 @@ __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, uns
 #pragma unroll
             for (int rr = 0; rr < 4; ++rr) {
                 size_t pix = ((size_t)ci.n * H + (4 * ci.iy + rr)) * W + 4 * ci.c0;
-                bulk_store(p.heat_up + pix * kHeatC, sh, hb);
-                bulk_store(p.paf_up + pix * kPafC, sp, pb);
+                if (p.l2_knobs & 2) {
+                    bulk_store_hint(p.heat_up + pix * kHeatC, sh, hb, pol_first);
+                    bulk_store_hint(p.paf_up + pix * kPafC, sp, pb, pol_first);
+                } else {
+                    bulk_store(p.heat_up + pix * kHeatC, sh, hb);
+                    bulk_store(p.paf_up + pix * kPafC, sp, pb);
+                }
             }
             bulk_commit();
         }
@@ -244,13 +296,16 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
     };
 
     // 7-row register window of low-res heat values around the current low-res row iy
-    float win[CPL][7], nxt[CPL];
+    // (nxt / nxt2 = the next two rows, already in flight: global-load latency under a saturated
+    // write stream is microseconds, one row of lead was measured not to cover it)
+    float win[CPL][7], nxt[CPL], nxt2[CPL];
     int iy = it.iy0 - 1;
 #pragma unroll
     for (int k = 0; k < CPL; ++k) {
 #pragma unroll
         for (int t = 0; t < 7; ++t) win[k][t] = hv(iy - 3 + t, k);
         nxt[k] = hv(iy + 4, k);
+        nxt2[k] = hv(iy + 5, k);
     }
     // NMS state: ga/gb ping-pong hold g of the previous / current row, vm = max(g[Y-2], g[Y-1])
     float ga[NPX], gb[NPX], vm[NPX];
@@ -261,20 +316,19 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
     const float thr_lo = p.thresh * (1.0f - 4e-5f);
     const bool is_part = c < kParts;
 
-    // one output row: g(Y) -> cur ; NMS decision for row Y-1 whose g is in prev
-    auto do_row = [&](const int Y, float (&cur)[NPX], float (&prev)[NPX]) {
-        const int py = Y & 3;
+    // one output row: g(Y) -> cur ; NMS decision for row Y-1 whose g is in prev.  The phase
+    // py = Y & 3 is a compile-time constant (rows are unrolled by 4), so every smoother weight is
+    // an immediate constant-bank operand.
+    auto do_row = [&](auto py_tag, const int Y, float (&cur)[NPX], float (&prev)[NPX]) {
+        constexpr int py = decltype(py_tag)::value;
         if (Y >= 0 && Y < H) {
             // vertical polyphase: gv[cell] = sum_t wp[py][t] * X[iy-3+t, cell, c]
-            float wv[7];
-#pragma unroll
-            for (int t = 0; t < 7; ++t) wv[t] = c_wp[py][t];
             float gv[CPL];
 #pragma unroll
             for (int k = 0; k < CPL; ++k) {
-                float a = wv[0] * win[k][0];
+                float a = c_wp[py][0] * win[k][0];
 #pragma unroll
-                for (int t = 1; t < 7; ++t) a = fmaf(wv[t], win[k][t], a);
+                for (int t = 1; t < 7; ++t) a = fmaf(c_wp[py][t], win[k][t], a);
                 gv[k] = a;
             }
             // window of gv over cells (own first cell - 3 .. own last cell + 3) via shuffles
@@ -386,7 +440,11 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
                     const uint32_t bytes = (uint32_t)tc * 4 * kHeatC * 4;
                     for (int rr = 0; rr <= jr; ++rr) {
                         size_t pix = ((size_t)n * H + (4 * it.iy0 + jfirst + rr)) * W + 4 * c0;
-                        bulk_store(p.peaks + pix * kHeatC, slot + (size_t)rr * pitch_px * kHeatC, bytes);
+                        if (p.l2_knobs & 2)
+                            bulk_store_hint(p.peaks + pix * kHeatC, slot + (size_t)rr * pitch_px * kHeatC, bytes,
+                                            policy_evict_first());
+                        else
+                            bulk_store(p.peaks + pix * kHeatC, slot + (size_t)rr * pitch_px * kHeatC, bytes);
                     }
                     bulk_commit();
                 }
@@ -396,24 +454,36 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
 #pragma unroll
         for (int i = 0; i < NPX; ++i) vm[i] = fmaxf(prev[i], cur[i]);
         if (py == 3) {
-            // slide the low-res window down one row; prefetch the row after next
+            // slide the low-res window down one row; prefetch two rows ahead
             ++iy;
 #pragma unroll
             for (int k = 0; k < CPL; ++k) {
 #pragma unroll
                 for (int t = 0; t < 6; ++t) win[k][t] = win[k][t + 1];
                 win[k][6] = nxt[k];
-                nxt[k] = hv(iy + 4, k);
+                nxt[k] = nxt2[k];
+                nxt2[k] = hv(iy + 5, k);
             }
         }
     };
 
-    // rows Ys .. Ys + 4*nrows + 1 (an even count), two per iteration so ga/gb swap roles without moves
+    // rows Ys .. Ys + 4*nrows + 1; Ys = 4*iy0 - 1 has phase 3, so a group of four rows has the
+    // phases 3,0,1,2 and ga/gb swap roles without moves; the last two rows (phases 3, 0) only feed
+    // the NMS of the band's last output rows.
+    using P0 = std::integral_constant<int, 0>;
+    using P1 = std::integral_constant<int, 1>;
+    using P2 = std::integral_constant<int, 2>;
+    using P3 = std::integral_constant<int, 3>;
+    int Yr = Ys;
 #pragma unroll 1
-    for (int r = 0; r < 4 * it.nrows + 2; r += 2) {
-        do_row(Ys + r, ga, gb);
-        do_row(Ys + r + 1, gb, ga);
+    for (int g4 = 0; g4 < it.nrows; ++g4, Yr += 4) {
+        do_row(P3(), Yr, ga, gb);
+        do_row(P0(), Yr + 1, gb, ga);
+        do_row(P1(), Yr + 2, ga, gb);
+        do_row(P2(), Yr + 3, gb, ga);
     }
+    do_row(P3(), Yr, ga, gb);
+    do_row(P0(), Yr + 1, gb, ga);
     if (DENSE) pgroup += (unsigned)((4 * it.nrows + PR - 1) / PR);
 }
 
@@ -439,9 +509,21 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
         }
         unsigned pgroup = 0;
         uint32_t wmask0 = 0u, wmask1 = 0u;
-        for (int item = blockIdx.x; item < p.nitems; item += gridDim.x) {
-            Item it = decode_item(p, item);
+        // this CTA's contiguous share of the flattened (frame, chunk, low-res row) space, walked as
+        // maximal runs inside one (frame, chunk)
+        long long u, uend;
+        span_of((long long)p.N * p.nchunks * p.h, blockIdx.x, gridDim.x, u, uend);
+        while (u < uend) {
+            const long long q = u / p.h;                    // q = n * nchunks + chunk
+            Item it;
+            it.iy0 = (int)(u - q * p.h);
+            it.nrows = (int)min((long long)(p.h - it.iy0), uend - u);
+            it.n = (int)(q / p.nchunks);
+            const int chunk = (int)(q - (long long)it.n * p.nchunks);
+            it.c0 = chunk * p.chunk_cells;
+            it.tc = min(p.chunk_cells, p.w - it.c0);
             blur_role<PR, DENSE>(p, it, pslots, pslot_floats, warp, lane, pgroup, wmask0, wmask1);
+            u += it.nrows;
         }
         if (DENSE && tid == 0) bulk_wait_all();
     } else {
@@ -471,8 +553,9 @@ int upload_polyphase_weights(const double *s1d, int ksize) {
 }
 
 int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t s) {
-    const int copy_items = dense ? p.N * p.h * p.copy_nchunks : 0;
-    const int grid = min(max(p.nitems, copy_items), sm_count);
+    // one CTA per SM; fewer only when there are fewer low-res rows than SMs
+    const long long units = (long long)p.N * p.nchunks * p.h;
+    const int grid = (int)min(units, (long long)sm_count);
     if (grid <= 0) return 0;
     if (!dense) {
         k1_fused_f4<4, false><<<grid, kBlurThreads, 0, s>>>(p);

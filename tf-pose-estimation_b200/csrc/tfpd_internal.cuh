@@ -87,9 +87,10 @@ struct K1Params {
     FrameCounters *counters;
     int max_peaks;
     int N, h, w;                        // low-res dims; H = 4h, W = 4w
-    int band_rows, nbands, chunk_cells, nchunks, nitems;   // blur role decomposition
-    int copy_chunk, copy_nchunks;                          // copy role decomposition (cells per row chunk)
+    int chunk_cells, nchunks;                              // blur role: <= 56-cell column chunks
+    int copy_chunk, copy_nchunks;                          // copy role: <= 32-cell row chunks (one lane per cell)
     float thresh;
+    int l2_knobs;                       // bit0 up-front L2 prefetch of X, bit1 evict_first stores, bit2 evict_last prefetch
     int debug_roles;                    // bit0 blur role, bit1 copy role (3 = normal; tuning/profiling only)
 };
 
