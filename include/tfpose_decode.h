@@ -183,6 +183,10 @@ TFPD_API int tfpd_gauss_kernel(int ksize, float sigma, float *k2d);
 TFPD_API int tfpd_last_launch_count(const tfpd_ctx *ctx);
 TFPD_API int tfpd_set_profiling(tfpd_ctx *ctx, int on);
 TFPD_API int tfpd_last_stage_ms(tfpd_ctx *ctx, float stage_ms[4]);
+/* Profiling aid (ctx created with the environment variable TFPD_K1_TIMES=1): per-CTA timestamps of the
+ * last fused-map kernel launch, out[cta*4 + {0,1,2,3}] = CTA start / blur-role end / copy-role end
+ * (globaltimer ns) / SM id, for the first max_ctas CTAs. */
+TFPD_API int tfpd_debug_k1_times(tfpd_ctx *ctx, uint64_t *out, int max_ctas);
 
 #ifdef __cplusplus
 }

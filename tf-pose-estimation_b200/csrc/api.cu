@@ -50,6 +50,13 @@ struct tfpd_ctx {
     std::vector<double> s1d;
     DevBuf in_buf, dense_buf, gen_buf;  // lazily sized: host-call input, dense outputs, generic-path scratch
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    // host-buffer calls: H2D, kernels and D2H of successive frame chunks run on three streams
+    cudaStream_t st_h2d = nullptr, st_work = nullptr, st_d2h = nullptr;
+    std::vector<cudaEvent_t> ev_chunk;  // 2 per chunk: input landed / chunk decoded
+    int host_chunks = 0;                // 0 = automatic (TFPD_HOST_CHUNKS overrides: tuning knob)
+    int k1_pr = 0;                      // TFPD_K1_PR
+    int k1_l2_knobs = 2, k1_roles = 3;  // TFPD_K1_L2 / TFPD_K1_ROLES tuning and profiling knobs
+    unsigned long long *d_k1_times = nullptr;   // TFPD_K1_TIMES=1: per-CTA timestamps of the last K1 launch
     bool profiling = false, have_timing = false;
     cudaStream_t last_stream = nullptr;
     int last_N = 0, last_H = 0, last_W = 0;
@@ -129,24 +136,47 @@ Thresholds thresholds_of(const tfpd_config &c) {
 }
 
 // zero the per-frame counters, then stages 2..4 shared by both seams
-int run_tail(tfpd_ctx *ctx, int N, const PafSource &src, size_t frame_stride, cudaStream_t s) {
+int run_tail(tfpd_ctx *ctx, const Workspace &ws, int N, const PafSource &src, size_t frame_stride, cudaStream_t s,
+             bool timed) {
     int r;
-    if (ctx->profiling) cudaEventRecord(ctx->ev[1], s);
-    if ((r = launch_sort_peaks(ctx->ws, N, s)) < 0) return fail(ctx, TFPD_ERR_CUDA, "k_sort_peaks launch failed");
+    if (timed) cudaEventRecord(ctx->ev[1], s);
+    if ((r = launch_sort_peaks(ws, N, s)) < 0) return fail(ctx, TFPD_ERR_CUDA, "k_sort_peaks launch failed");
     ctx->launches += r;
-    if (ctx->profiling) cudaEventRecord(ctx->ev[2], s);
-    if ((r = launch_limb_score(ctx->ws, N, src, frame_stride, thresholds_of(ctx->cfg), ctx->sm_count, s)) < 0)
+    if (timed) cudaEventRecord(ctx->ev[2], s);
+    if ((r = launch_limb_score(ws, N, src, frame_stride, thresholds_of(ctx->cfg), ctx->sm_count, s)) < 0)
         return fail(ctx, TFPD_ERR_CUDA, "k_limb_score launch failed");
     ctx->launches += r;
-    if (ctx->profiling) cudaEventRecord(ctx->ev[3], s);
-    if ((r = launch_assemble(ctx->ws, N, thresholds_of(ctx->cfg), s)) < 0)
+    if (timed) cudaEventRecord(ctx->ev[3], s);
+    if ((r = launch_assemble(ws, N, thresholds_of(ctx->cfg), s)) < 0)
         return fail(ctx, TFPD_ERR_CUDA, "k_assemble launch failed: %s", cudaGetErrorString(cudaGetLastError()));
     ctx->launches += r;
-    if (ctx->profiling) {
+    if (timed) {
         cudaEventRecord(ctx->ev[4], s);
         ctx->have_timing = true;
     }
     return TFPD_OK;
+}
+
+// the per-frame arrays of `w` starting at frame f0 (kernels index frames from 0)
+Workspace ws_view(const Workspace &w, int f0) {
+    Workspace v = w;
+    const size_t f = (size_t)f0, MP = (size_t)w.max_peaks, MC = (size_t)w.max_cands;
+    v.counters += f;
+    v.rec_key += f * MP;
+    v.rec_val += f * MP;
+    v.pk_x += f * MP;
+    v.pk_y += f * MP;
+    v.pk_score += f * MP;
+    v.part_first += f * 20;
+    v.cand_key += f * MC;
+    v.conn_cid1 += f * MC;
+    v.conn_cid2 += f * MC;
+    v.conn_score += f * MC;
+    v.conn_start += f * 20;
+    v.conn_count += f * 20;
+    v.humans += f * (size_t)w.max_humans;
+    v.info += f;
+    return v;
 }
 
 void begin_call(tfpd_ctx *ctx, int N, int H, int W, cudaStream_t s) {
@@ -217,9 +247,10 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
         Workspace probe{};
         probe.max_cands = next_pow2(cfg->max_cands);
         probe.max_rows = cfg->max_rows;
+        probe.max_peaks = next_pow2(cfg->max_peaks);
         if (assemble_smem_bytes(probe) + 1024 > 227 * 1024)
             return fail(nullptr, TFPD_ERR_INVALID,
-                        "tfpd_create: max_cands=%d with max_rows=%d needs %zu bytes of shared memory in the assembly "
+                        "tfpd_create: max_cands=%d with max_rows=%d (and the peak table) needs %zu bytes of shared memory in the assembly "
                         "kernel (limit 227 KB): lower one of them",
                         probe.max_cands, cfg->max_rows, assemble_smem_bytes(probe));
     }
@@ -300,6 +331,16 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
         return fail(nullptr, TFPD_ERR_CUDA, "smoother weight upload failed: %s", cudaGetErrorString(cudaGetLastError()));
     }
     for (auto &ev : ctx->ev) cudaEventCreate(&ev);
+    cudaStreamCreateWithFlags(&ctx->st_h2d, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&ctx->st_work, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&ctx->st_d2h, cudaStreamNonBlocking);
+    if (const char *e = getenv("TFPD_HOST_CHUNKS")) ctx->host_chunks = atoi(e);
+    if (const char *e = getenv("TFPD_K1_L2")) ctx->k1_l2_knobs = atoi(e);
+    if (const char *e = getenv("TFPD_K1_ROLES")) ctx->k1_roles = atoi(e);
+    if (const char *e = getenv("TFPD_K1_PR")) ctx->k1_pr = atoi(e);
+    if (const char *e = getenv("TFPD_K1_TIMES"))
+        if (atoi(e) && cudaMalloc((void **)&ctx->d_k1_times, 1024 * 4 * 8) == cudaSuccess)
+            cudaMemset(ctx->d_k1_times, 0, 1024 * 4 * 8);
     *out = ctx;
     return TFPD_OK;
 }
@@ -310,9 +351,13 @@ void tfpd_destroy(tfpd_ctx *ctx) {
     if (ctx->decoded) cudaStreamSynchronize(ctx->last_stream);
     for (auto &ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);
+    for (auto &ev : ctx->ev_chunk) cudaEventDestroy(ev);
+    for (cudaStream_t st : {ctx->st_h2d, ctx->st_work, ctx->st_d2h})
+        if (st) cudaStreamDestroy(st);
     if (ctx->ws_block) cudaFree(ctx->ws_block);
     if (ctx->h_result) cudaFreeHost(ctx->h_result);
     if (ctx->d_k1d) cudaFree(ctx->d_k1d);
+    if (ctx->d_k1_times) cudaFree(ctx->d_k1_times);
     ctx->in_buf.release();
     ctx->dense_buf.release();
     ctx->gen_buf.release();
@@ -327,6 +372,16 @@ int tfpd_set_profiling(tfpd_ctx *ctx, int on) {
 
 int tfpd_last_launch_count(const tfpd_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
+int tfpd_debug_k1_times(tfpd_ctx *ctx, uint64_t *out, int max_ctas) {
+    if (!ctx || !out || max_ctas < 1) return TFPD_ERR_INVALID;
+    if (!ctx->d_k1_times) return fail(ctx, TFPD_ERR_STATE, "per-CTA timestamps are off (create the ctx with TFPD_K1_TIMES=1)");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    CUDA_TRY(ctx, cudaDeviceSynchronize());
+    const int n = max_ctas < 1024 ? max_ctas : 1024;
+    CUDA_TRY(ctx, cudaMemcpy(out, ctx->d_k1_times, (size_t)n * 4 * 8, cudaMemcpyDeviceToHost));
+    return TFPD_OK;
+}
+
 int tfpd_last_stage_ms(tfpd_ctx *ctx, float stage_ms[4]) {
     if (!ctx || !stage_ms) return TFPD_ERR_INVALID;
     if (!ctx->have_timing) return fail(ctx, TFPD_ERR_STATE, "no timing recorded (tfpd_set_profiling + decode first)");
@@ -335,25 +390,12 @@ int tfpd_last_stage_ms(tfpd_ctx *ctx, float stage_ms[4]) {
     return TFPD_OK;
 }
 
-int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W, void *stream,
-                       const tfpd_dense *dense) {
-    if (!ctx) return TFPD_ERR_INVALID;
-    if (!net_out) return fail(ctx, TFPD_ERR_INVALID, "decode: net_out is null");
-    if (((uintptr_t)net_out) & 15) return fail(ctx, TFPD_ERR_INVALID, "decode: net_out must be 16-byte aligned");
-    if (N < 1 || N > ctx->cfg.max_batch) return fail(ctx, TFPD_ERR_INVALID, "decode: batch %d outside 1..%d", N, ctx->cfg.max_batch);
-    if (h < 1 || w < 1 || H < 1 || W < 1) return fail(ctx, TFPD_ERR_INVALID, "decode: non-positive dimension");
-    if (H > ctx->cfg.max_h || W > ctx->cfg.max_w)
-        return fail(ctx, TFPD_ERR_INVALID, "decode: upsample %dx%d exceeds ctx max %dx%d", H, W, ctx->cfg.max_h, ctx->cfg.max_w);
-    const bool want_dense = dense && (dense->heat_up || dense->paf_up || dense->peaks);
-    if (want_dense && !(dense->heat_up && dense->paf_up && dense->peaks))
-        return fail(ctx, TFPD_ERR_INVALID, "decode: dense outputs must be all set or all null");
-    if (want_dense && ((((uintptr_t)dense->heat_up) | ((uintptr_t)dense->paf_up) | ((uintptr_t)dense->peaks)) & 15))
-        return fail(ctx, TFPD_ERR_INVALID, "decode: dense output pointers must be 16-byte aligned");
-    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
-    cudaStream_t s = (cudaStream_t)stream;
-    begin_call(ctx, N, H, W, s);
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->ws.counters, 0, (size_t)N * sizeof(FrameCounters), s));
-    if (ctx->profiling) cudaEventRecord(ctx->ev[0], s);
+// Enqueue the whole decode of N frames on stream s into the workspace view `ws` (arguments validated by the caller).
+static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_out, int N, int h, int w, int H, int W,
+                          cudaStream_t s, const tfpd_dense *dense, bool timed) {
+    const bool want_dense = dense && dense->heat_up;
+    CUDA_TRY(ctx, cudaMemsetAsync(ws.counters, 0, (size_t)N * sizeof(FrameCounters), s));
+    if (timed) cudaEventRecord(ctx->ev[0], s);
 
     PafSource src;
     size_t frame_stride;
@@ -364,10 +406,10 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
         p.heat_up = want_dense ? dense->heat_up : nullptr;
         p.paf_up = want_dense ? dense->paf_up : nullptr;
         p.peaks = want_dense ? dense->peaks : nullptr;
-        p.rec_key = ctx->ws.rec_key;
-        p.rec_val = ctx->ws.rec_val;
-        p.counters = ctx->ws.counters;
-        p.max_peaks = ctx->ws.max_peaks;
+        p.rec_key = ws.rec_key;
+        p.rec_val = ws.rec_val;
+        p.counters = ws.counters;
+        p.max_peaks = ws.max_peaks;
         p.N = N;
         p.h = h;
         p.w = w;
@@ -376,10 +418,10 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
         p.copy_nchunks = (w + 31) / 32;                     // <= 32 cells (29 KB staged) per copy item
         p.copy_chunk = (w + p.copy_nchunks - 1) / p.copy_nchunks;
         p.thresh = ctx->cfg.thresh_heat;
-        p.l2_knobs = 0;
-        if (const char *e = getenv("TFPD_K1_L2")) p.l2_knobs = atoi(e);         // tuning knob
-        p.debug_roles = 3;
-        if (const char *e = getenv("TFPD_K1_ROLES")) p.debug_roles = atoi(e);   // profiling knob
+        p.l2_knobs = ctx->k1_l2_knobs;
+        p.debug_roles = ctx->k1_roles;
+        p.dbg_times = ctx->d_k1_times;
+        p.force_pr = ctx->k1_pr;
         int r = launch_k1_fused_f4(p, want_dense, ctx->sm_count, s);
         if (r < 0) return fail(ctx, TFPD_ERR_CUDA, "k1_fused_f4 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
         ctx->launches += r;
@@ -408,7 +450,7 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
             peaks = nullptr;
         }
         int r = launch_generic_maps(net_out, N, h, w, H, W, ctx->d_k1d, ctx->cfg.blur_ksize, heat_up, paf_up, peaks,
-                                    scratch, ctx->ws, ctx->cfg.thresh_heat, s);
+                                    scratch, ws, ctx->cfg.thresh_heat, s);
         if (r < 0) return fail(ctx, TFPD_ERR_CUDA, "generic map kernels failed: %s", cudaGetErrorString(cudaGetLastError()));
         ctx->launches += r;
         src.base = paf_up;
@@ -420,7 +462,27 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
         src.H = H;
         frame_stride = (size_t)H * W * kPafC;
     }
-    int rc = run_tail(ctx, N, src, frame_stride, s);
+    return run_tail(ctx, ws, N, src, frame_stride, s, timed);
+}
+
+int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W, void *stream,
+                       const tfpd_dense *dense) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!net_out) return fail(ctx, TFPD_ERR_INVALID, "decode: net_out is null");
+    if (((uintptr_t)net_out) & 15) return fail(ctx, TFPD_ERR_INVALID, "decode: net_out must be 16-byte aligned");
+    if (N < 1 || N > ctx->cfg.max_batch) return fail(ctx, TFPD_ERR_INVALID, "decode: batch %d outside 1..%d", N, ctx->cfg.max_batch);
+    if (h < 1 || w < 1 || H < 1 || W < 1) return fail(ctx, TFPD_ERR_INVALID, "decode: non-positive dimension");
+    if (H > ctx->cfg.max_h || W > ctx->cfg.max_w)
+        return fail(ctx, TFPD_ERR_INVALID, "decode: upsample %dx%d exceeds ctx max %dx%d", H, W, ctx->cfg.max_h, ctx->cfg.max_w);
+    const bool want_dense = dense && (dense->heat_up || dense->paf_up || dense->peaks);
+    if (want_dense && !(dense->heat_up && dense->paf_up && dense->peaks))
+        return fail(ctx, TFPD_ERR_INVALID, "decode: dense outputs must be all set or all null");
+    if (want_dense && ((((uintptr_t)dense->heat_up) | ((uintptr_t)dense->paf_up) | ((uintptr_t)dense->peaks)) & 15))
+        return fail(ctx, TFPD_ERR_INVALID, "decode: dense output pointers must be 16-byte aligned");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    begin_call(ctx, N, H, W, s);
+    int rc = enqueue_decode(ctx, ctx->ws, net_out, N, h, w, H, W, s, want_dense ? dense : nullptr, ctx->profiling);
     if (rc != TFPD_OK) return rc;
     ctx->decoded = true;
     return TFPD_OK;
@@ -518,29 +580,76 @@ int tfpd_decode_host(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, i
     if (!net_out) return fail(ctx, TFPD_ERR_INVALID, "decode_host: net_out is null");
     if (N < 1 || N > ctx->cfg.max_batch || h < 1 || w < 1 || H < 1 || W < 1)
         return fail(ctx, TFPD_ERR_INVALID, "decode_host: bad batch or dimension");
+    if (H > ctx->cfg.max_h || W > ctx->cfg.max_w)
+        return fail(ctx, TFPD_ERR_INVALID, "decode_host: upsample %dx%d exceeds ctx max %dx%d", H, W, ctx->cfg.max_h,
+                    ctx->cfg.max_w);
     const bool want_dense = heat_up || paf_up || peaks;
     if (want_dense && !(heat_up && paf_up && peaks))
         return fail(ctx, TFPD_ERR_INVALID, "decode_host: dense outputs must be all set or all null");
     CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
-    const size_t in_bytes = (size_t)N * h * w * kNetC * 4;
-    CUDA_TRY(ctx, ctx->in_buf.reserve(in_bytes));
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->in_buf.p, net_out, in_bytes, cudaMemcpyHostToDevice, nullptr));
-    tfpd_dense d = {nullptr, nullptr, nullptr};
-    const size_t px = (size_t)N * H * W;
+    const size_t frame_in = (size_t)h * w * kNetC * 4;      // multiple of 4; chunk offsets are kept 16-byte aligned below
+    const size_t fpx = (size_t)H * W;
+    CUDA_TRY(ctx, ctx->in_buf.reserve((size_t)N * frame_in));
+    float *d_heat = nullptr, *d_paf = nullptr, *d_peaks = nullptr;
     if (want_dense) {
+        const size_t px = (size_t)N * fpx;
         CUDA_TRY(ctx, ctx->dense_buf.reserve(px * (2 * kHeatC + kPafC) * 4));
-        d.heat_up = (float *)ctx->dense_buf.p;
-        d.paf_up = d.heat_up + px * kHeatC;
-        d.peaks = d.paf_up + px * kPafC;
+        d_heat = (float *)ctx->dense_buf.p;
+        d_paf = d_heat + px * kHeatC;
+        d_peaks = d_paf + px * kPafC;
     }
-    int rc = tfpd_decode_device(ctx, (const float *)ctx->in_buf.p, N, h, w, H, W, nullptr, want_dense ? &d : nullptr);
-    if (rc != TFPD_OK) return rc;
-    if (want_dense) {
-        CUDA_TRY(ctx, cudaMemcpyAsync(heat_up, d.heat_up, px * kHeatC * 4, cudaMemcpyDeviceToHost, nullptr));
-        CUDA_TRY(ctx, cudaMemcpyAsync(paf_up, d.paf_up, px * kPafC * 4, cudaMemcpyDeviceToHost, nullptr));
-        CUDA_TRY(ctx, cudaMemcpyAsync(peaks, d.peaks, px * kHeatC * 4, cudaMemcpyDeviceToHost, nullptr));
+    // Frame chunks: while chunk k is decoded, chunk k+1 crosses PCIe and (dense mode) the maps of chunk k-1 go
+    // back on the other DMA direction.  The x4 fast path only (the generic path has whole-batch scratch), chunk
+    // boundaries on 16-byte aligned input offsets, at least ~4 MB of input per chunk.
+    const bool fast = (H == 4 * h && W == 4 * w && ctx->cfg.blur_ksize == 25);
+    int nchunk = 1;
+    if (fast && N > 1) {
+        int want = ctx->host_chunks > 0 ? ctx->host_chunks : 4;
+        const size_t min_bytes = ctx->host_chunks > 0 ? 1 : ((size_t)4 << 20);
+        while (want > 1 && ((size_t)N * frame_in) / want < min_bytes) --want;
+        nchunk = want < N ? want : N;
     }
-    return tfpd_fetch_humans(ctx, nullptr, nullptr);    // synchronises; reports capacity overflow
+    int align_frames = 1;
+    while ((align_frames * frame_in) & 15) align_frames *= 2;          // <= 4
+    int per = (N + nchunk - 1) / nchunk;
+    per = (per + align_frames - 1) / align_frames * align_frames;
+    nchunk = (N + per - 1) / per;
+    while ((int)ctx->ev_chunk.size() < 2 * nchunk) {
+        cudaEvent_t e;
+        CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->ev_chunk.push_back(e);
+    }
+    begin_call(ctx, N, H, W, ctx->st_work);
+    const bool timed = ctx->profiling && nchunk == 1;
+    for (int k = 0; k < nchunk; ++k) {
+        const int f0 = k * per, n = (f0 + per <= N) ? per : N - f0;
+        const unsigned char *src = (const unsigned char *)net_out + (size_t)f0 * frame_in;
+        unsigned char *dst = (unsigned char *)ctx->in_buf.p + (size_t)f0 * frame_in;
+        CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, (size_t)n * frame_in, cudaMemcpyHostToDevice, ctx->st_h2d));
+        CUDA_TRY(ctx, cudaEventRecord(ctx->ev_chunk[2 * k], ctx->st_h2d));
+        CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->st_work, ctx->ev_chunk[2 * k], 0));
+        tfpd_dense d = {nullptr, nullptr, nullptr};
+        if (want_dense) {
+            d.heat_up = d_heat + (size_t)f0 * fpx * kHeatC;
+            d.paf_up = d_paf + (size_t)f0 * fpx * kPafC;
+            d.peaks = d_peaks + (size_t)f0 * fpx * kHeatC;
+        }
+        int rc = enqueue_decode(ctx, ws_view(ctx->ws, f0), (const float *)dst, n, h, w, H, W, ctx->st_work,
+                                want_dense ? &d : nullptr, timed);
+        if (rc != TFPD_OK) return rc;
+        if (want_dense) {
+            CUDA_TRY(ctx, cudaEventRecord(ctx->ev_chunk[2 * k + 1], ctx->st_work));
+            CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->st_d2h, ctx->ev_chunk[2 * k + 1], 0));
+            const size_t o19 = (size_t)f0 * fpx * kHeatC, o38 = (size_t)f0 * fpx * kPafC;
+            CUDA_TRY(ctx, cudaMemcpyAsync(heat_up + o19, d.heat_up, (size_t)n * fpx * kHeatC * 4, cudaMemcpyDeviceToHost, ctx->st_d2h));
+            CUDA_TRY(ctx, cudaMemcpyAsync(paf_up + o38, d.paf_up, (size_t)n * fpx * kPafC * 4, cudaMemcpyDeviceToHost, ctx->st_d2h));
+            CUDA_TRY(ctx, cudaMemcpyAsync(peaks + o19, d.peaks, (size_t)n * fpx * kHeatC * 4, cudaMemcpyDeviceToHost, ctx->st_d2h));
+        }
+    }
+    ctx->decoded = true;
+    int rc = tfpd_fetch_humans(ctx, nullptr, nullptr);    // synchronises st_work; reports capacity overflow
+    if (want_dense) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->st_d2h));
+    return rc;
 }
 
 int tfpd_process_paf_device(tfpd_ctx *ctx, int p1, int p2, int p3, const float *peaks, int h1, int h2, int h3,
@@ -568,7 +677,7 @@ int tfpd_process_paf_device(tfpd_ctx *ctx, int p1, int p2, int p3, const float *
     src.chan_off = 0;
     src.shift = 0;
     src.H = h1;
-    int rc = run_tail(ctx, 1, src, (size_t)p1 * p2 * kPafC, s);
+    int rc = run_tail(ctx, ctx->ws, 1, src, (size_t)p1 * p2 * kPafC, s, ctx->profiling);
     if (rc != TFPD_OK) return rc;
     ctx->decoded = true;
     return 0;

@@ -34,7 +34,8 @@ namespace {
 
 constexpr int CPL = 2;                      // low-res cells per lane
 constexpr int kBlurWarps = kHeatC;          // 19
-constexpr int kCopyWarps = 1;
+constexpr int kCopyWarps = 1;                // dedicated copy warps (20 warps = 5 per SM sub-partition -> 96 registers)
+constexpr int kHelperWarps = 2;              // blur warps that turn into copy warps once the blur role is done
 constexpr int kBlurThreads = kBlurWarps * 32;
 constexpr int kCopyThreads = kCopyWarps * 32;
 constexpr int kThreads = kBlurThreads + kCopyThreads;   // 640 -> 96 registers per thread
@@ -100,6 +101,11 @@ __device__ __forceinline__ void named_bar(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 __host__ __device__ constexpr int floordiv(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
 
 // bytes of one raw input chunk buffer: the 16-byte aligned superset of copy_chunk cells, 128-byte padded
@@ -151,12 +157,16 @@ __device__ __forceinline__ void copy_prefetch(const K1Params &p, long long R, un
     bulk_load(raw, reinterpret_cast<const unsigned char *>(p.X) + a0, bytes, bar);
 }
 
+// One copy warp.  Items come from a grid-wide queue (atomic counter in the launch's first FrameCounters):
+// per-CTA finish times of a static split spread by +-20 % (measured, tools/k1_cta_times.py) because the
+// warp's pace is set by how fast ITS stores drain, so the split has to follow the pace.  The warp always
+// holds two grabbed items: the one it expands and the one whose bulk load is in flight.
 __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, unsigned char *raws, int raw_bytes,
                           uint64_t *bars, int lane) {
     const int H = 4 * p.h, W = 4 * p.w;
     const size_t total_bytes = (size_t)p.N * p.h * p.w * (kNetC * 4);
-    long long R, Rend;
-    span_of((long long)p.N * p.h * p.copy_nchunks, blockIdx.x, gridDim.x, R, Rend);
+    const long long Rend = (long long)p.N * p.h * p.copy_nchunks;
+    int *queue = &p.counters[0].k1_queue;
     if (lane == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
@@ -164,24 +174,22 @@ __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, uns
     }
     __syncwarp();
     const uint64_t pol_first = policy_evict_first();
-    if ((p.l2_knobs & 1) && lane == 0) {
-        // Pull this CTA's 1/gridDim share of X into L2 up front: DRAM then sees one read burst followed
-        // by an (almost) pure write stream instead of reads sprinkled into the writes.
-        const size_t lo = (total_bytes * blockIdx.x / gridDim.x) & ~(size_t)15;
-        const size_t hi = (blockIdx.x + 1 == gridDim.x) ? (total_bytes & ~(size_t)15)
-                                                        : ((total_bytes * (blockIdx.x + 1) / gridDim.x) & ~(size_t)15);
-        const uint64_t pol_last = policy_evict_last();
-        for (size_t o = lo; o < hi; o += 32768) {
-            const uint32_t nb = (uint32_t)min((size_t)32768, hi - o);
-            if (p.l2_knobs & 4) prefetch_l2_hint(reinterpret_cast<const unsigned char *>(p.X) + o, nb, pol_last);
-            else prefetch_l2(reinterpret_cast<const unsigned char *>(p.X) + o, nb);
-        }
+    long long R = 0, Rn = 0;
+    if (lane == 0) {
+        R = atomicAdd(queue, 1);
+        Rn = atomicAdd(queue, 1);
+        if (R < Rend) copy_prefetch(p, R, raws, &bars[0]);
     }
-    if (R < Rend && lane == 0) copy_prefetch(p, R, raws, &bars[0]);
+    R = __shfl_sync(0xffffffffu, R, 0);
+    Rn = __shfl_sync(0xffffffffu, Rn, 0);
     unsigned k = 0;
-    for (; R < Rend; ++R, ++k) {
+    for (; R < Rend; ++k) {
         const unsigned b = k & 1u;
-        if (R + 1 < Rend && lane == 0) copy_prefetch(p, R + 1, raws + (size_t)(b ^ 1u) * raw_bytes, &bars[b ^ 1u]);
+        long long Rnn = 0;
+        if (lane == 0) {
+            if (Rn < Rend) copy_prefetch(p, Rn, raws + (size_t)(b ^ 1u) * raw_bytes, &bars[b ^ 1u]);
+            Rnn = atomicAdd(queue, 1);                     // consumed at the end of this iteration
+        }
         const CopyItem ci = copy_item(p, R);
         float *sh = cslots + (size_t)b * slot_floats;      // heat part: tc*76 floats
         float *sp = sh + ci.tc * 4 * kHeatC;               // paf part:  tc*152 floats
@@ -245,6 +253,8 @@ __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, uns
             }
             bulk_commit();
         }
+        R = Rn;
+        Rn = __shfl_sync(0xffffffffu, Rnn, 0);
     }
 }
 
@@ -496,10 +506,17 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
     const int cslot_floats = p.copy_chunk * 4 * kNetC;
     const int raw_bytes = k1_raw_bytes(p.copy_chunk);
     float *pslots = smem;                                 // 2 peak-row slots (blur role)
-    float *cslots = smem + 2 * (size_t)pslot_floats;      // 2 replication slots (copy role)
-    unsigned char *raws = reinterpret_cast<unsigned char *>(cslots + 2 * (size_t)cslot_floats);   // 2 raw chunks
-    uint64_t *bars = reinterpret_cast<uint64_t *>(raws + 2 * (size_t)raw_bytes);
+    // per copy warp: 2 replication slots + 2 raw chunks; then 2 mbarriers per copy warp
+    const size_t cw_bytes = 2 * (size_t)cslot_floats * 4 + 2 * (size_t)raw_bytes;
+    unsigned char *cbase = reinterpret_cast<unsigned char *>(smem + 2 * (size_t)pslot_floats);
+    uint64_t *bars_all = reinterpret_cast<uint64_t *>(cbase + kCopyWarps * cw_bytes);
 
+    if (p.dbg_times && tid == 0) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        p.dbg_times[blockIdx.x * 4 + 0] = global_ns();
+        p.dbg_times[blockIdx.x * 4 + 3] = smid;
+    }
     if (warp < kBlurWarps) {
         if (!(p.debug_roles & 1)) return;
         if (DENSE) {
@@ -526,11 +543,30 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
             u += it.nrows;
         }
         if (DENSE && tid == 0) bulk_wait_all();
+        if (p.dbg_times && tid == 0) p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
+        if (DENSE && (p.debug_roles & 2) && kHelperWarps > 0) {
+            // The blur role of this CTA is done (measured: at ~65 % of the kernel) and its peak-row slots are
+            // idle: the first kHelperWarps blur warps carve them into staging buffers and pull copy items from
+            // the same queue as the copy warp until it is empty.
+            named_bar(1, kBlurThreads);                   // every blur warp is past its last slot access; stores drained
+            const size_t cw_bytes_h = 2 * (size_t)cslot_floats * 4 + 2 * (size_t)raw_bytes;
+            const int fit = (int)((2 * (size_t)pslot_floats * 4) / cw_bytes_h);
+            if (warp < kHelperWarps && warp < fit) {
+                float *hslots = reinterpret_cast<float *>(reinterpret_cast<unsigned char *>(pslots) + warp * cw_bytes_h);
+                unsigned char *hraws = reinterpret_cast<unsigned char *>(hslots + 2 * (size_t)cslot_floats);
+                copy_role(p, hslots, cslot_floats, hraws, raw_bytes, bars_all + 2 * (kCopyWarps + warp), lane);
+                if (lane == 0) bulk_wait_all();
+            }
+        }
     } else {
+        const int cw = warp - kBlurWarps;
         if (DENSE && (p.debug_roles & 2)) {
-            copy_role(p, cslots, cslot_floats, raws, raw_bytes, bars, lane);
+            float *cslots = reinterpret_cast<float *>(cbase + cw * cw_bytes);
+            unsigned char *raws = reinterpret_cast<unsigned char *>(cslots + 2 * (size_t)cslot_floats);
+            copy_role(p, cslots, cslot_floats, raws, raw_bytes, bars_all + 2 * cw, lane);
             if (lane == 0) bulk_wait_all();
         }
+        if (p.dbg_times && lane == 0 && cw == 0) p.dbg_times[blockIdx.x * 4 + 2] = global_ns();
     }
 }
 
@@ -563,20 +599,25 @@ int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t
     }
     const size_t cslot = (size_t)p.copy_chunk * 4 * kNetC * 4;
     const size_t raw = (size_t)k1_raw_bytes(p.copy_chunk);
-    const size_t pslot4 = (size_t)4 * p.chunk_cells * 4 * kHeatC * 4;
-    const size_t fixed = 2 * cslot + 2 * raw + 64;
+    const size_t prow = (size_t)p.chunk_cells * 4 * kHeatC * 4;     // one peaks row of a blur chunk
+    const size_t fixed = kCopyWarps * (2 * cslot + 2 * raw) + 16 * (kCopyWarps + kHelperWarps);
     const size_t limit = 227 * 1024 - 1024;
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(k1_fused_f4<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
+        cudaFuncSetAttribute(k1_fused_f4<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
         cudaFuncSetAttribute(k1_fused_f4<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
         attr_set = true;
     }
-    if (2 * pslot4 + fixed <= limit) {
-        k1_fused_f4<4, true><<<grid, kThreads, 2 * pslot4 + fixed, s>>>(p);
-    } else {
-        k1_fused_f4<2, true><<<grid, kThreads, pslot4 + fixed, s>>>(p);
-    }
+    // peak rows per TMA store group: as many as fit next to the copy warps' staging
+    int pr = 4;
+    if (p.force_pr >= 2 && p.force_pr <= 4) pr = p.force_pr;
+    while (pr > 2 && 2 * pr * prow + fixed > limit) --pr;
+    const size_t smem = 2 * pr * prow + fixed;
+    if (smem > limit) return -1;
+    if (pr == 4) k1_fused_f4<4, true><<<grid, kThreads, smem, s>>>(p);
+    else if (pr == 3) k1_fused_f4<3, true><<<grid, kThreads, smem, s>>>(p);
+    else k1_fused_f4<2, true><<<grid, kThreads, smem, s>>>(p);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -24,6 +24,11 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
     unsigned long long *keys = reinterpret_cast<unsigned long long *>(sm_raw);            // [max_cands]
     float *rows = reinterpret_cast<float *>(keys + ws.max_cands);                        // [20][max_rows] SoA
     uint32_t *used = reinterpret_cast<uint32_t *>(rows + 20 * (size_t)ws.max_rows);      // [19][2][128]
+    // the frame's peak table, staged once: assembly and the getter view index it by cid (a dependent global
+    // load per connection was the latency chain of this kernel)
+    float *s_pscore = reinterpret_cast<float *>(used + kLimbs * 2 * kBitmapWords);       // [max_peaks]
+    int16_t *s_pkx = reinterpret_cast<int16_t *>(s_pscore + ws.max_peaks);               // [max_peaks]
+    int16_t *s_pky = s_pkx + ws.max_peaks;                                               // [max_peaks]
     __shared__ int s_lstart[kLimbs + 1];
     __shared__ int s_ccount[kLimbs];
     __shared__ int s_first[kHeatC + 1];
@@ -42,6 +47,15 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
     if (tid <= kLimbs) s_lstart[tid] = cnt;
     if (tid < kLimbs) s_ccount[tid] = 0;
     if (tid == 0) s_flags = (raw > ws.max_cands) ? TFPD_FLAG_CAND_OVERFLOW : 0;
+    {
+        const int npk = min(ws.part_first[n * 20 + kParts], ws.max_peaks);
+        const size_t po = (size_t)n * ws.max_peaks;
+        for (int i = tid; i < npk; i += kK3Threads) {
+            s_pscore[i] = ws.pk_score[po + i];
+            s_pkx[i] = ws.pk_x[po + i];
+            s_pky[i] = ws.pk_y[po + i];
+        }
+    }
     __syncthreads();
 
     // ---- 1. sort ----
@@ -89,7 +103,11 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
             ub[b >> 5] |= 1u << (b & 31);
             c1[beg + nconn] = (int16_t)(fa + a);                // conn.cid1 = peak_a_list[idx1].id (:122)
             c2[beg + nconn] = (int16_t)(fb + b);
-            cs[beg + nconn] = __uint_as_float(0xffffffffu - (uint32_t)((key >> 24) & 0xffffffffu));
+            const uint32_t sbits = 0xffffffffu - (uint32_t)((key >> 24) & 0xffffffffu);
+            cs[beg + nconn] = __uint_as_float(sbits);
+            // the same record for phase 3, packed over a key this walk has already consumed (beg+nconn <= i)
+            keys[beg + nconn] = ((unsigned long long)sbits << 32) | ((unsigned long long)(uint32_t)(fa + a) << 16) |
+                                (unsigned long long)(uint32_t)(fb + b);
             ++nconn;
         }
         s_ccount[limb] = nconn;
@@ -102,7 +120,7 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
     if (warp != 0) return;
 
     // ---- 3. subset assembly (warp 0) ----
-    const float *pscore = ws.pk_score + (size_t)n * ws.max_peaks;
+    const float *pscore = s_pscore;
     int nrows = 0;
     bool row_overflow = false;
     for (int limb = 0; limb < kLimbs; ++limb) {
@@ -111,8 +129,9 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
         float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
         const int beg = s_lstart[limb], nconn = s_ccount[limb];
         for (int k = 0; k < nconn; ++k) {
-            const int cid1 = c1[beg + k], cid2 = c2[beg + k];
-            const float cscore = cs[beg + k];
+            const unsigned long long rec = keys[beg + k];
+            const int cid1 = (int)((rec >> 16) & 0xffffu), cid2 = (int)(rec & 0xffffu);
+            const float cscore = __uint_as_float((uint32_t)(rec >> 32));
             const float f1 = (float)cid1, f2 = (float)cid2;
             int found = 0, r1 = 0, r2 = 0;
             for (int base = 0; base < nrows; base += 32) {
@@ -195,7 +214,7 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
 
     // ---- 4. filter (:185-189) + getter view ----
     const float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
-    const int16_t *pkx = ws.pk_x + (size_t)n * ws.max_peaks, *pky = ws.pk_y + (size_t)n * ws.max_peaks;
+    const int16_t *pkx = s_pkx, *pky = s_pky;
     tfpd_human *out = ws.humans + (size_t)n * ws.max_humans;
     int nh = 0;
     bool human_overflow = false;
@@ -212,7 +231,7 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
             if (slot < ws.max_humans) {
                 tfpd_human *hm = out + slot;
                 hm->score = __fdiv_rn(col18[r], col19[r]);                             // get_score (:202-204)
-#pragma unroll 1
+#pragma unroll 6
                 for (int p = 0; p < kParts; ++p) {
                     const int cid = (int)rows[(size_t)p * MR + r];                     // get_part_cid (:198-200)
                     hm->cid[p] = (int16_t)cid;
@@ -241,7 +260,8 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
 }  // namespace
 
 size_t assemble_smem_bytes(const Workspace &ws) {
-    return (size_t)ws.max_cands * 8 + (size_t)20 * ws.max_rows * 4 + (size_t)kLimbs * 2 * kBitmapWords * 4;
+    return (size_t)ws.max_cands * 8 + (size_t)20 * ws.max_rows * 4 + (size_t)kLimbs * 2 * kBitmapWords * 4 +
+           (size_t)ws.max_peaks * 8;
 }
 
 int launch_assemble(const Workspace &ws, int N, const Thresholds &th, cudaStream_t s) {

@@ -51,6 +51,8 @@ struct FrameCounters {
     int near_ties;
     int n_cand;         // candidates appended by K2 (may exceed max_cands)
     int flags;
+    int k1_queue;       // frame 0 of a launch only: head of K1's copy-item queue (dynamic distribution)
+    int pad_[3];
 };
 
 struct Workspace {
@@ -92,6 +94,8 @@ struct K1Params {
     float thresh;
     int l2_knobs;                       // bit0 up-front L2 prefetch of X, bit1 evict_first stores, bit2 evict_last prefetch
     int debug_roles;                    // bit0 blur role, bit1 copy role (3 = normal; tuning/profiling only)
+    int force_pr;                       // 0 = automatic; 2..4 = peak rows per store group (tuning knob)
+    unsigned long long *dbg_times;      // null, or [grid][4]: CTA start / blur role end / copy role end (ns), SM id
 };
 
 // launchers (each returns the number of kernel launches it issued, <0 on launch error)

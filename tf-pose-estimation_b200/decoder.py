@@ -163,10 +163,12 @@ class PoseDecoder(object):
         self.decode_async(net_out, upsample_size, dense=dense, stream=stream)
         return self.fetch()
 
-    def decode_host(self, net_out, upsample_size, want_dense=False):
+    def decode_host(self, net_out, upsample_size, want_dense=False, out=None):
         """NumPy ``net_out[N,h,w,57]`` (or [h,w,57]) in host memory -> DecodeResult; with
         ``want_dense`` also returns (heat_up, paf_up, peaks) NumPy arrays, i.e. everything one
-        ``sess.run`` + ``estimate_paf`` of the reference yields (estimator.py:536-551)."""
+        ``sess.run`` + ``estimate_paf`` of the reference yields (estimator.py:536-551).
+        ``out`` = preallocated (heat_up, paf_up, peaks) float32 C-contiguous arrays to fill (page-locked
+        memory makes the device->host copies asynchronous and several times faster)."""
         x = np.ascontiguousarray(net_out, np.float32)
         if x.ndim == 3:
             x = x[None]
@@ -175,7 +177,14 @@ class PoseDecoder(object):
         N, h, w, _ = x.shape
         H, W = int(upsample_size[0]), int(upsample_size[1])
         hu = pu = pk = None
-        if want_dense:
+        if out is not None:
+            want_dense = True
+            hu, pu, pk = out
+            for a, ch in ((hu, 19), (pu, 38), (pk, 19)):
+                if not (isinstance(a, np.ndarray) and a.dtype == np.float32 and a.flags.c_contiguous
+                        and a.shape == (N, H, W, ch)):
+                    raise ValueError("out arrays must be C-contiguous float32 [N,H,W,19|38|19]")
+        elif want_dense:
             hu = np.empty((N, H, W, 19), np.float32)
             pu = np.empty((N, H, W, 38), np.float32)
             pk = np.empty((N, H, W, 19), np.float32)
@@ -219,6 +228,13 @@ class PoseDecoder(object):
         out = (C.c_float * 4)()
         self._check(self._L.tfpd_last_stage_ms(self._ctx, C.byref(out)))
         return [float(v) for v in out]
+
+    def k1_cta_times(self, n_ctas=148):
+        """[n_ctas,4] uint64: CTA start / blur-role end / copy-role end (ns), SM id of the last K1 launch
+        (needs TFPD_K1_TIMES=1 in the environment when the decoder is created)."""
+        out = np.zeros((n_ctas, 4), np.uint64)
+        self._check(self._L.tfpd_debug_k1_times(self._ctx, out.ctypes.data, n_ctas))
+        return out
 
     def launch_count(self):
         return int(self._L.tfpd_last_launch_count(self._ctx))
