@@ -224,3 +224,64 @@ def test_argument_validation(cuda):
         d2.fetch()                                                  # fetch before decode
     d2.close()
     dec.close()
+
+
+@pytest.mark.parametrize("mode", ["asbuilt", "upstream"])
+def test_assembly_register_and_shared_memory_paths_agree(cuda, monkeypatch, mode):
+    """K3 keeps the first 64 subset rows in registers and continues in shared memory beyond that
+    (pafprocess.cpp:127-183 either way).  TFPD_K3_REGROWS lowers the switch-over point: 0 = all in shared
+    memory, 3 / 17 = switch in the middle of a limb; every variant must give the same tables as the default,
+    on sparse and on crowded frames."""
+    import torch
+    from helpers import table_tuples
+    xs = [synth.synth_batch(4, 46, 54, config_id=2, first_frame=300),
+          synth.synth_batch(3, 46, 54, config_id=4, people=30, first_frame=20)]
+    cfg = dict(max_peaks=4096, max_cands=8192, max_rows=512, max_humans=128)
+
+    def run(x):
+        dec = tp.PoseDecoder(max_batch=len(x), max_upsample=(184, 216), mode=mode, **cfg)
+        res = dec.decode(torch.from_numpy(x).cuda(), (184, 216))
+        out = ([table_tuples(res, i) for i in range(len(x))], res.info.copy())
+        dec.close()
+        return out
+
+    monkeypatch.delenv("TFPD_K3_REGROWS", raising=False)
+    want = [run(x) for x in xs]
+    assert max(int(w[1]["n_rows"].max()) for w in want) > 17, "the crowded frames must exceed the test's switch-over points"
+    for cap in ("0", "3", "17"):
+        monkeypatch.setenv("TFPD_K3_REGROWS", cap)
+        for x, (tabs, info) in zip(xs, want):
+            got_tabs, got_info = run(x)
+            assert got_tabs == tabs, "TFPD_K3_REGROWS=%s changes the humans" % cap
+            assert np.array_equal(got_info, info)
+
+
+def test_decode_host_chunk_pipelining_is_invisible(cuda, monkeypatch):
+    """tfpd_decode_host overlaps H2D, decode and D2H over frame chunks; any chunk count gives the same
+    tables and dense maps, including ragged last chunks and chunk sizes rounded for 16-byte alignment."""
+    import torch
+    from helpers import table_tuples
+    x = synth.synth_batch(11, 46, 54, config_id=2, first_frame=500)
+    results = []
+    for chunks in ("1", "2", "3", "11", "64"):
+        monkeypatch.setenv("TFPD_HOST_CHUNKS", chunks)
+        dec = tp.PoseDecoder(max_batch=16, max_upsample=(184, 216))
+        res, maps = dec.decode_host(x, (184, 216), want_dense=True)
+        r_min = dec.decode_host(x, (184, 216))
+        results.append(([table_tuples(res, i) for i in range(11)], maps, res.info.copy()))
+        assert [table_tuples(r_min, i) for i in range(11)] == results[-1][0]
+        dec.close()
+    for tabs, maps, info in results[1:]:
+        assert tabs == results[0][0]
+        assert np.array_equal(info, results[0][2])
+        assert all(np.array_equal(a, b) for a, b in zip(maps, results[0][1]))
+    # odd map width: 3*5*57*4 bytes per frame is not a multiple of 16 -> chunk boundaries are rounded
+    x2 = synth.synth_batch(7, 3, 5, config_id=2, first_frame=0)
+    outs = []
+    for chunks in ("1", "4"):
+        monkeypatch.setenv("TFPD_HOST_CHUNKS", chunks)
+        dec = tp.PoseDecoder(max_batch=8, max_upsample=(12, 20))
+        r = dec.decode_host(x2, (12, 20))
+        outs.append([table_tuples(r, i) for i in range(7)] + [r.info.tobytes()])
+        dec.close()
+    assert outs[0] == outs[1]

@@ -10,11 +10,25 @@
 //      in `asbuilt` (found==2 never merges: `int membership;` UB at :152 as compiled by GCC -O2)
 //      or `upstream` (membership = 0) mode,
 //   4. the filter (:185-189) and the getter view (:194-214) -> tfpd_human records.
+#include <type_traits>
+
 #include "tfpd_internal.cuh"
 
 namespace tfpd {
 
 namespace {
+
+// COCOPAIRS (pafprocess.h:16-19) as compile-time functions: the register-resident assembly below needs the
+// part columns of a limb as constants so that the row registers are indexed statically.
+__host__ __device__ constexpr int limb_pa(int l) {
+    constexpr int t[kLimbs] = {1, 1, 2, 3, 5, 6, 1, 8, 9, 1, 11, 12, 1, 0, 14, 0, 15, 2, 5};
+    return t[l];
+}
+__host__ __device__ constexpr int limb_pb(int l) {
+    constexpr int t[kLimbs] = {2, 5, 3, 4, 6, 7, 8, 9, 10, 11, 12, 13, 0, 14, 16, 15, 17, 16, 17};
+    return t[l];
+}
+constexpr int kRegRowsMax = 64;             // subset rows held in registers (2 per lane) before spilling to smem
 
 constexpr int kK3Threads = 640;             // 20 warps: 19 greedy walkers + sort helpers
 constexpr int kBitmapWords = kMaxPeaksHard / 32;   // 128
@@ -120,15 +134,178 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
     if (warp != 0) return;
 
     // ---- 3. subset assembly (warp 0) ----
+    // Fast path: the first kRegRowsMax rows live in registers, row r in lane r & 31, slot r >> 5 (20 floats
+    // each, exactly the reference's vector<float> rows).  One connection is then: two compares per lane, a
+    // ballot, and an update inside the owning lane -- no shared-memory round trips on the serial chain
+    // (the smem version spent ~900 cycles per connection on them).  When a 65th row is needed the registers
+    // are spilled to the smem rows and the generic loop below continues from the same (limb, connection).
     const float *pscore = s_pscore;
+    const unsigned FULL = 0xffffffffu;
     int nrows = 0;
     bool row_overflow = false;
-    for (int limb = 0; limb < kLimbs; ++limb) {
+    int limb0 = kLimbs, k0 = 0;                       // where the generic loop resumes (kLimbs = nowhere)
+    {
+        float rr[2][20];
+#pragma unroll
+        for (int c = 0; c < 20; ++c) rr[0][c] = rr[1][c] = -1.0f;
+        const int reg_cap = min(min(ws.k3_reg_rows, kRegRowsMax), MR);
+        bool in_regs = true;
+        auto fast_limb = [&](auto ltag) {
+            constexpr int L = decltype(ltag)::value;
+            constexpr int PA = limb_pa(L), PB = limb_pb(L);
+            if (!in_regs) return;
+            const int beg = s_lstart[L], nconn = s_ccount[L];
+            for (int k = 0; k < nconn; ++k) {
+                const unsigned long long rec = keys[beg + k];
+                const int cid1 = (int)((rec >> 16) & 0xffffu), cid2 = (int)(rec & 0xffffu);
+                const float cscore = __uint_as_float((uint32_t)(rec >> 32));
+                const float f1 = (float)cid1, f2 = (float)cid2;
+                const float ps1 = pscore[cid1], ps2 = pscore[cid2];
+                const bool h0 = (lane < nrows) && (rr[0][PA] == f1 || rr[0][PB] == f2);             // :137
+                const unsigned b0 = __ballot_sync(FULL, h0);
+                unsigned b1 = 0u;
+                if (nrows > 32) {
+                    const bool h1 = (lane + 32 < nrows) && (rr[1][PA] == f1 || rr[1][PB] == f2);
+                    b1 = __ballot_sync(FULL, h1);
+                }
+                const int found = __popc(b0) + __popc(b1);
+                if (found == 0) {
+                    if (L < 17) {                                                               // :171-181
+                        if (nrows >= reg_cap) {
+                            if (nrows >= MR) {
+                                row_overflow = true;
+                                continue;
+                            }
+                            in_regs = false;            // continue in shared memory from this connection
+                            limb0 = L;
+                            k0 = k;
+                            return;
+                        }
+                        const float sc = __fadd_rn(__fadd_rn(ps1, ps2), cscore);
+                        if (lane == (nrows & 31)) {
+                            if (nrows < 32) {
+#pragma unroll
+                                for (int c = 0; c < 18; ++c) rr[0][c] = -1.0f;
+                                rr[0][PA] = f1;
+                                rr[0][PB] = f2;
+                                rr[0][18] = sc;
+                                rr[0][19] = 2.0f;
+                            } else {
+#pragma unroll
+                                for (int c = 0; c < 18; ++c) rr[1][c] = -1.0f;
+                                rr[1][PA] = f1;
+                                rr[1][PB] = f2;
+                                rr[1][18] = sc;
+                                rr[1][19] = 2.0f;
+                            }
+                        }
+                        ++nrows;
+                    }
+                } else if (found <= 2) {
+                    const int r1 = b0 ? (__ffs(b0) - 1) : (32 + __ffs(b1) - 1);
+                    bool merge = false;
+                    int r2 = 0;
+                    if (found == 2 && th.mode == TFPD_MODE_UPSTREAM) {
+                        const unsigned rest0 = b0 & (b0 - 1u);
+                        r2 = (b0 == 0u) ? (32 + __ffs(b1 & (b1 - 1u)) - 1) : (rest0 ? (__ffs(rest0) - 1) : (32 + __ffs(b1) - 1));
+                        // row r2 to every lane, then lane r1 tests the membership condition (:153-157)
+                        float v2[20];
+#pragma unroll
+                        for (int c = 0; c < 20; ++c) v2[c] = __shfl_sync(FULL, (r2 < 32) ? rr[0][c] : rr[1][c], r2 & 31);
+                        bool both = false;
+                        if (lane == (r1 & 31)) {
+#pragma unroll
+                            for (int c = 0; c < 18; ++c) {
+                                const float own = (r1 < 32) ? rr[0][c] : rr[1][c];
+                                both = both || (own > 0.0f && v2[c] > 0.0f);
+                            }
+                        }
+                        merge = (__ballot_sync(FULL, both) == 0u);
+                        if (merge) {                                                            // :159-165
+                            if (lane == (r1 & 31)) {
+#pragma unroll
+                                for (int c = 0; c < 18; ++c) {
+                                    if (r1 < 32) rr[0][c] = __fadd_rn(rr[0][c], __fadd_rn(v2[c], 1.0f));
+                                    else rr[1][c] = __fadd_rn(rr[1][c], __fadd_rn(v2[c], 1.0f));
+                                }
+                                if (r1 < 32) {
+                                    rr[0][19] = __fadd_rn(rr[0][19], v2[19]);
+                                    rr[0][18] = __fadd_rn(__fadd_rn(rr[0][18], v2[18]), cscore);
+                                } else {
+                                    rr[1][19] = __fadd_rn(rr[1][19], v2[19]);
+                                    rr[1][18] = __fadd_rn(__fadd_rn(rr[1][18], v2[18]), cscore);
+                                }
+                            }
+                            // subset.erase(begin + r2): every later row moves up by one
+#pragma unroll
+                            for (int c = 0; c < 20; ++c) {
+                                float n0 = __shfl_down_sync(FULL, rr[0][c], 1);
+                                const float first1 = __shfl_sync(FULL, rr[1][c], 0);
+                                const float n1 = __shfl_down_sync(FULL, rr[1][c], 1);
+                                if (lane == 31) n0 = first1;
+                                if (r2 < 32) {
+                                    if (lane >= r2) rr[0][c] = n0;
+                                    rr[1][c] = n1;
+                                } else if (lane >= r2 - 32) {
+                                    rr[1][c] = n1;
+                                }
+                            }
+                            --nrows;
+                        }
+                    }
+                    if (!merge && lane == (r1 & 31)) {                            // :144-149 / :166-170
+                        if (r1 < 32) {
+                            if (found == 2 || rr[0][PB] != f2) {
+                                rr[0][PB] = f2;
+                                rr[0][19] = __fadd_rn(rr[0][19], 1.0f);
+                                rr[0][18] = __fadd_rn(rr[0][18], __fadd_rn(ps2, cscore));
+                            }
+                        } else {
+                            if (found == 2 || rr[1][PB] != f2) {
+                                rr[1][PB] = f2;
+                                rr[1][19] = __fadd_rn(rr[1][19], 1.0f);
+                                rr[1][18] = __fadd_rn(rr[1][18], __fadd_rn(ps2, cscore));
+                            }
+                        }
+                    }
+                } else {
+                    if (lane == 0) atomicOr(&s_flags, TFPD_FLAG_FOUND_GT2);
+                }
+            }
+        };
+        fast_limb(std::integral_constant<int, 0>());
+        fast_limb(std::integral_constant<int, 1>());
+        fast_limb(std::integral_constant<int, 2>());
+        fast_limb(std::integral_constant<int, 3>());
+        fast_limb(std::integral_constant<int, 4>());
+        fast_limb(std::integral_constant<int, 5>());
+        fast_limb(std::integral_constant<int, 6>());
+        fast_limb(std::integral_constant<int, 7>());
+        fast_limb(std::integral_constant<int, 8>());
+        fast_limb(std::integral_constant<int, 9>());
+        fast_limb(std::integral_constant<int, 10>());
+        fast_limb(std::integral_constant<int, 11>());
+        fast_limb(std::integral_constant<int, 12>());
+        fast_limb(std::integral_constant<int, 13>());
+        fast_limb(std::integral_constant<int, 14>());
+        fast_limb(std::integral_constant<int, 15>());
+        fast_limb(std::integral_constant<int, 16>());
+        fast_limb(std::integral_constant<int, 17>());
+        fast_limb(std::integral_constant<int, 18>());
+        // the rows go to shared memory either way: the generic loop, the filter and the getter view read them there
+#pragma unroll
+        for (int c = 0; c < 20; ++c) {
+            if (lane < nrows) rows[(size_t)c * MR + lane] = rr[0][c];
+            if (lane + 32 < nrows) rows[(size_t)c * MR + lane + 32] = rr[1][c];
+        }
+        __syncwarp();
+    }
+    for (int limb = limb0; limb < kLimbs; ++limb) {
         const int pa = c_limb_part[limb][0], pb = c_limb_part[limb][1];
         float *colA = rows + (size_t)pa * MR, *colB = rows + (size_t)pb * MR;
         float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
         const int beg = s_lstart[limb], nconn = s_ccount[limb];
-        for (int k = 0; k < nconn; ++k) {
+        for (int k = (limb == limb0) ? k0 : 0; k < nconn; ++k) {
             const unsigned long long rec = keys[beg + k];
             const int cid1 = (int)((rec >> 16) & 0xffffu), cid2 = (int)(rec & 0xffffu);
             const float cscore = __uint_as_float((uint32_t)(rec >> 32));
