@@ -134,137 +134,142 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
     if (warp != 0) return;
 
     // ---- 3. subset assembly (warp 0) ----
-    // Fast path: the first kRegRowsMax rows live in registers, row r in lane r & 31, slot r >> 5 (20 floats
-    // each, exactly the reference's vector<float> rows).  One connection is then: two compares per lane, a
-    // ballot, and an update inside the owning lane -- no shared-memory round trips on the serial chain
-    // (the smem version spent ~900 cycles per connection on them).  When a 65th row is needed the registers
-    // are spilled to the smem rows and the generic loop below continues from the same (limb, connection).
+    // Fast path for the first kRegRowsMax rows: row r belongs to lane r & 31, slot r >> 5.  A limb only ever
+    // looks at two columns of a row (its parts PA, PB) and updates PB, the score and the count, so per limb each
+    // lane pulls its rows' PA / PB entries out of the smem table ONCE, keeps score and count in registers for the
+    // whole assembly, and a connection is then two compares per lane, a ballot and an update inside the owning
+    // lane -- no shared-memory round trip on the serial chain (the all-smem loop below spends ~900 cycles per
+    // connection on them) and, unlike a per-limb instantiation with statically indexed row registers, one small
+    // loop body that stays in the instruction cache.  When a 65th row is needed, the registers go back to the smem
+    // rows and the generic loop below continues from the same (limb, connection).
     const float *pscore = s_pscore;
     const unsigned FULL = 0xffffffffu;
     int nrows = 0;
     bool row_overflow = false;
     int limb0 = kLimbs, k0 = 0;                       // where the generic loop resumes (kLimbs = nowhere)
     {
-        float rr[2][20];
-#pragma unroll
-        for (int c = 0; c < 20; ++c) rr[0][c] = rr[1][c] = -1.0f;
         const int reg_cap = min(min(ws.k3_reg_rows, kRegRowsMax), MR);
-        bool in_regs = true;
-        auto fast_limb = [&](auto ltag) {
-            constexpr int L = decltype(ltag)::value;
-            constexpr int PA = limb_pa(L), PB = limb_pb(L);
-            if (!in_regs) return;
-            const int beg = s_lstart[L], nconn = s_ccount[L];
+        // a row that does not exist yet reads as "no part anywhere": creating one (:172-180) is then 4 writes
+        for (int c = 0; c < kParts; ++c) {
+            if (lane < MR) rows[(size_t)c * MR + lane] = -1.0f;
+            if (lane + 32 < MR) rows[(size_t)c * MR + lane + 32] = -1.0f;
+        }
+        __syncwarp();
+        float sc0 = 0.f, sc1 = 0.f, cn0 = 0.f, cn1 = 0.f;            // columns 18 / 19 of this lane's two rows
+        const bool own0 = lane < MR, own1 = lane + 32 < MR;
+        for (int limb = 0; limb < kLimbs && limb0 == kLimbs; ++limb) {
+            const int pa = c_limb_part[limb][0], pb = c_limb_part[limb][1];
+            float *colA = rows + (size_t)pa * MR, *colB = rows + (size_t)pb * MR;
+            float a0 = own0 ? colA[lane] : -1.0f, a1 = own1 ? colA[lane + 32] : -1.0f;
+            float b0v = own0 ? colB[lane] : -1.0f, b1v = own1 ? colB[lane + 32] : -1.0f;
+            const int beg = s_lstart[limb], nconn = s_ccount[limb];
             for (int k = 0; k < nconn; ++k) {
                 const unsigned long long rec = keys[beg + k];
                 const int cid1 = (int)((rec >> 16) & 0xffffu), cid2 = (int)(rec & 0xffffu);
                 const float cscore = __uint_as_float((uint32_t)(rec >> 32));
                 const float f1 = (float)cid1, f2 = (float)cid2;
                 const float ps1 = pscore[cid1], ps2 = pscore[cid2];
-                const bool h0 = (lane < nrows) && (rr[0][PA] == f1 || rr[0][PB] == f2);             // :137
-                const unsigned b0 = __ballot_sync(FULL, h0);
-                unsigned b1 = 0u;
-                if (nrows > 32) {
-                    const bool h1 = (lane + 32 < nrows) && (rr[1][PA] == f1 || rr[1][PB] == f2);
-                    b1 = __ballot_sync(FULL, h1);
-                }
-                const int found = __popc(b0) + __popc(b1);
+                const unsigned m0 = __ballot_sync(FULL, (lane < nrows) && (a0 == f1 || b0v == f2));     // :137
+                unsigned m1 = 0u;
+                if (nrows > 32) m1 = __ballot_sync(FULL, (lane + 32 < nrows) && (a1 == f1 || b1v == f2));
+                const int found = __popc(m0) + __popc(m1);
                 if (found == 0) {
-                    if (L < 17) {                                                               // :171-181
+                    if (limb < 17) {                                                            // :171-181
                         if (nrows >= reg_cap) {
                             if (nrows >= MR) {
                                 row_overflow = true;
                                 continue;
                             }
-                            in_regs = false;            // continue in shared memory from this connection
-                            limb0 = L;
+                            limb0 = limb;               // continue in shared memory from this connection
                             k0 = k;
-                            return;
+                            break;
                         }
                         const float sc = __fadd_rn(__fadd_rn(ps1, ps2), cscore);
                         if (lane == (nrows & 31)) {
                             if (nrows < 32) {
-#pragma unroll
-                                for (int c = 0; c < 18; ++c) rr[0][c] = -1.0f;
-                                rr[0][PA] = f1;
-                                rr[0][PB] = f2;
-                                rr[0][18] = sc;
-                                rr[0][19] = 2.0f;
+                                a0 = f1;
+                                b0v = f2;
+                                sc0 = sc;
+                                cn0 = 2.0f;
                             } else {
-#pragma unroll
-                                for (int c = 0; c < 18; ++c) rr[1][c] = -1.0f;
-                                rr[1][PA] = f1;
-                                rr[1][PB] = f2;
-                                rr[1][18] = sc;
-                                rr[1][19] = 2.0f;
+                                a1 = f1;
+                                b1v = f2;
+                                sc1 = sc;
+                                cn1 = 2.0f;
                             }
                         }
                         ++nrows;
                     }
                 } else if (found <= 2) {
-                    const int r1 = b0 ? (__ffs(b0) - 1) : (32 + __ffs(b1) - 1);
-                    bool merge = false;
-                    int r2 = 0;
+                    const int r1 = m0 ? (__ffs(m0) - 1) : (32 + __ffs(m1) - 1);
+                    bool merged = false;
                     if (found == 2 && th.mode == TFPD_MODE_UPSTREAM) {
-                        const unsigned rest0 = b0 & (b0 - 1u);
-                        r2 = (b0 == 0u) ? (32 + __ffs(b1 & (b1 - 1u)) - 1) : (rest0 ? (__ffs(rest0) - 1) : (32 + __ffs(b1) - 1));
-                        // row r2 to every lane, then lane r1 tests the membership condition (:153-157)
-                        float v2[20];
-#pragma unroll
-                        for (int c = 0; c < 20; ++c) v2[c] = __shfl_sync(FULL, (r2 < 32) ? rr[0][c] : rr[1][c], r2 & 31);
-                        bool both = false;
-                        if (lane == (r1 & 31)) {
-#pragma unroll
-                            for (int c = 0; c < 18; ++c) {
-                                const float own = (r1 < 32) ? rr[0][c] : rr[1][c];
-                                both = both || (own > 0.0f && v2[c] > 0.0f);
-                            }
+                        // :151-165, rare: done on the smem rows (one copy of the code), registers re-read after
+                        const unsigned rest0 = m0 & (m0 - 1u);
+                        const int r2 = (m0 == 0u) ? (32 + __ffs(m1 & (m1 - 1u)) - 1)
+                                                  : (rest0 ? (__ffs(rest0) - 1) : (32 + __ffs(m1) - 1));
+                        float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
+                        if (lane < nrows) {
+                            colA[lane] = a0;
+                            colB[lane] = b0v;
+                            col18[lane] = sc0;
+                            col19[lane] = cn0;
                         }
-                        merge = (__ballot_sync(FULL, both) == 0u);
-                        if (merge) {                                                            // :159-165
-                            if (lane == (r1 & 31)) {
-#pragma unroll
-                                for (int c = 0; c < 18; ++c) {
-                                    if (r1 < 32) rr[0][c] = __fadd_rn(rr[0][c], __fadd_rn(v2[c], 1.0f));
-                                    else rr[1][c] = __fadd_rn(rr[1][c], __fadd_rn(v2[c], 1.0f));
-                                }
-                                if (r1 < 32) {
-                                    rr[0][19] = __fadd_rn(rr[0][19], v2[19]);
-                                    rr[0][18] = __fadd_rn(__fadd_rn(rr[0][18], v2[18]), cscore);
-                                } else {
-                                    rr[1][19] = __fadd_rn(rr[1][19], v2[19]);
-                                    rr[1][18] = __fadd_rn(__fadd_rn(rr[1][18], v2[18]), cscore);
-                                }
+                        if (lane + 32 < nrows) {
+                            colA[lane + 32] = a1;
+                            colB[lane + 32] = b1v;
+                            col18[lane + 32] = sc1;
+                            col19[lane + 32] = cn1;
+                        }
+                        __syncwarp();
+                        const bool both = (lane < kParts) && (rows[(size_t)lane * MR + r1] > 0.0f) &&
+                                          (rows[(size_t)lane * MR + r2] > 0.0f);
+                        merged = (__ballot_sync(FULL, both) == 0u);                    // :153-157
+                        if (merged) {
+                            if (lane < kParts) {
+                                float *cc = rows + (size_t)lane * MR;
+                                cc[r1] = __fadd_rn(cc[r1], __fadd_rn(cc[r2], 1.0f));
+                            } else if (lane == 18) {
+                                col18[r1] = __fadd_rn(__fadd_rn(col18[r1], col18[r2]), cscore);
+                            } else if (lane == 19) {
+                                col19[r1] = __fadd_rn(col19[r1], col19[r2]);
                             }
-                            // subset.erase(begin + r2): every later row moves up by one
-#pragma unroll
+                            __syncwarp();
+                            // subset.erase(begin + r2); the vacated last row reads as "not there" again
                             for (int c = 0; c < 20; ++c) {
-                                float n0 = __shfl_down_sync(FULL, rr[0][c], 1);
-                                const float first1 = __shfl_sync(FULL, rr[1][c], 0);
-                                const float n1 = __shfl_down_sync(FULL, rr[1][c], 1);
-                                if (lane == 31) n0 = first1;
-                                if (r2 < 32) {
-                                    if (lane >= r2) rr[0][c] = n0;
-                                    rr[1][c] = n1;
-                                } else if (lane >= r2 - 32) {
-                                    rr[1][c] = n1;
-                                }
+                                float *cc = rows + (size_t)c * MR;
+                                const int ra = lane, rb = lane + 32;
+                                float v0 = 0.f, v1 = 0.f;
+                                if (ra >= r2 && ra < nrows) v0 = (ra + 1 < nrows) ? cc[ra + 1] : -1.0f;
+                                if (rb >= r2 && rb < nrows) v1 = (rb + 1 < nrows) ? cc[rb + 1] : -1.0f;
+                                __syncwarp();
+                                if (ra >= r2 && ra < nrows) cc[ra] = v0;
+                                if (rb >= r2 && rb < nrows) cc[rb] = v1;
                             }
                             --nrows;
+                            __syncwarp();
+                            a0 = own0 ? colA[lane] : -1.0f;
+                            a1 = own1 ? colA[lane + 32] : -1.0f;
+                            b0v = own0 ? colB[lane] : -1.0f;
+                            b1v = own1 ? colB[lane + 32] : -1.0f;
+                            sc0 = own0 ? col18[lane] : 0.f;
+                            sc1 = own1 ? col18[lane + 32] : 0.f;
+                            cn0 = own0 ? col19[lane] : 0.f;
+                            cn1 = own1 ? col19[lane + 32] : 0.f;
                         }
                     }
-                    if (!merge && lane == (r1 & 31)) {                            // :144-149 / :166-170
+                    if (!merged && lane == (r1 & 31)) {                           // :144-149 / :166-170
                         if (r1 < 32) {
-                            if (found == 2 || rr[0][PB] != f2) {
-                                rr[0][PB] = f2;
-                                rr[0][19] = __fadd_rn(rr[0][19], 1.0f);
-                                rr[0][18] = __fadd_rn(rr[0][18], __fadd_rn(ps2, cscore));
+                            if (found == 2 || b0v != f2) {
+                                b0v = f2;
+                                cn0 = __fadd_rn(cn0, 1.0f);
+                                sc0 = __fadd_rn(sc0, __fadd_rn(ps2, cscore));
                             }
                         } else {
-                            if (found == 2 || rr[1][PB] != f2) {
-                                rr[1][PB] = f2;
-                                rr[1][19] = __fadd_rn(rr[1][19], 1.0f);
-                                rr[1][18] = __fadd_rn(rr[1][18], __fadd_rn(ps2, cscore));
+                            if (found == 2 || b1v != f2) {
+                                b1v = f2;
+                                cn1 = __fadd_rn(cn1, 1.0f);
+                                sc1 = __fadd_rn(sc1, __fadd_rn(ps2, cscore));
                             }
                         }
                     }
@@ -272,31 +277,25 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
                     if (lane == 0) atomicOr(&s_flags, TFPD_FLAG_FOUND_GT2);
                 }
             }
-        };
-        fast_limb(std::integral_constant<int, 0>());
-        fast_limb(std::integral_constant<int, 1>());
-        fast_limb(std::integral_constant<int, 2>());
-        fast_limb(std::integral_constant<int, 3>());
-        fast_limb(std::integral_constant<int, 4>());
-        fast_limb(std::integral_constant<int, 5>());
-        fast_limb(std::integral_constant<int, 6>());
-        fast_limb(std::integral_constant<int, 7>());
-        fast_limb(std::integral_constant<int, 8>());
-        fast_limb(std::integral_constant<int, 9>());
-        fast_limb(std::integral_constant<int, 10>());
-        fast_limb(std::integral_constant<int, 11>());
-        fast_limb(std::integral_constant<int, 12>());
-        fast_limb(std::integral_constant<int, 13>());
-        fast_limb(std::integral_constant<int, 14>());
-        fast_limb(std::integral_constant<int, 15>());
-        fast_limb(std::integral_constant<int, 16>());
-        fast_limb(std::integral_constant<int, 17>());
-        fast_limb(std::integral_constant<int, 18>());
-        // the rows go to shared memory either way: the generic loop, the filter and the getter view read them there
-#pragma unroll
-        for (int c = 0; c < 20; ++c) {
-            if (lane < nrows) rows[(size_t)c * MR + lane] = rr[0][c];
-            if (lane + 32 < nrows) rows[(size_t)c * MR + lane + 32] = rr[1][c];
+            // this limb's columns go back to the table (PA changes only where a row was created)
+            if (lane < nrows) {
+                colA[lane] = a0;
+                colB[lane] = b0v;
+            }
+            if (lane + 32 < nrows) {
+                colA[lane + 32] = a1;
+                colB[lane + 32] = b1v;
+            }
+            __syncwarp();
+        }
+        float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
+        if (lane < nrows) {
+            col18[lane] = sc0;
+            col19[lane] = cn0;
+        }
+        if (lane + 32 < nrows) {
+            col18[lane + 32] = sc1;
+            col19[lane + 32] = cn1;
         }
         __syncwarp();
     }
