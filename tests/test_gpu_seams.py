@@ -228,10 +228,11 @@ def test_argument_validation(cuda):
 
 @pytest.mark.parametrize("mode", ["asbuilt", "upstream"])
 def test_assembly_register_and_shared_memory_paths_agree(cuda, monkeypatch, mode):
-    """K3 keeps the first 64 subset rows in registers and continues in shared memory beyond that
+    """K3 keeps the first 128 subset rows in registers and continues in shared memory beyond that
     (pafprocess.cpp:127-183 either way).  TFPD_K3_REGROWS lowers the switch-over point: 0 = all in shared
-    memory, 3 / 17 = switch in the middle of a limb; every variant must give the same tables as the default,
-    on sparse and on crowded frames."""
+    memory, 3 / 17 / 25 = switch in the middle of a limb; TFPD_K3_WARPSORT=0 forces the frame-wide sort instead
+    of the per-limb warp sorts.  Every variant must give the same tables as the default, on sparse and on
+    crowded frames."""
     import torch
     from helpers import table_tuples
     xs = [synth.synth_batch(4, 46, 54, config_id=2, first_frame=300),
@@ -246,14 +247,17 @@ def test_assembly_register_and_shared_memory_paths_agree(cuda, monkeypatch, mode
         return out
 
     monkeypatch.delenv("TFPD_K3_REGROWS", raising=False)
+    monkeypatch.delenv("TFPD_K3_WARPSORT", raising=False)
     want = [run(x) for x in xs]
-    assert max(int(w[1]["n_rows"].max()) for w in want) > 17, "the crowded frames must exceed the test's switch-over points"
-    for cap in ("0", "3", "17"):
-        monkeypatch.setenv("TFPD_K3_REGROWS", cap)
+    assert max(int(w[1]["n_rows"].max()) for w in want) > 25, "the crowded frames must exceed the test's switch-over points"
+    for var, val in (("TFPD_K3_REGROWS", "0"), ("TFPD_K3_REGROWS", "3"), ("TFPD_K3_REGROWS", "17"),
+                     ("TFPD_K3_REGROWS", "25"), ("TFPD_K3_WARPSORT", "0")):
+        monkeypatch.setenv(var, val)
         for x, (tabs, info) in zip(xs, want):
             got_tabs, got_info = run(x)
-            assert got_tabs == tabs, "TFPD_K3_REGROWS=%s changes the humans" % cap
+            assert got_tabs == tabs, "%s=%s changes the humans" % (var, val)
             assert np.array_equal(got_info, info)
+        monkeypatch.delenv(var)
 
 
 def test_decode_host_chunk_pipelining_is_invisible(cuda, monkeypatch):

@@ -28,7 +28,8 @@ __host__ __device__ constexpr int limb_pb(int l) {
     constexpr int t[kLimbs] = {2, 5, 3, 4, 6, 7, 8, 9, 10, 11, 12, 13, 0, 14, 16, 15, 17, 16, 17};
     return t[l];
 }
-constexpr int kRegRowsMax = 64;             // subset rows held in registers (2 per lane) before spilling to smem
+constexpr int kWarpSortMax = 1024;           // longest limb segment a single warp sorts
+constexpr int kRegRowsMax = 128;            // subset rows held in registers (4 per lane) before spilling to smem
 
 constexpr int kK3Threads = 640;             // 20 warps: 19 greedy walkers + sort helpers
 constexpr int kBitmapWords = kMaxPeaksHard / 32;   // 128
@@ -48,18 +49,17 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
     __shared__ int s_first[kHeatC + 1];
     __shared__ int s_flags;
 
+    __shared__ int s_lcount[kLimbs], s_lfill[kLimbs];
+    __shared__ int s_maxseg;
+
     const int n = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int MR = ws.max_rows;
     const int raw = ws.counters[n].n_cand;
     const int cnt = min(raw, ws.max_cands);
-    int np2 = 32;
-    while (np2 < cnt) np2 <<= 1;
-    for (int i = tid; i < np2; i += kK3Threads)
-        keys[i] = (i < cnt) ? ws.cand_key[(size_t)n * ws.max_cands + i] : ~0ull;
+    const unsigned long long *gkeys = ws.cand_key + (size_t)n * ws.max_cands;
     for (int i = tid; i < kLimbs * 2 * kBitmapWords; i += kK3Threads) used[i] = 0u;
     if (tid <= kHeatC) s_first[tid] = ws.part_first[n * 20 + tid];
-    if (tid <= kLimbs) s_lstart[tid] = cnt;
-    if (tid < kLimbs) s_ccount[tid] = 0;
+    if (tid < kLimbs) s_ccount[tid] = s_lcount[tid] = s_lfill[tid] = 0;
     if (tid == 0) s_flags = (raw > ws.max_cands) ? TFPD_FLAG_CAND_OVERFLOW : 0;
     {
         const int npk = min(ws.part_first[n * 20 + kParts], ws.max_peaks);
@@ -72,30 +72,83 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
     }
     __syncthreads();
 
-    // ---- 1. sort ----
-    for (int k = 2; k <= np2; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = tid; i < np2; i += kK3Threads) {
-                int ixj = i ^ j;
-                if (ixj > i) {
-                    bool up = ((i & k) == 0);
-                    unsigned long long a = keys[i], b = keys[ixj];
-                    if ((a > b) == up) {
-                        keys[i] = b;
-                        keys[ixj] = a;
+    // ---- 1. per-limb ordering ----
+    // The key's top byte is the limb, so the frame-wide order is: limb segments, each sorted.  Bucket the
+    // candidates by limb (count, prefix, scatter: two passes over the global list), then every limb's segment
+    // is sorted by its own warp with only warp-level synchronisation -- a frame-wide bitonic sort pays a
+    // 640-thread barrier per stage (66 stages for 2048 candidates).
+    for (int i = tid; i < cnt; i += kK3Threads) atomicAdd(&s_lcount[(int)(gkeys[i] >> 56)], 1);
+    __syncthreads();
+    if (tid == 0) {
+        int acc = 0, mx = 0;
+        for (int l = 0; l < kLimbs; ++l) {
+            s_lstart[l] = acc;
+            acc += s_lcount[l];
+            mx = max(mx, s_lcount[l]);
+        }
+        s_lstart[kLimbs] = acc;
+        s_maxseg = mx;
+    }
+    __syncthreads();
+    for (int i = tid; i < cnt; i += kK3Threads) {
+        const unsigned long long key = gkeys[i];
+        const int limb = (int)(key >> 56);
+        keys[s_lstart[limb] + atomicAdd(&s_lfill[limb], 1)] = key;
+    }
+    __syncthreads();
+    if (s_maxseg <= min(kWarpSortMax, ws.k3_warp_sort_max)) {
+        // bitonic network with a mirrored first stage per block: every comparator puts the smaller key at the
+        // lower index, so the (virtual) +inf padding beyond the segment never moves and is simply skipped
+        if (warp < kLimbs) {
+            unsigned long long *seg = keys + s_lstart[warp];
+            const int len = s_lcount[warp];
+            int np2 = 1;
+            while (np2 < len) np2 <<= 1;
+            for (int k = 2; k <= np2; k <<= 1) {
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    const int mask = (j == (k >> 1)) ? (k - 1) : j;
+                    for (int i = lane; i < len; i += 32) {
+                        const int l = i ^ mask;
+                        if (l > i && l < len) {
+                            const unsigned long long a = seg[i], b = seg[l];
+                            if (a > b) {
+                                seg[i] = b;
+                                seg[l] = a;
+                            }
+                        }
                     }
+                    __syncwarp();
                 }
             }
-            __syncthreads();
+        }
+    } else {
+        // a very long segment (one limb with > kWarpSortMax candidates): frame-wide bitonic sort by all threads;
+        // the key order (limb first) keeps the segments where they are
+        int np2 = 32;
+        while (np2 < cnt) np2 <<= 1;
+        for (int i = cnt + tid; i < np2; i += kK3Threads) keys[i] = ~0ull;
+        __syncthreads();
+        for (int k = 2; k <= np2; k <<= 1) {
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int i = tid; i < np2; i += kK3Threads) {
+                    int ixj = i ^ j;
+                    if (ixj > i) {
+                        bool up = ((i & k) == 0);
+                        unsigned long long a = keys[i], b = keys[ixj];
+                        if ((a > b) == up) {
+                            keys[i] = b;
+                            keys[ixj] = a;
+                        }
+                    }
+                }
+                __syncthreads();
+            }
         }
     }
-    // limb segments + exact-tie detection
-    for (int i = tid; i < cnt; i += kK3Threads) {
-        int limb = (int)(keys[i] >> 56);
-        int prev = (i == 0) ? -1 : (int)(keys[i - 1] >> 56);
-        for (int q = prev + 1; q <= limb; ++q) s_lstart[q] = i;
-        if (i > 0 && (keys[i] >> 24) == (keys[i - 1] >> 24)) atomicOr(&s_flags, TFPD_FLAG_SCORE_TIE);
-    }
+    __syncthreads();
+    // exact-tie detection: equal (limb, score) neighbours
+    for (int i = tid + 1; i < cnt; i += kK3Threads)
+        if ((keys[i] >> 24) == (keys[i - 1] >> 24)) atomicOr(&s_flags, TFPD_FLAG_SCORE_TIE);
     __syncthreads();
 
     // ---- 2. greedy matching, one warp per limb (lane 0 walks; the walk is inherently serial) ----
@@ -137,166 +190,193 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
     // Fast path for the first kRegRowsMax rows: row r belongs to lane r & 31, slot r >> 5.  A limb only ever
     // looks at two columns of a row (its parts PA, PB) and updates PB, the score and the count, so per limb each
     // lane pulls its rows' PA / PB entries out of the smem table ONCE, keeps score and count in registers for the
-    // whole assembly, and a connection is then two compares per lane, a ballot and an update inside the owning
-    // lane -- no shared-memory round trip on the serial chain (the all-smem loop below spends ~900 cycles per
-    // connection on them) and, unlike a per-limb instantiation with statically indexed row registers, one small
-    // loop body that stays in the instruction cache.  When a 65th row is needed, the registers go back to the smem
-    // rows and the generic loop below continues from the same (limb, connection).
+    // whole assembly, and a connection is then two compares per lane and slot, a ballot and an update inside the
+    // owning lane -- no shared-memory round trip on the serial chain (the all-smem loop below spends ~900 cycles
+    // per connection on them) and, unlike a per-limb instantiation with statically indexed row registers, one
+    // small loop body that stays in the instruction cache.  When row kRegRowsMax+1 is needed, the registers go
+    // back to the smem rows and the generic loop below continues from the same (limb, connection).
     const float *pscore = s_pscore;
     const unsigned FULL = 0xffffffffu;
     int nrows = 0;
     bool row_overflow = false;
     int limb0 = kLimbs, k0 = 0;                       // where the generic loop resumes (kLimbs = nowhere)
     {
+        constexpr int S = kRegRowsMax / 32;
         const int reg_cap = min(min(ws.k3_reg_rows, kRegRowsMax), MR);
         // a row that does not exist yet reads as "no part anywhere": creating one (:172-180) is then 4 writes
-        for (int c = 0; c < kParts; ++c) {
-            if (lane < MR) rows[(size_t)c * MR + lane] = -1.0f;
-            if (lane + 32 < MR) rows[(size_t)c * MR + lane + 32] = -1.0f;
-        }
+        for (int c = 0; c < kParts; ++c)
+#pragma unroll
+            for (int q = 0; q < S; ++q)
+                if (lane + 32 * q < MR) rows[(size_t)c * MR + lane + 32 * q] = -1.0f;
         __syncwarp();
-        float sc0 = 0.f, sc1 = 0.f, cn0 = 0.f, cn1 = 0.f;            // columns 18 / 19 of this lane's two rows
-        const bool own0 = lane < MR, own1 = lane + 32 < MR;
+        float sc[S], cn[S];                                          // columns 18 / 19 of this lane's rows
+        bool own[S];
+#pragma unroll
+        for (int q = 0; q < S; ++q) {
+            sc[q] = cn[q] = 0.f;
+            own[q] = lane + 32 * q < MR;
+        }
+        // found == 2 in upstream mode on the smem rows (:153-165); true when the two rows were merged
+        auto merge_rows = [&](int r1, int r2, float cscore) -> bool {
+            float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
+            const bool both = (lane < kParts) && (rows[(size_t)lane * MR + r1] > 0.0f) &&
+                              (rows[(size_t)lane * MR + r2] > 0.0f);
+            if (__ballot_sync(FULL, both) != 0u) return false;
+            if (lane < kParts) {
+                float *cc = rows + (size_t)lane * MR;
+                cc[r1] = __fadd_rn(cc[r1], __fadd_rn(cc[r2], 1.0f));
+            } else if (lane == 18) {
+                col18[r1] = __fadd_rn(__fadd_rn(col18[r1], col18[r2]), cscore);
+            } else if (lane == 19) {
+                col19[r1] = __fadd_rn(col19[r1], col19[r2]);
+            }
+            __syncwarp();
+            // subset.erase(begin + r2); the vacated last row reads as "not there" again
+            for (int c = 0; c < 20; ++c) {
+                float *cc = rows + (size_t)c * MR;
+                float v[S];
+#pragma unroll
+                for (int q = 0; q < S; ++q) {
+                    const int r = lane + 32 * q;
+                    v[q] = 0.f;
+                    if (r >= r2 && r < nrows) v[q] = (r + 1 < nrows) ? cc[r + 1] : -1.0f;
+                }
+                __syncwarp();
+#pragma unroll
+                for (int q = 0; q < S; ++q) {
+                    const int r = lane + 32 * q;
+                    if (r >= r2 && r < nrows) cc[r] = v[q];
+                }
+            }
+            --nrows;
+            __syncwarp();
+            return true;
+        };
         for (int limb = 0; limb < kLimbs && limb0 == kLimbs; ++limb) {
             const int pa = c_limb_part[limb][0], pb = c_limb_part[limb][1];
             float *colA = rows + (size_t)pa * MR, *colB = rows + (size_t)pb * MR;
-            float a0 = own0 ? colA[lane] : -1.0f, a1 = own1 ? colA[lane + 32] : -1.0f;
-            float b0v = own0 ? colB[lane] : -1.0f, b1v = own1 ? colB[lane + 32] : -1.0f;
+            float av[S], bv[S];
+#pragma unroll
+            for (int q = 0; q < S; ++q) {
+                av[q] = own[q] ? colA[lane + 32 * q] : -1.0f;
+                bv[q] = own[q] ? colB[lane + 32 * q] : -1.0f;
+            }
             const int beg = s_lstart[limb], nconn = s_ccount[limb];
-            for (int k = 0; k < nconn; ++k) {
+            // one connection; NS = slots that can hold a row right now (instantiated for 1, 2 and S so that the
+            // common case -- at most 32 rows -- runs the shortest instruction chain).  Returns true to bail out.
+            auto step = [&](auto ns_tag, int k) -> bool {
+                constexpr int NS = decltype(ns_tag)::value;
                 const unsigned long long rec = keys[beg + k];
                 const int cid1 = (int)((rec >> 16) & 0xffffu), cid2 = (int)(rec & 0xffffu);
                 const float cscore = __uint_as_float((uint32_t)(rec >> 32));
                 const float f1 = (float)cid1, f2 = (float)cid2;
                 const float ps1 = pscore[cid1], ps2 = pscore[cid2];
-                const unsigned m0 = __ballot_sync(FULL, (lane < nrows) && (a0 == f1 || b0v == f2));     // :137
-                unsigned m1 = 0u;
-                if (nrows > 32) m1 = __ballot_sync(FULL, (lane + 32 < nrows) && (a1 == f1 || b1v == f2));
-                const int found = __popc(m0) + __popc(m1);
+                unsigned m[NS];
+                int found = 0;
+#pragma unroll
+                for (int q = 0; q < NS; ++q) {                                                          // :137
+                    m[q] = __ballot_sync(FULL, (lane + 32 * q < nrows) && (av[q] == f1 || bv[q] == f2));
+                    found += __popc(m[q]);
+                }
                 if (found == 0) {
                     if (limb < 17) {                                                            // :171-181
                         if (nrows >= reg_cap) {
                             if (nrows >= MR) {
                                 row_overflow = true;
-                                continue;
+                                return false;
                             }
                             limb0 = limb;               // continue in shared memory from this connection
                             k0 = k;
-                            break;
+                            return true;
                         }
-                        const float sc = __fadd_rn(__fadd_rn(ps1, ps2), cscore);
-                        if (lane == (nrows & 31)) {
-                            if (nrows < 32) {
-                                a0 = f1;
-                                b0v = f2;
-                                sc0 = sc;
-                                cn0 = 2.0f;
-                            } else {
-                                a1 = f1;
-                                b1v = f2;
-                                sc1 = sc;
-                                cn1 = 2.0f;
-                            }
+                        const float scn = __fadd_rn(__fadd_rn(ps1, ps2), cscore);
+                        // (selects, not indexed stores: the row arrays must stay in registers)
+                        const bool mine = lane == (nrows & 31);
+#pragma unroll
+                        for (int q = 0; q < S; ++q) {
+                            const bool wr = mine && (nrows >= 32 * q) && (nrows < 32 * q + 32);
+                            av[q] = wr ? f1 : av[q];
+                            bv[q] = wr ? f2 : bv[q];
+                            sc[q] = wr ? scn : sc[q];
+                            cn[q] = wr ? 2.0f : cn[q];
                         }
                         ++nrows;
                     }
                 } else if (found <= 2) {
-                    const int r1 = m0 ? (__ffs(m0) - 1) : (32 + __ffs(m1) - 1);
+                    // first (and second) matching row in row order
+                    int r1 = -1, r2 = -1;
+#pragma unroll
+                    for (int q = 0; q < NS; ++q) {
+                        unsigned mm = m[q];
+                        if (mm && r1 < 0) {
+                            r1 = 32 * q + __ffs(mm) - 1;
+                            mm &= mm - 1u;
+                        }
+                        if (mm && r1 >= 0 && r2 < 0) r2 = 32 * q + __ffs(mm) - 1;
+                    }
                     bool merged = false;
                     if (found == 2 && th.mode == TFPD_MODE_UPSTREAM) {
                         // :151-165, rare: done on the smem rows (one copy of the code), registers re-read after
-                        const unsigned rest0 = m0 & (m0 - 1u);
-                        const int r2 = (m0 == 0u) ? (32 + __ffs(m1 & (m1 - 1u)) - 1)
-                                                  : (rest0 ? (__ffs(rest0) - 1) : (32 + __ffs(m1) - 1));
                         float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
-                        if (lane < nrows) {
-                            colA[lane] = a0;
-                            colB[lane] = b0v;
-                            col18[lane] = sc0;
-                            col19[lane] = cn0;
-                        }
-                        if (lane + 32 < nrows) {
-                            colA[lane + 32] = a1;
-                            colB[lane + 32] = b1v;
-                            col18[lane + 32] = sc1;
-                            col19[lane + 32] = cn1;
-                        }
+#pragma unroll
+                        for (int q = 0; q < S; ++q)
+                            if (lane + 32 * q < nrows) {
+                                colA[lane + 32 * q] = av[q];
+                                colB[lane + 32 * q] = bv[q];
+                                col18[lane + 32 * q] = sc[q];
+                                col19[lane + 32 * q] = cn[q];
+                            }
                         __syncwarp();
-                        const bool both = (lane < kParts) && (rows[(size_t)lane * MR + r1] > 0.0f) &&
-                                          (rows[(size_t)lane * MR + r2] > 0.0f);
-                        merged = (__ballot_sync(FULL, both) == 0u);                    // :153-157
+                        merged = merge_rows(r1, r2, cscore);
                         if (merged) {
-                            if (lane < kParts) {
-                                float *cc = rows + (size_t)lane * MR;
-                                cc[r1] = __fadd_rn(cc[r1], __fadd_rn(cc[r2], 1.0f));
-                            } else if (lane == 18) {
-                                col18[r1] = __fadd_rn(__fadd_rn(col18[r1], col18[r2]), cscore);
-                            } else if (lane == 19) {
-                                col19[r1] = __fadd_rn(col19[r1], col19[r2]);
+#pragma unroll
+                            for (int q = 0; q < S; ++q) {
+                                av[q] = own[q] ? colA[lane + 32 * q] : -1.0f;
+                                bv[q] = own[q] ? colB[lane + 32 * q] : -1.0f;
+                                sc[q] = own[q] ? col18[lane + 32 * q] : 0.f;
+                                cn[q] = own[q] ? col19[lane + 32 * q] : 0.f;
                             }
-                            __syncwarp();
-                            // subset.erase(begin + r2); the vacated last row reads as "not there" again
-                            for (int c = 0; c < 20; ++c) {
-                                float *cc = rows + (size_t)c * MR;
-                                const int ra = lane, rb = lane + 32;
-                                float v0 = 0.f, v1 = 0.f;
-                                if (ra >= r2 && ra < nrows) v0 = (ra + 1 < nrows) ? cc[ra + 1] : -1.0f;
-                                if (rb >= r2 && rb < nrows) v1 = (rb + 1 < nrows) ? cc[rb + 1] : -1.0f;
-                                __syncwarp();
-                                if (ra >= r2 && ra < nrows) cc[ra] = v0;
-                                if (rb >= r2 && rb < nrows) cc[rb] = v1;
-                            }
-                            --nrows;
-                            __syncwarp();
-                            a0 = own0 ? colA[lane] : -1.0f;
-                            a1 = own1 ? colA[lane + 32] : -1.0f;
-                            b0v = own0 ? colB[lane] : -1.0f;
-                            b1v = own1 ? colB[lane + 32] : -1.0f;
-                            sc0 = own0 ? col18[lane] : 0.f;
-                            sc1 = own1 ? col18[lane + 32] : 0.f;
-                            cn0 = own0 ? col19[lane] : 0.f;
-                            cn1 = own1 ? col19[lane + 32] : 0.f;
                         }
                     }
-                    if (!merged && lane == (r1 & 31)) {                           // :144-149 / :166-170
-                        if (r1 < 32) {
-                            if (found == 2 || b0v != f2) {
-                                b0v = f2;
-                                cn0 = __fadd_rn(cn0, 1.0f);
-                                sc0 = __fadd_rn(sc0, __fadd_rn(ps2, cscore));
-                            }
-                        } else {
-                            if (found == 2 || b1v != f2) {
-                                b1v = f2;
-                                cn1 = __fadd_rn(cn1, 1.0f);
-                                sc1 = __fadd_rn(sc1, __fadd_rn(ps2, cscore));
-                            }
+                    if (!merged) {                                                // :144-149 / :166-170
+                        const bool mine = lane == (r1 & 31);
+                        const float add = __fadd_rn(ps2, cscore);
+#pragma unroll
+                        for (int q = 0; q < NS; ++q) {
+                            const bool wr = mine && (r1 >= 32 * q) && (r1 < 32 * q + 32) && (found == 2 || bv[q] != f2);
+                            bv[q] = wr ? f2 : bv[q];
+                            cn[q] = wr ? __fadd_rn(cn[q], 1.0f) : cn[q];
+                            sc[q] = wr ? __fadd_rn(sc[q], add) : sc[q];
                         }
                     }
                 } else {
                     if (lane == 0) atomicOr(&s_flags, TFPD_FLAG_FOUND_GT2);
                 }
+                return false;
+            };
+            for (int k = 0; k < nconn; ++k) {
+                bool bail;
+                if (nrows <= 32) bail = step(std::integral_constant<int, 1>(), k);
+                else if (nrows <= 64) bail = step(std::integral_constant<int, 2>(), k);
+                else bail = step(std::integral_constant<int, S>(), k);
+                if (bail) break;
             }
             // this limb's columns go back to the table (PA changes only where a row was created)
-            if (lane < nrows) {
-                colA[lane] = a0;
-                colB[lane] = b0v;
-            }
-            if (lane + 32 < nrows) {
-                colA[lane + 32] = a1;
-                colB[lane + 32] = b1v;
-            }
+#pragma unroll
+            for (int q = 0; q < S; ++q)
+                if (lane + 32 * q < nrows) {
+                    colA[lane + 32 * q] = av[q];
+                    colB[lane + 32 * q] = bv[q];
+                }
             __syncwarp();
         }
         float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
-        if (lane < nrows) {
-            col18[lane] = sc0;
-            col19[lane] = cn0;
-        }
-        if (lane + 32 < nrows) {
-            col18[lane + 32] = sc1;
-            col19[lane + 32] = cn1;
-        }
+#pragma unroll
+        for (int q = 0; q < S; ++q)
+            if (lane + 32 * q < nrows) {
+                col18[lane + 32 * q] = sc[q];
+                col19[lane + 32 * q] = cn[q];
+            }
         __syncwarp();
     }
     for (int limb = limb0; limb < kLimbs; ++limb) {
