@@ -187,9 +187,40 @@ def boxes_golden(est_mod):
           sum(1 for r in recs for b in r["boxes"] if b["upper"]), "upper-body boxes")
 
 
+def coco_golden(est_mod):
+    """Results of the reference's own output writers -- write_coco_json (tf_pose/eval.py:35-44) and
+    translate_op_top_coco (ariel_run.py:22-28) with the keypoint list of ariel_run.py:73-80 -- for the
+    same random humans, everything else those scripts import stubbed."""
+    names = ["common", "estimator", "networks", "pycocotools", "pycocotools.coco", "pycocotools.cocoeval", "tqdm",
+             "cv2", "tf_pose", "tf_pose.common", "tf_pose.estimator", "tf_pose.networks"]
+    stubs = {n: _Stub(n) for n in names}
+    ev = load_reference_module(os.path.join(REF, "tf_pose/eval.py"), "ref_eval", stubs)
+    ar = load_reference_module(os.path.join(REF, "ariel_run.py"), "ref_ariel_run", stubs)
+    recs = []
+    for hm in random_humans(est_mod, n=24, seed=23):
+        rec = {"parts": {str(k): [bp.x, bp.y, bp.score] for k, bp in hm.body_parts.items()}, "score": hm.score,
+               "sizes": []}
+        for (iw, ih) in ((432, 368), (1312, 736), (101, 37)):
+            kps = []
+            for i in range(18):        # ariel_run.py:76-80, verbatim semantics
+                if i in hm.body_parts.keys():
+                    kps += [hm.body_parts[i].x * iw, hm.body_parts[i].y * ih, hm.body_parts[i].score]
+                else:
+                    kps += [0, 0, 0]
+            rec["sizes"].append({"w": iw, "h": ih, "write_coco_json": ev.write_coco_json(hm, iw, ih),
+                                 "translate_op_top_coco": ar.translate_op_top_coco(kps)})
+        recs.append(rec)
+    with open(os.path.join(HERE, "coco_writers.json"), "w") as fh:
+        json.dump(recs, fh)
+    print("coco writers:", len(recs), "humans x 3 image sizes")
+
+
 def main():
     if len(sys.argv) > 1 and sys.argv[1] == "boxes":
         boxes_golden(reference_estimator("asbuilt"))
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "coco":
+        coco_golden(reference_estimator("asbuilt"))
         return
     k = reference_gauss_kernel()
     np.save(os.path.join(HERE, "gauss_kernel_25_3.npy"), k)
@@ -220,6 +251,7 @@ def main():
     with open(os.path.join(HERE, "synth_humans.json"), "w") as fh:
         json.dump({"toy": toy, "cases": cases}, fh)
     boxes_golden(est["asbuilt"])
+    coco_golden(est["asbuilt"])
 
 
 if __name__ == "__main__":

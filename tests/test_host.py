@@ -249,3 +249,56 @@ def test_gather_results_over_gloo(world, tmp_path):
     outs = [p.communicate(timeout=180)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), "\n".join(outs)
     assert "GATHER_OK" in outs[0]
+
+
+def test_coco_writers_match_reference_golden():
+    """tests/golden/coco_writers.json holds what the reference's own write_coco_json (tf_pose/eval.py:35-44)
+    and translate_op_top_coco (ariel_run.py:22-28) returned for random humans (make_golden.py coco)."""
+    import json
+    from tfpose_b200 import writers
+    recs = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "coco_writers.json")))
+    assert len(recs) >= 20
+    for i, rec in enumerate(recs):
+        hm = tp.Human([])
+        for k, (x, y, s) in rec["parts"].items():
+            hm.body_parts[int(k)] = tp.BodyPart('%d-%s' % (i, k), int(k), x, y, s)
+        hm.score = rec["score"]
+        for sz in rec["sizes"]:
+            assert writers.write_coco_json(hm, sz["w"], sz["h"]) == sz["write_coco_json"]
+            kps = writers.openpose_keypoints(hm, sz["w"], sz["h"])
+            assert writers.translate_op_to_coco(kps) == sz["translate_op_top_coco"]
+            item = writers.coco_result_item(hm, 7, sz["w"], sz["h"])
+            assert item == {"image_id": 7, "category_id": 1, "keypoints": sz["write_coco_json"], "score": rec["score"]}
+            a = writers.ariel_result_item(hm, "a.jpg", 3, sz["w"], sz["h"])
+            assert a["keypoints"] == sz["translate_op_top_coco"] and a["filename"] == "a.jpg" and a["image_id"] == 3
+
+
+def test_coco_items_from_table_equal_the_per_human_writer():
+    """The batch writer that reads the tfpd_human tables directly gives the same records as
+    write_coco_json over the Human objects built from the same tables."""
+    from tfpose_b200 import writers, _lib
+    from tfpose_b200.decoder import DecodeResult
+    rng = np.random.default_rng(5)
+    N, MH, H, W = 3, 6, 184, 216
+    info = np.zeros(N, _lib.INFO_DTYPE)
+    table = np.zeros((N, MH), _lib.HUMAN_DTYPE)
+    for i in range(N):
+        info["n_humans"][i] = rng.integers(0, MH + 1)
+        for j in range(int(info["n_humans"][i])):
+            present = rng.random(18) < 0.7
+            if j == 0:
+                present[:] = False                      # a human without parts is skipped (estimator.py:293)
+            table["cid"][i, j] = np.where(present, rng.integers(0, 300, 18), -1)
+            table["x"][i, j] = np.where(present, rng.integers(0, W, 18), -1)
+            table["y"][i, j] = np.where(present, rng.integers(0, H, 18), -1)
+            table["part_score"][i, j] = np.where(present, rng.random(18), 0).astype(np.float32)
+            table["score"][i, j] = rng.random()
+    res = DecodeResult(info, table, H, W)
+    sizes = [(432, 368), (640, 427), (101, 37)]
+    got = writers.coco_items_from_table(res, [10, 11, 12], sizes)
+    want = []
+    for i in range(N):
+        want += [writers.coco_result_item(h, 10 + i, *sizes[i]) for h in res.humans(i)]
+    assert got == want
+    kp = writers.table_to_keypoint_array(res, 1)
+    assert kp.shape == (int(info["n_humans"][1]), 18, 3)

@@ -10,6 +10,7 @@ from .common import CocoPart, CocoPairs, CocoPairsRender, CocoPairsNetwork, Coco
 from .humans import Human, BodyPart  # noqa: F401
 from .decoder import PoseDecoder, DecodeResult, upsample_size_for, humans_from_table  # noqa: F401
 from .estimator import PoseEstimator, TfPosePostProcessor  # noqa: F401
+from . import writers  # noqa: F401
 from ._lib import DecodeError, CapacityError, DecodeLibraryMissing  # noqa: F401
 
 __all__ = ["CocoPart", "CocoPairs", "CocoPairsRender", "CocoPairsNetwork", "CocoColors", "Human", "BodyPart",
