@@ -1,7 +1,8 @@
 // k2_limbs.cu -- K2: PAF line-integral scoring of every (peak a, peak b) pair of every limb,
 // pafprocess.cpp:48-94 with get_paf_vectors (:216-233) and roundpaf (:235-237).
 //
-// A warp scores three candidate pairs at a time: 10 lanes per pair, one lane per PAF sample
+// A warp takes 30 candidate pairs per pass: pair-level values are computed with one lane per pair, then
+// three pairs at a time are scored with 10 lanes per pair, one lane per PAF sample
 // (STEP_PAF = 10, pafprocess.h:13).  The ten sample scores of a pair are then summed in the
 // reference's i = 0..9 order by every lane of the group (shuffle broadcast), so the float32
 // sum is bit-identical to the sequential C++ loop.  Arithmetic follows the C++ promotion
@@ -18,16 +19,8 @@ namespace tfpd {
 namespace {
 
 constexpr int kK2Threads = 256;
-constexpr int kPairsPerWarp = 3;
-constexpr int kUnroll = 2;                 // candidate triples in flight per warp (gather latency overlap)
-
-struct PairSetup {
-    int limb, a, b;
-    float vx, vy, norm;
-    bool valid, skip;
-    const float *pp;        // address of the PAF pixel this lane samples
-    int ch0, ch1;
-};
+constexpr int kPairsPerWarp = 3;           // pairs scored at once: 10 lanes (PAF samples) each
+constexpr int kPairsPerPass = 30;          // pairs set up at once: one lane each
 
 __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSource src, size_t frame_stride,
                                                           Thresholds th) {
@@ -60,27 +53,36 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
     __syncthreads();
     const int total = s_tstart[kLimbs];
     const float *paf = src.base + (size_t)n * frame_stride;
+    const unsigned FULL = 0xffffffffu;
 
-    const int slot = lane / kStepPaf;           // 0..2 ; lanes 30,31 -> 3 (idle)
+    const int slot = lane / kStepPaf;           // 0..2 ; lanes 30,31 -> 3 (idle in the scoring phase)
     const int i = lane - slot * kStepPaf;       // sample index 0..9
     const int group_base = slot * kStepPaf;
+    const unsigned group_mask = (slot < kPairsPerWarp) ? (0x3ffu << group_base) : 0u;
     const int warps_total = gridDim.x * (kK2Threads / 32);
-    const int stride = warps_total * kPairsPerWarp;
 
-    auto setup = [&](int q0) -> PairSetup {
-        PairSetup ps;
-        const int q = q0 + slot;
-        ps.valid = (slot < kPairsPerWarp) && (q < total);
-        ps.limb = 0;
-        ps.a = ps.b = 0;
-        ps.vx = ps.vy = 0.f;
-        ps.norm = 1.f;
-        ps.skip = true;
-        ps.pp = paf;
-        ps.ch0 = ps.ch1 = 0;
-        if (ps.valid) {
-            int limb = 0;
+    // Two phases per pass of 30 candidate pairs, because the per-PAIR arithmetic (limb lookup, index split,
+    // sqrt, four IEEE divisions) was 3/4 of the instructions when every one of a pair's 10 sample lanes repeated
+    // it (ncu: issue-bound, 427 warp instructions per pair triple):
+    //   setup    lane p owns pair base+p and computes the pair-level values once;
+    //   scoring  ten sub-steps, each takes three of the pairs, 10 lanes per pair (one per PAF sample); the
+    //            pair-level values come by shuffle from the owning lane, the gathers of sub-step t+1 are issued
+    //            before sub-step t is reduced.
+    // pairs per pass: 30 when there is enough work, fewer (a multiple of 3) when the frame has so few pairs
+    // that spreading them over all warps shortens the serial chain of sub-steps
+    int per = (total + warps_total - 1) / warps_total;
+    per = min(kPairsPerPass, max(kPairsPerWarp, (per + kPairsPerWarp - 1) / kPairsPerWarp * kPairsPerWarp));
+    int limb_hint = 0;                          // pairs are visited in increasing order: resume the limb search
+    for (int base = (blockIdx.x * (kK2Threads / 32) + warp) * per; base < total; base += warps_total * per) {
+        // ---- setup (lane = pair) ----
+        const int q = base + lane;
+        const bool pvalid = (lane < per) && (q < total);
+        int xy1 = 0, lab = 0, meta = 0;         // x1 | y1 << 16 ; limb << 24 | a << 12 | b ; chan0 | ok << 8
+        float vx = 0.f, vy = 0.f, norm = 1.f, stepx = 0.f, stepy = 0.f;
+        if (pvalid) {
+            int limb = limb_hint;
             while (q >= s_tstart[limb + 1]) ++limb;
+            limb_hint = limb;
             const int pa = c_limb_part[limb][0], pb = c_limb_part[limb][1];
             const int nb = s_first[pb + 1] - s_first[pb];
             const int r = q - s_tstart[limb];
@@ -88,77 +90,82 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
             const int b = r - a * nb;
             const int ia = s_first[pa] + a, ib = s_first[pb] + b;
             const int x1 = s_px[ia], y1 = s_py[ia], x2 = s_px[ib], y2 = s_py[ib];
-            float vx = (float)(x2 - x1);                                              // :63-64
-            float vy = (float)(y2 - y1);
-            const float norm = __fsqrt_rn(__fadd_rn(__fmul_rn(vx, vx), __fmul_rn(vy, vy))); // :65
-            ps.limb = limb;
-            ps.a = a;
-            ps.b = b;
-            ps.norm = norm;
-            ps.skip = (norm < 1e-12f);                                             // :66 (norm is 0 or >= 1)
-            if (!ps.skip) {
-                ps.vx = __fdiv_rn(vx, norm);                                       // :67-68
-                ps.vy = __fdiv_rn(vy, norm);
-                const float stepx = __fdiv_rn((float)(x2 - x1), (float)kStepPaf);   // :219-220
-                const float stepy = __fdiv_rn((float)(y2 - y1), (float)kStepPaf);
+            const float dx = (float)(x2 - x1), dy = (float)(y2 - y1);                     // :63-64
+            norm = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));           // :65
+            const bool ok = !(norm < 1e-12f);                                             // :66 (norm is 0 or >= 1)
+            if (ok) {
+                vx = __fdiv_rn(dx, norm);                                                 // :67-68
+                vy = __fdiv_rn(dy, norm);
+                stepx = __fdiv_rn(dx, (float)kStepPaf);                                   // :219-220
+                stepy = __fdiv_rn(dy, (float)kStepPaf);
+            }
+            xy1 = (x1 & 0xffff) | (y1 << 16);
+            lab = (limb << 24) | (a << 12) | b;
+            meta = c_limb_chan[limb][0] | (ok ? 0x100 : 0);
+        }
+        const int npass = min(per, total - base);                                         // warp-uniform
+        const int nsub = (npass + kPairsPerWarp - 1) / kPairsPerWarp;
+
+        // ---- scoring (10 lanes per pair) ----
+        auto fetch = [&](int t, float &o_vx, float &o_vy, float &o_pvx, float &o_pvy, bool &o_ok) {
+            const int owner = min(kPairsPerWarp * t + slot, 31);
+            const int g_xy = __shfl_sync(FULL, xy1, owner);
+            const int g_meta = __shfl_sync(FULL, meta, owner);
+            const float g_sx = __shfl_sync(FULL, stepx, owner), g_sy = __shfl_sync(FULL, stepy, owner);
+            o_vx = __shfl_sync(FULL, vx, owner);
+            o_vy = __shfl_sync(FULL, vy, owner);
+            o_ok = (slot < kPairsPerWarp) && (kPairsPerWarp * t + slot < npass) && (g_meta & 0x100);
+            o_pvx = o_pvy = 0.f;
+            if (o_ok) {
+                const int x1 = (int)(int16_t)(g_xy & 0xffff), y1 = g_xy >> 16;
                 // roundpaf(peak1.x + i*STEP_X): float product, float sum, then +0.5 in double (:223-224,:235-237)
-                const float fx = __fadd_rn((float)x1, __fmul_rn((float)i, stepx));
-                const float fy = __fadd_rn((float)y1, __fmul_rn((float)i, stepy));
+                const float fx = __fadd_rn((float)x1, __fmul_rn((float)i, g_sx));
+                const float fy = __fadd_rn((float)y1, __fmul_rn((float)i, g_sy));
                 const int lx = (int)((double)fx + 0.5);
                 const int ly = (int)((double)fy + 0.5);
-                ps.pp = paf + ((size_t)(ly >> src.shift) * src.cols + (lx >> src.shift)) * src.chan + src.chan_off;
-                ps.ch0 = c_limb_chan[limb][0];
-                ps.ch1 = c_limb_chan[limb][1];
+                const float *pp = paf + ((size_t)(ly >> src.shift) * src.cols + (lx >> src.shift)) * src.chan +
+                                  src.chan_off + (g_meta & 0xff);
+                o_pvx = __ldg(pp);              // the two PAF channels of a limb are adjacent (pafprocess.h:20-24)
+                o_pvy = __ldg(pp + 1);
             }
-        }
-        return ps;
-    };
-
-    for (int q0 = (blockIdx.x * (kK2Threads / 32) + warp) * kPairsPerWarp; q0 < total; q0 += stride * kUnroll) {
-        PairSetup ps[kUnroll];
-        float pvx[kUnroll], pvy[kUnroll];
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u) ps[u] = setup(q0 + u * stride);       // q >= total -> invalid
-        // all gathers of the kUnroll triples are issued before any is consumed
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-            pvx[u] = pvy[u] = 0.f;
-            if (ps[u].valid && !ps[u].skip) {
-                pvx[u] = __ldg(ps[u].pp + ps[u].ch0);
-                pvy[u] = __ldg(ps[u].pp + ps[u].ch1);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-            if (q0 + u * stride >= total) break;                                   // warp-uniform
-            float s = 0.f;
-            if (ps[u].valid && !ps[u].skip)
-                s = __fadd_rn(__fmul_rn(ps[u].vx, pvx[u]), __fmul_rn(ps[u].vy, pvy[u]));         // :77
+        };
+        float c_vx, c_vy, c_pvx, c_pvy;
+        bool c_ok;
+        fetch(0, c_vx, c_vy, c_pvx, c_pvy, c_ok);
+        for (int t = 0; t < nsub; ++t) {
+            float n_vx = 0.f, n_vy = 0.f, n_pvx = 0.f, n_pvy = 0.f;
+            bool n_ok = false;
+            if (t + 1 < nsub) fetch(t + 1, n_vx, n_vy, n_pvx, n_pvy, n_ok);
+            const float s = c_ok ? __fadd_rn(__fmul_rn(c_vx, c_pvx), __fmul_rn(c_vy, c_pvy)) : 0.f;   // :77
             // scores += score, i = 0..9, in order (:78); criterion1 counts score > THRESH_VECTOR_SCORE (:80)
             float total_s = 0.0f;
-            int hits = 0;
 #pragma unroll
-            for (int k = 0; k < kStepPaf; ++k) {
-                const float sk = __shfl_sync(0xffffffffu, s, (group_base + k) & 31);
-                total_s = __fadd_rn(total_s, sk);
-                hits += (sk > th.vector_score) ? 1 : 0;
-            }
-            if (ps[u].valid && !ps[u].skip && i == 0) {
+            for (int k = 0; k < kStepPaf; ++k) total_s = __fadd_rn(total_s, __shfl_sync(FULL, s, (group_base + k) & 31));
+            const int hits = __popc(__ballot_sync(FULL, s > th.vector_score) & group_mask);
+            const int owner = min(kPairsPerWarp * t + slot, 31);
+            const float g_norm = __shfl_sync(FULL, norm, owner);
+            const int g_lab = __shfl_sync(FULL, lab, owner);
+            if (c_ok && i == 0 && hits > th.vector_cnt1) {                        // first half of :85
                 // float criterion2 = scores / STEP_PAF + min(0.0, 0.5 * h1 / norm - 1.0);   (:83)
-                const double pen = 0.5 * (double)src.H / (double)ps[u].norm - 1.0;
+                const double pen = 0.5 * (double)src.H / (double)g_norm - 1.0;
                 const double d = (double)__fdiv_rn(total_s, (float)kStepPaf) + (pen < 0.0 ? pen : 0.0);
                 const float crit2 = (float)d;
-                if (hits > th.vector_cnt1 && crit2 > 0.0f) {                       // :85
+                if (crit2 > 0.0f) {                                                // second half of :85
                     int idx = atomicAdd(&ws.counters[n].n_cand, 1);
                     if (idx < ws.max_cands) {
                         // ascending key order == (limb asc, score desc, idx1 asc, idx2 asc)
-                        unsigned long long key = ((unsigned long long)ps[u].limb << 56) |
+                        unsigned long long key = ((unsigned long long)(g_lab >> 24) << 56) |
                                                  ((unsigned long long)(0xffffffffu - __float_as_uint(crit2)) << 24) |
-                                                 ((unsigned long long)ps[u].a << 12) | (unsigned long long)ps[u].b;
+                                                 (unsigned long long)(g_lab & 0xffffff);
                         ws.cand_key[(size_t)n * ws.max_cands + idx] = key;
                     }
                 }
             }
+            c_vx = n_vx;
+            c_vy = n_vy;
+            c_pvx = n_pvx;
+            c_pvy = n_pvy;
+            c_ok = n_ok;
         }
     }
 }
