@@ -231,7 +231,8 @@ def test_assembly_register_and_shared_memory_paths_agree(cuda, monkeypatch, mode
     """K3 keeps the first 128 subset rows in registers and continues in shared memory beyond that
     (pafprocess.cpp:127-183 either way).  TFPD_K3_REGROWS lowers the switch-over point: 0 = all in shared
     memory, 3 / 17 / 25 = switch in the middle of a limb; TFPD_K3_WARPSORT=0 forces the frame-wide sort instead
-    of the per-limb warp sorts.  Every variant must give the same tables as the default, on sparse and on
+    of the per-limb warp sorts; TFPD_K3_PARALLEL=0 turns the whole-limb assembly steps off (every connection
+    one by one).  Every variant must give the same tables as the default, on sparse and on
     crowded frames."""
     import torch
     from helpers import table_tuples
@@ -251,7 +252,7 @@ def test_assembly_register_and_shared_memory_paths_agree(cuda, monkeypatch, mode
     want = [run(x) for x in xs]
     assert max(int(w[1]["n_rows"].max()) for w in want) > 25, "the crowded frames must exceed the test's switch-over points"
     for var, val in (("TFPD_K3_REGROWS", "0"), ("TFPD_K3_REGROWS", "3"), ("TFPD_K3_REGROWS", "17"),
-                     ("TFPD_K3_REGROWS", "25"), ("TFPD_K3_WARPSORT", "0")):
+                     ("TFPD_K3_REGROWS", "25"), ("TFPD_K3_WARPSORT", "0"), ("TFPD_K3_PARALLEL", "0")):
         monkeypatch.setenv(var, val)
         for x, (tabs, info) in zip(xs, want):
             got_tabs, got_info = run(x)

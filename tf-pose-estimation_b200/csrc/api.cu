@@ -276,6 +276,8 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     w.max_humans = cfg->max_humans;
     w.k3_reg_rows = 128;
     w.k3_warp_sort_max = 1024;
+    w.k3_parallel_limbs = 1;
+    if (const char *e = getenv("TFPD_K3_PARALLEL")) w.k3_parallel_limbs = atoi(e) != 0;
     if (const char *e = getenv("TFPD_K3_WARPSORT")) w.k3_warp_sort_max = atoi(e);
     if (const char *e = getenv("TFPD_K3_REGROWS")) w.k3_reg_rows = atoi(e) < 0 ? 0 : atoi(e);
     const size_t N = (size_t)cfg->max_batch, MP = (size_t)w.max_peaks, MC = (size_t)w.max_cands;

@@ -354,7 +354,81 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
                 }
                 return false;
             };
-            for (int k = 0; k < nconn; ++k) {
+            // Whole-limb step.  Within one limb the greedy matching made every cid1 and every cid2 unique, so
+            // if, in the state at the start of a pass of <= 32 connections, (1) no row holds any of the pass's
+            // cid2 at PB and (2) no cid1 is held by more than one row at PA, then the connections cannot see each
+            // other's effects: found is 0 or 1 for each, a matched row is matched by exactly one connection and
+            // takes its update, and the unmatched ones append rows in connection order -- exactly what the
+            // sequential loop (:134-183) would do, without its serial chain.  Limbs 0..16 normally qualify (their PB
+            // column is still empty); anything else, and the redundant ear-shoulder limbs 17/18, go one by one.
+            int kpar = 0;
+            while (limb < 17 && ws.k3_parallel_limbs && kpar < nconn) {
+                const int np = min(32, nconn - kpar);
+                float cf1 = -2.0f, cf2 = -2.0f, cadd = 0.f, cnew = 0.f;
+                if (lane < np) {
+                    const unsigned long long rec = keys[beg + kpar + lane];
+                    const int cid1 = (int)((rec >> 16) & 0xffffu), cid2 = (int)(rec & 0xffffu);
+                    const float cscore = __uint_as_float((uint32_t)(rec >> 32));
+                    cf1 = (float)cid1;
+                    cf2 = (float)cid2;
+                    cadd = __fadd_rn(pscore[cid2], cscore);                                     // :147 / :169
+                    cnew = __fadd_rn(__fadd_rn(pscore[cid1], pscore[cid2]), cscore);            // :176-178
+                }
+                unsigned mybits[S];
+                bool anyb = false;
+#pragma unroll
+                for (int q = 0; q < S; ++q) mybits[q] = 0u;
+                for (int j = 0; j < np; ++j) {
+                    const float f1j = __shfl_sync(FULL, cf1, j), f2j = __shfl_sync(FULL, cf2, j);
+#pragma unroll
+                    for (int q = 0; q < S; ++q) {
+                        const bool live = lane + 32 * q < nrows;
+                        mybits[q] |= (live && av[q] == f1j) ? (1u << j) : 0u;
+                        anyb = anyb || (live && bv[q] == f2j);
+                    }
+                }
+                unsigned allbits = 0u;
+                int nmatch = 0;
+#pragma unroll
+                for (int q = 0; q < S; ++q) {
+                    allbits |= mybits[q];
+                    nmatch += __popc(mybits[q]);
+                }
+                const unsigned foundmask = __reduce_or_sync(FULL, allbits);
+                const int total_matches = __reduce_add_sync(FULL, nmatch);
+                const unsigned passmask = (np == 32) ? 0xffffffffu : ((1u << np) - 1u);
+                const unsigned unfound = ~foundmask & passmask;
+                const int nnew = __popc(unfound);
+                const bool bad = __any_sync(FULL, anyb) || (total_matches != __popc(foundmask)) ||
+                                 (nrows + nnew > reg_cap);
+                if (bad) break;                         // this pass (and the rest of the limb) one by one
+                // matched rows take their connection's update (:144-149); a row matches at most one connection
+#pragma unroll
+                for (int q = 0; q < S; ++q) {
+                    const int kk = mybits[q] ? (__ffs(mybits[q]) - 1) : 0;
+                    const float g2 = __shfl_sync(FULL, cf2, kk), gadd = __shfl_sync(FULL, cadd, kk);
+                    const bool wr = mybits[q] != 0u;
+                    bv[q] = wr ? g2 : bv[q];
+                    cn[q] = wr ? __fadd_rn(cn[q], 1.0f) : cn[q];
+                    sc[q] = wr ? __fadd_rn(sc[q], gadd) : sc[q];
+                }
+                // unmatched connections append rows in connection order (:171-181)
+#pragma unroll
+                for (int q = 0; q < S; ++q) {
+                    const int j = 32 * q + lane - nrows;            // rank of the new row this lane/slot would hold
+                    const bool wr = j >= 0 && j < nnew;
+                    const int srcl = wr ? (int)__fns(unfound, 0, j + 1) : 0;
+                    const float n1 = __shfl_sync(FULL, cf1, srcl), n2 = __shfl_sync(FULL, cf2, srcl);
+                    const float ns = __shfl_sync(FULL, cnew, srcl);
+                    av[q] = wr ? n1 : av[q];
+                    bv[q] = wr ? n2 : bv[q];
+                    sc[q] = wr ? ns : sc[q];
+                    cn[q] = wr ? 2.0f : cn[q];
+                }
+                nrows += nnew;
+                kpar += np;
+            }
+            for (int k = kpar; k < nconn; ++k) {
                 bool bail;
                 if (nrows <= 32) bail = step(std::integral_constant<int, 1>(), k);
                 else if (nrows <= 64) bail = step(std::integral_constant<int, 2>(), k);
