@@ -345,8 +345,10 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     if (const char *e = getenv("TFPD_K1_ROLES")) ctx->k1_roles = atoi(e);
     if (const char *e = getenv("TFPD_K1_PR")) ctx->k1_pr = atoi(e);
     if (const char *e = getenv("TFPD_K1_TIMES"))
-        if (atoi(e) && cudaMalloc((void **)&ctx->d_k1_times, 1024 * 4 * 8) == cudaSuccess)
+        if (atoi(e) && cudaMalloc((void **)&ctx->d_k1_times, 1024 * 4 * 8) == cudaSuccess) {
             cudaMemset(ctx->d_k1_times, 0, 1024 * 4 * 8);
+            ctx->ws.dbg_times = ctx->d_k1_times;
+        }
     *out = ctx;
     return TFPD_OK;
 }

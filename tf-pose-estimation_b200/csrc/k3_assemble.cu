@@ -51,8 +51,10 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
 
     __shared__ int s_lcount[kLimbs], s_lfill[kLimbs];
     __shared__ int s_maxseg;
+    __shared__ float s_stage[3][kRegRowsMax];   // new subset rows on their way from connection lanes to row lanes
 
     const int n = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (ws.dbg_times && tid == 0 && n < 64) ws.dbg_times[2048 + n * 8 + 0] = clock64();
     const int MR = ws.max_rows;
     const int raw = ws.counters[n].n_cand;
     const int cnt = min(raw, ws.max_cands);
@@ -71,6 +73,7 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
         }
     }
     __syncthreads();
+    if (ws.dbg_times && tid == 0 && n < 64) ws.dbg_times[2048 + n * 8 + 1] = clock64();
 
     // ---- 1. per-limb ordering ----
     // The key's top byte is the limb, so the frame-wide order is: limb segments, each sorted.  Bucket the
@@ -96,6 +99,7 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
         keys[s_lstart[limb] + atomicAdd(&s_lfill[limb], 1)] = key;
     }
     __syncthreads();
+    if (ws.dbg_times && tid == 0 && n < 64) ws.dbg_times[2048 + n * 8 + 2] = clock64();
     if (s_maxseg <= min(kWarpSortMax, ws.k3_warp_sort_max)) {
         // bitonic network with a mirrored first stage per block: every comparator puts the smaller key at the
         // lower index, so the (virtual) +inf padding beyond the segment never moves and is simply skipped
@@ -146,6 +150,7 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
         }
     }
     __syncthreads();
+    if (ws.dbg_times && tid == 0 && n < 64) ws.dbg_times[2048 + n * 8 + 3] = clock64();
     // exact-tie detection: equal (limb, score) neighbours
     for (int i = tid + 1; i < cnt; i += kK3Threads)
         if ((keys[i] >> 24) == (keys[i - 1] >> 24)) atomicOr(&s_flags, TFPD_FLAG_SCORE_TIE);
@@ -180,6 +185,7 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
         s_ccount[limb] = nconn;
     }
     __syncthreads();
+    if (ws.dbg_times && tid == 0 && n < 64) ws.dbg_times[2048 + n * 8 + 4] = clock64();
     if (tid < kLimbs) {
         ws.conn_start[n * 20 + tid] = s_lstart[tid];
         ws.conn_count[n * 20 + tid] = s_ccount[tid];
@@ -362,8 +368,9 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
             // sequential loop (:134-183) would do, without its serial chain.  Limbs 0..16 normally qualify (their PB
             // column is still empty); anything else, and the redundant ear-shoulder limbs 17/18, go one by one.
             int kpar = 0;
-            while (limb < 17 && ws.k3_parallel_limbs && kpar < nconn) {
-                const int np = min(32, nconn - kpar);
+            // one pass of <= 32 connections over NS row slots; false = conditions not met, nothing changed
+            auto limb_pass = [&](auto ns_tag, int np) -> bool {
+                constexpr int NS = decltype(ns_tag)::value;
                 float cf1 = -2.0f, cf2 = -2.0f, cadd = 0.f, cnew = 0.f;
                 if (lane < np) {
                     const unsigned long long rec = keys[beg + kpar + lane];
@@ -374,14 +381,14 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
                     cadd = __fadd_rn(pscore[cid2], cscore);                                     // :147 / :169
                     cnew = __fadd_rn(__fadd_rn(pscore[cid1], pscore[cid2]), cscore);            // :176-178
                 }
-                unsigned mybits[S];
+                unsigned mybits[NS];
                 bool anyb = false;
 #pragma unroll
-                for (int q = 0; q < S; ++q) mybits[q] = 0u;
+                for (int q = 0; q < NS; ++q) mybits[q] = 0u;
                 for (int j = 0; j < np; ++j) {
                     const float f1j = __shfl_sync(FULL, cf1, j), f2j = __shfl_sync(FULL, cf2, j);
 #pragma unroll
-                    for (int q = 0; q < S; ++q) {
+                    for (int q = 0; q < NS; ++q) {
                         const bool live = lane + 32 * q < nrows;
                         mybits[q] |= (live && av[q] == f1j) ? (1u << j) : 0u;
                         anyb = anyb || (live && bv[q] == f2j);
@@ -390,7 +397,7 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
                 unsigned allbits = 0u;
                 int nmatch = 0;
 #pragma unroll
-                for (int q = 0; q < S; ++q) {
+                for (int q = 0; q < NS; ++q) {
                     allbits |= mybits[q];
                     nmatch += __popc(mybits[q]);
                 }
@@ -399,12 +406,12 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
                 const unsigned passmask = (np == 32) ? 0xffffffffu : ((1u << np) - 1u);
                 const unsigned unfound = ~foundmask & passmask;
                 const int nnew = __popc(unfound);
-                const bool bad = __any_sync(FULL, anyb) || (total_matches != __popc(foundmask)) ||
-                                 (nrows + nnew > reg_cap);
-                if (bad) break;                         // this pass (and the rest of the limb) one by one
+                if (__any_sync(FULL, anyb) || (total_matches != __popc(foundmask)) || (nrows + nnew > reg_cap) ||
+                    (nrows + nnew > 32 * NS))
+                    return false;
                 // matched rows take their connection's update (:144-149); a row matches at most one connection
 #pragma unroll
-                for (int q = 0; q < S; ++q) {
+                for (int q = 0; q < NS; ++q) {
                     const int kk = mybits[q] ? (__ffs(mybits[q]) - 1) : 0;
                     const float g2 = __shfl_sync(FULL, cf2, kk), gadd = __shfl_sync(FULL, cadd, kk);
                     const bool wr = mybits[q] != 0u;
@@ -412,20 +419,37 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
                     cn[q] = wr ? __fadd_rn(cn[q], 1.0f) : cn[q];
                     sc[q] = wr ? __fadd_rn(sc[q], gadd) : sc[q];
                 }
-                // unmatched connections append rows in connection order (:171-181)
+                // unmatched connections append rows in connection order (:171-181): each posts its row at its
+                // rank, the lane that owns that row index picks it up
+                if (nnew) {
+                    if ((unfound >> lane) & 1u) {
+                        const int idx = nrows + __popc(unfound & ((1u << lane) - 1u));
+                        s_stage[0][idx] = cf1;
+                        s_stage[1][idx] = cf2;
+                        s_stage[2][idx] = cnew;
+                    }
+                    __syncwarp();
 #pragma unroll
-                for (int q = 0; q < S; ++q) {
-                    const int j = 32 * q + lane - nrows;            // rank of the new row this lane/slot would hold
-                    const bool wr = j >= 0 && j < nnew;
-                    const int srcl = wr ? (int)__fns(unfound, 0, j + 1) : 0;
-                    const float n1 = __shfl_sync(FULL, cf1, srcl), n2 = __shfl_sync(FULL, cf2, srcl);
-                    const float ns = __shfl_sync(FULL, cnew, srcl);
-                    av[q] = wr ? n1 : av[q];
-                    bv[q] = wr ? n2 : bv[q];
-                    sc[q] = wr ? ns : sc[q];
-                    cn[q] = wr ? 2.0f : cn[q];
+                    for (int q = 0; q < NS; ++q) {
+                        const int idx = 32 * q + lane;
+                        const bool wr = idx >= nrows && idx < nrows + nnew;
+                        av[q] = wr ? s_stage[0][idx] : av[q];
+                        bv[q] = wr ? s_stage[1][idx] : bv[q];
+                        sc[q] = wr ? s_stage[2][idx] : sc[q];
+                        cn[q] = wr ? 2.0f : cn[q];
+                    }
+                    __syncwarp();
+                    nrows += nnew;
                 }
-                nrows += nnew;
+                return true;
+            };
+            while (limb < 17 && ws.k3_parallel_limbs && kpar < nconn) {
+                const int np = min(32, nconn - kpar);
+                bool ok;
+                if (nrows + np <= 32) ok = limb_pass(std::integral_constant<int, 1>(), np);
+                else if (nrows + np <= 64) ok = limb_pass(std::integral_constant<int, 2>(), np);
+                else ok = limb_pass(std::integral_constant<int, S>(), np);
+                if (!ok) break;                         // this pass (and the rest of the limb) one by one
                 kpar += np;
             }
             for (int k = kpar; k < nconn; ++k) {
@@ -542,6 +566,7 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
         }
     }
 
+    if (ws.dbg_times && tid == 0 && n < 64) ws.dbg_times[2048 + n * 8 + 5] = clock64();
     // ---- 4. filter (:185-189) + getter view ----
     const float *col18 = rows + 18 * (size_t)MR, *col19 = rows + 19 * (size_t)MR;
     const int16_t *pkx = s_pkx, *pky = s_pky;
@@ -584,6 +609,7 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
         ws.info[n].n_cands = cnt;
         ws.info[n].n_rows = nrows;
         ws.info[n].flags = flags;
+        if (ws.dbg_times && n < 64) ws.dbg_times[2048 + n * 8 + 6] = clock64();
     }
 }
 
