@@ -171,6 +171,15 @@ TFPD_API int tfpd_get_part_x(tfpd_ctx *ctx, int cid);
 TFPD_API int tfpd_get_part_y(tfpd_ctx *ctx, int cid);
 TFPD_API float tfpd_get_part_score(tfpd_ctx *ctx, int cid);
 
+/* Tuning options, by name (unknown name or out-of-range value -> TFPD_ERR_INVALID):
+ *   "k1_ctas"      CTAs of the fused upsample/smoother/NMS kernel; 0 = one per SM (default).  The kernel is
+ *                  HBM-bound, so with several contexts in flight on different streams a smaller grid (128 of
+ *                  148 SMs) leaves SMs on which the latency-bound scoring / assembly kernels of the previous
+ *                  batch run concurrently.
+ *   "host_chunks"  frame chunks tfpd_decode_host pipelines H2D / decode / D2H over; 0 = automatic.
+ *   "k1_l2"        bit 0: prefetch the input into L2 up front, bit 1: evict-first stores (default 2).  */
+TFPD_API int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value);
+
 /* Introspection used by the tests and the bench. */
 TFPD_API int tfpd_version(void);
 /* 25-tap separable factor and polyphase weights the kernels use (float64 -> float32):

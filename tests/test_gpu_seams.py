@@ -290,3 +290,27 @@ def test_decode_host_chunk_pipelining_is_invisible(cuda, monkeypatch):
         outs.append([table_tuples(r, i) for i in range(7)] + [r.info.tobytes()])
         dec.close()
     assert outs[0] == outs[1]
+
+
+def test_tuning_options_do_not_change_results(cuda):
+    """tfpd_set_option: any grid size of the fused map kernel / L2 knob gives the same maps and tables;
+    unknown names and out-of-range values are rejected."""
+    import torch
+    from helpers import table_tuples
+    x = synth.synth_batch(6, 46, 54, config_id=2, first_frame=700)
+    xd = torch.from_numpy(x).cuda()
+    dec = tp.PoseDecoder(max_batch=6, max_upsample=(184, 216))
+    outs = []
+    for name, val in (("k1_ctas", 0), ("k1_ctas", 128), ("k1_ctas", 7), ("k1_l2", 0), ("k1_l2", 3)):
+        dec.set_option(name, val)
+        dense = tuple(torch.full((6, 184, 216, c), 3.0, device="cuda") for c in (19, 38, 19))
+        res = dec.decode(xd, (184, 216), dense=dense)
+        outs.append(([table_tuples(res, i) for i in range(6)], res.info.tobytes(), [t.cpu().numpy() for t in dense]))
+    for tabs, info, maps in outs[1:]:
+        assert tabs == outs[0][0] and info == outs[0][1]
+        assert all(np.array_equal(a, b) for a, b in zip(maps, outs[0][2]))
+    with pytest.raises(tp.DecodeError):
+        dec.set_option("no_such_option", 1)
+    with pytest.raises(tp.DecodeError):
+        dec.set_option("k1_ctas", 100000)
+    dec.close()

@@ -82,6 +82,7 @@ SIGNATURES = {
     "tfpd_set_profiling": (_I, [_P, _I]),
     "tfpd_last_stage_ms": (_I, [_P, C.POINTER(C.c_float * 4)]),
     "tfpd_debug_k1_times": (_I, [_P, _P, _I]),
+    "tfpd_set_option": (_I, [_P, C.c_char_p, _I]),
 }
 
 _lib = None

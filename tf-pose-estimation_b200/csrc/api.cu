@@ -55,6 +55,7 @@ struct tfpd_ctx {
     std::vector<cudaEvent_t> ev_chunk;  // 2 per chunk: input landed / chunk decoded
     int host_chunks = 0;                // 0 = automatic (TFPD_HOST_CHUNKS overrides: tuning knob)
     int k1_pr = 0;                      // TFPD_K1_PR
+    int k1_grid = 0;                    // TFPD_K1_GRID: CTAs of the fused map kernel (0 = one per SM)
     int k1_l2_knobs = 2, k1_roles = 3;  // TFPD_K1_L2 / TFPD_K1_ROLES tuning and profiling knobs
     unsigned long long *d_k1_times = nullptr;   // TFPD_K1_TIMES=1: per-CTA timestamps of the last K1 launch
     bool profiling = false, have_timing = false;
@@ -344,6 +345,7 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     if (const char *e = getenv("TFPD_K1_L2")) ctx->k1_l2_knobs = atoi(e);
     if (const char *e = getenv("TFPD_K1_ROLES")) ctx->k1_roles = atoi(e);
     if (const char *e = getenv("TFPD_K1_PR")) ctx->k1_pr = atoi(e);
+    if (const char *e = getenv("TFPD_K1_GRID")) ctx->k1_grid = atoi(e);
     if (const char *e = getenv("TFPD_K1_TIMES"))
         if (atoi(e) && cudaMalloc((void **)&ctx->d_k1_times, 1024 * 4 * 8) == cudaSuccess) {
             cudaMemset(ctx->d_k1_times, 0, 1024 * 4 * 8);
@@ -375,6 +377,23 @@ void tfpd_destroy(tfpd_ctx *ctx) {
 int tfpd_set_profiling(tfpd_ctx *ctx, int on) {
     if (!ctx) return TFPD_ERR_INVALID;
     ctx->profiling = on != 0;
+    return TFPD_OK;
+}
+
+int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
+    if (!ctx || !name) return TFPD_ERR_INVALID;
+    if (!strcmp(name, "k1_ctas")) {
+        if (value < 0 || value > ctx->sm_count) return fail(ctx, TFPD_ERR_INVALID, "k1_ctas=%d out of range", value);
+        ctx->k1_grid = value;
+    } else if (!strcmp(name, "host_chunks")) {
+        if (value < 0 || value > 4096) return fail(ctx, TFPD_ERR_INVALID, "host_chunks=%d out of range", value);
+        ctx->host_chunks = value;
+    } else if (!strcmp(name, "k1_l2")) {
+        if (value < 0 || value > 7) return fail(ctx, TFPD_ERR_INVALID, "k1_l2=%d out of range", value);
+        ctx->k1_l2_knobs = value;
+    } else {
+        return fail(ctx, TFPD_ERR_INVALID, "unknown option '%s'", name);
+    }
     return TFPD_OK;
 }
 
@@ -430,7 +449,7 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         p.debug_roles = ctx->k1_roles;
         p.dbg_times = ctx->d_k1_times;
         p.force_pr = ctx->k1_pr;
-        int r = launch_k1_fused_f4(p, want_dense, ctx->sm_count, s);
+        int r = launch_k1_fused_f4(p, want_dense, ctx->k1_grid > 0 ? ctx->k1_grid : ctx->sm_count, s);
         if (r < 0) return fail(ctx, TFPD_ERR_CUDA, "k1_fused_f4 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
         ctx->launches += r;
         src.base = net_out;
