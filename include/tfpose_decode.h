@@ -138,6 +138,13 @@ TFPD_API int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int 
 TFPD_API int tfpd_decode_host(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W,
                      float *heat_up, float *paf_up, float *peaks);
 
+/* Same, asynchronous: enqueues the copies and kernels on the ctx's own streams and returns; net_out and
+ * the dense output buffers must stay valid until tfpd_fetch_humans (which waits for everything) returns.
+ * With page-locked host memory the input of the next batch (on a second ctx) crosses PCIe while this
+ * batch is decoded. */
+TFPD_API int tfpd_decode_host_async(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W,
+                           float *heat_up, float *paf_up, float *peaks);
+
 /* Waits for the decode, copies the per-frame tables to the host.
  * humans: [N * max_humans] (frame i at humans + i*max_humans), info: [N].  Either may be null.
  * Returns TFPD_ERR_CAPACITY if any frame overflowed a table (tables are still filled). */

@@ -314,3 +314,33 @@ def test_tuning_options_do_not_change_results(cuda):
     with pytest.raises(tp.DecodeError):
         dec.set_option("k1_ctas", 100000)
     dec.close()
+
+
+def test_async_host_call_matches_the_synchronous_one(cuda):
+    """tfpd_decode_host_async + tfpd_fetch_humans on two alternating contexts == tfpd_decode_host."""
+    from helpers import table_tuples
+    xs = [synth.synth_batch(5, 46, 54, config_id=2, first_frame=800 + 5 * k) for k in range(4)]
+    ref = tp.PoseDecoder(max_batch=8, max_upsample=(184, 216))
+    want = []
+    for x in xs:
+        r, maps = ref.decode_host(x, (184, 216), want_dense=True)
+        want.append(([table_tuples(r, i) for i in range(5)], maps))
+    ref.close()
+    decs = [tp.PoseDecoder(max_batch=8, max_upsample=(184, 216)) for _ in range(2)]
+    got, inflight = [], []
+    for k, x in enumerate(xs):
+        d = decs[k % 2]
+        if len(inflight) == 2:
+            dd = inflight.pop(0)
+            r = dd.fetch()
+            got.append(([table_tuples(r, i) for i in range(5)], dd.host_maps()))
+        d.decode_host_async(x, (184, 216), want_dense=True)
+        inflight.append(d)
+    for dd in inflight:
+        r = dd.fetch()
+        got.append(([table_tuples(r, i) for i in range(5)], dd.host_maps()))
+    for (tg, mg), (tw, mw) in zip(got, want):
+        assert tg == tw
+        assert all(np.array_equal(a, b) for a, b in zip(mg, mw))
+    for d in decs:
+        d.close()

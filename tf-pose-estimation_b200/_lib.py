@@ -65,6 +65,7 @@ SIGNATURES = {
     "tfpd_last_error": (C.c_char_p, [_P]),
     "tfpd_decode_device": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, C.POINTER(Dense)]),
     "tfpd_decode_host": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P]),
+    "tfpd_decode_host_async": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P]),
     "tfpd_fetch_humans": (_I, [_P, _P, _P]),
     "tfpd_fetch_peaks": (_I, [_P, _I, _I, _P, _P, _P, _P, C.POINTER(_I)]),
     "tfpd_fetch_connections": (_I, [_P, _I, _I, _P, _P, _P, _P, C.POINTER(_I)]),

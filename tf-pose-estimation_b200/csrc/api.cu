@@ -62,7 +62,7 @@ struct tfpd_ctx {
     cudaStream_t last_stream = nullptr;
     int last_N = 0, last_H = 0, last_W = 0;
     int launches = 0;
-    bool decoded = false, fetched = false;
+    bool decoded = false, fetched = false, d2h_pending = false;
     std::string err;
     // host caches for the seam-2 getters
     std::vector<tfpd_human> g_humans;
@@ -188,6 +188,7 @@ void begin_call(tfpd_ctx *ctx, int N, int H, int W, cudaStream_t s) {
     ctx->last_W = W;
     ctx->decoded = false;
     ctx->fetched = false;
+    ctx->d2h_pending = false;
     ctx->getters_ready = false;
     ctx->have_timing = false;
 }
@@ -529,6 +530,10 @@ int tfpd_fetch_humans(tfpd_ctx *ctx, tfpd_human *humans, tfpd_frame_info *info) 
                                       (size_t)N * ctx->ws.max_humans * sizeof(tfpd_human), cudaMemcpyDeviceToHost,
                                       ctx->last_stream));
         CUDA_TRY(ctx, cudaStreamSynchronize(ctx->last_stream));
+        if (ctx->d2h_pending) {         // dense maps of a host-buffer call still on their way back
+            CUDA_TRY(ctx, cudaStreamSynchronize(ctx->st_d2h));
+            ctx->d2h_pending = false;
+        }
         ctx->fetched = true;
     }
     const tfpd_frame_info *hi = (const tfpd_frame_info *)ctx->h_result;
@@ -601,8 +606,8 @@ int tfpd_fetch_connections(tfpd_ctx *ctx, int frame, int cap, int *limb, int *ci
     return TFPD_OK;
 }
 
-int tfpd_decode_host(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W, float *heat_up,
-                     float *paf_up, float *peaks) {
+int tfpd_decode_host_async(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W, float *heat_up,
+                           float *paf_up, float *peaks) {
     if (!ctx) return TFPD_ERR_INVALID;
     if (!net_out) return fail(ctx, TFPD_ERR_INVALID, "decode_host: net_out is null");
     if (N < 1 || N > ctx->cfg.max_batch || h < 1 || w < 1 || H < 1 || W < 1)
@@ -674,9 +679,15 @@ int tfpd_decode_host(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, i
         }
     }
     ctx->decoded = true;
-    int rc = tfpd_fetch_humans(ctx, nullptr, nullptr);    // synchronises st_work; reports capacity overflow
-    if (want_dense) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->st_d2h));
-    return rc;
+    ctx->d2h_pending = want_dense;
+    return TFPD_OK;
+}
+
+int tfpd_decode_host(tfpd_ctx *ctx, const float *net_out, int N, int h, int w, int H, int W, float *heat_up,
+                     float *paf_up, float *peaks) {
+    int rc = tfpd_decode_host_async(ctx, net_out, N, h, w, H, W, heat_up, paf_up, peaks);
+    if (rc != TFPD_OK) return rc;
+    return tfpd_fetch_humans(ctx, nullptr, nullptr);    // synchronises; reports capacity overflow
 }
 
 int tfpd_process_paf_device(tfpd_ctx *ctx, int p1, int p2, int p3, const float *peaks, int h1, int h2, int h3,

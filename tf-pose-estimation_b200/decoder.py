@@ -91,6 +91,7 @@ class PoseDecoder(object):
         self.device = int(device)
         self._shape = None      # (N, H, W) of the last call
         self._keep = None       # buffers borrowed by the in-flight call
+        self._host_maps = None
 
     # -- lifetime ------------------------------------------------------------------------
     def close(self):
@@ -163,12 +164,12 @@ class PoseDecoder(object):
         self.decode_async(net_out, upsample_size, dense=dense, stream=stream)
         return self.fetch()
 
-    def decode_host(self, net_out, upsample_size, want_dense=False, out=None):
-        """NumPy ``net_out[N,h,w,57]`` (or [h,w,57]) in host memory -> DecodeResult; with
-        ``want_dense`` also returns (heat_up, paf_up, peaks) NumPy arrays, i.e. everything one
-        ``sess.run`` + ``estimate_paf`` of the reference yields (estimator.py:536-551).
-        ``out`` = preallocated (heat_up, paf_up, peaks) float32 C-contiguous arrays to fill (page-locked
-        memory makes the device->host copies asynchronous and several times faster)."""
+    def decode_host_async(self, net_out, upsample_size, want_dense=False, out=None):
+        """Enqueue the decode of a NumPy ``net_out[N,h,w,57]`` (or [h,w,57]) in host memory and return at once;
+        ``fetch()`` waits and returns the DecodeResult, ``host_maps()`` the dense arrays.  The arrays are kept
+        alive (and must not be written) until ``fetch()``.  ``out`` = preallocated (heat_up, paf_up, peaks)
+        float32 C-contiguous arrays to fill (page-locked memory makes the device->host copies asynchronous
+        and several times faster)."""
         x = np.ascontiguousarray(net_out, np.float32)
         if x.ndim == 3:
             x = x[None]
@@ -189,13 +190,25 @@ class PoseDecoder(object):
             pu = np.empty((N, H, W, 38), np.float32)
             pk = np.empty((N, H, W, 19), np.float32)
         self._shape = None
-        self._check(self._L.tfpd_decode_host(self._ctx, x.ctypes.data, N, h, w, H, W,
-                                             hu.ctypes.data if want_dense else None,
-                                             pu.ctypes.data if want_dense else None,
-                                             pk.ctypes.data if want_dense else None))
+        self._keep = (x, hu, pu, pk)
+        self._check(self._L.tfpd_decode_host_async(self._ctx, x.ctypes.data, N, h, w, H, W,
+                                                   hu.ctypes.data if want_dense else None,
+                                                   pu.ctypes.data if want_dense else None,
+                                                   pk.ctypes.data if want_dense else None))
         self._shape = (N, H, W)
+        self._host_maps = (hu, pu, pk) if want_dense else None
+
+    def host_maps(self):
+        """(heat_up, paf_up, peaks) of the last ``decode_host_async(..., want_dense=True)``; valid after ``fetch()``."""
+        return self._host_maps
+
+    def decode_host(self, net_out, upsample_size, want_dense=False, out=None):
+        """NumPy ``net_out[N,h,w,57]`` (or [h,w,57]) in host memory -> DecodeResult; with
+        ``want_dense`` also returns (heat_up, paf_up, peaks) NumPy arrays, i.e. everything one
+        ``sess.run`` + ``estimate_paf`` of the reference yields (estimator.py:536-551).  Synchronous."""
+        self.decode_host_async(net_out, upsample_size, want_dense=want_dense, out=out)
         res = self.fetch()
-        return (res, (hu, pu, pk)) if want_dense else res
+        return (res, self._host_maps) if self._host_maps is not None else res
 
     # -- introspection -------------------------------------------------------------------
     def peaks(self, frame=0):
