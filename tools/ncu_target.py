@@ -25,6 +25,7 @@ if DENSE:
              torch.empty((B, H, W, 19), device="cuda"))
 dec = tp.PoseDecoder(max_batch=B, max_upsample=(H, W), **({"max_peaks": 4096, "max_cands": 8192, "max_humans": 128} if CFG == 4 else {}))
 dec.set_profiling(True)
+dec.set_option("k1_ctas", int(os.environ.get("K1_CTAS", "128")))      # the bench setting
 for i in range(Wm + K):
     res = dec.decode(x, (H, W), dense=dense)
     print("step", i, ["%.3f" % v for v in dec.stage_ms()], int(res.info["n_humans"].sum()))
