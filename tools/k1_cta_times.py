@@ -19,9 +19,11 @@ dense = (torch.empty((B, H, W, 19), device="cuda"), torch.empty((B, H, W, 38), d
          torch.empty((B, H, W, 19), device="cuda"))
 dec = tp.PoseDecoder(max_batch=B, max_upsample=(H, W))
 dec.set_profiling(True)
+NC = int(os.environ.get("K1_CTAS", "128"))
+dec.set_option("k1_ctas", NC)
 for it in range(6):
     dec.decode(x, (H, W), dense=dense)
-    t = dec.k1_cta_times(148).astype(np.int64)
+    t = dec.k1_cta_times(NC).astype(np.int64)
     t0 = t[:, 0].min()
     start, blur, copy = (t[:, 0] - t0) / 1e3, (t[:, 1] - t0) / 1e3, (t[:, 2] - t0) / 1e3
     if it >= 3:
@@ -32,6 +34,9 @@ for it in range(6):
             print("slowest CTAs (cta, sm, blur_end, copy_end):", [(int(c), int(t[c, 3]), round(float(blur[c]), 1), round(float(copy[c]), 1)) for c in order[-8:]])
             print("fastest CTAs:", [(int(c), int(t[c, 3]), round(float(blur[c]), 1), round(float(copy[c]), 1)) for c in order[:8]])
             # by die / GPC guess: SM id halves
+            print("blur end by CTA index (us):", " ".join("%.0f" % v for v in blur))
+            print("copy end by CTA index (us):", " ".join("%.0f" % v for v in copy))
+            print("SM id by CTA index:", " ".join("%d" % v for v in t[:, 3]))
             for name, sel in (("sm<74", t[:, 3] < 74), ("sm>=74", t[:, 3] >= 74)):
                 print(name, "blur end mean %.1f copy end mean %.1f" % (blur[sel].mean(), copy[sel].mean()))
 dec.close()
