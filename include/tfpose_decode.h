@@ -178,6 +178,20 @@ TFPD_API int tfpd_get_part_x(tfpd_ctx *ctx, int cid);
 TFPD_API int tfpd_get_part_y(tfpd_ctx *ctx, int cid);
 TFPD_API float tfpd_get_part_score(tfpd_ctx *ctx, int cid);
 
+/* draw_humans (tf_pose/estimator.py:391-415) on a headless buffer: for every human a radius-3, thickness-3
+ * circle per present part and a thickness-3 line per CocoPairsRender pair, colours of common.py:108-110, later
+ * primitives over earlier ones -- the pixels cv2.circle / cv2.line would set, bit for bit.  No window, no GL.
+ *
+ * tfpd_draw_humans: images [N,img_h,img_w,3] uint8 (HOST pointer when on_device == 0: copied in, drawn, copied
+ *   back; DEVICE pointer otherwise, asynchronous on stream).  centers: HOST int32 [N][max_h][18][2] = (x, y) image
+ *   pixels per part exactly as draw_humans computes them (int(part.x * w + 0.5)), x == INT32_MIN for an absent
+ *   part; counts: HOST int32 [N] humans per image (<= max_h).
+ * tfpd_draw_decoded: draws the humans of the LAST decode on ctx straight from its device tables into DEVICE
+ *   images [N,img_h,img_w,3] (N = frames of that decode); nothing crosses PCIe. */
+TFPD_API int tfpd_draw_humans(tfpd_ctx *ctx, uint8_t *images, int on_device, int N, int img_h, int img_w,
+                     const int32_t *centers, const int32_t *counts, int max_h, void *stream);
+TFPD_API int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int img_w, void *stream);
+
 /* Tuning options, by name (unknown name or out-of-range value -> TFPD_ERR_INVALID):
  *   "k1_ctas"      CTAs of the fused upsample/smoother/NMS kernel; 0 = one per SM (default).  The kernel is
  *                  HBM-bound, so with several contexts in flight on different streams a smaller grid (128 of

@@ -84,6 +84,8 @@ SIGNATURES = {
     "tfpd_last_stage_ms": (_I, [_P, C.POINTER(C.c_float * 4)]),
     "tfpd_debug_k1_times": (_I, [_P, _P, _I]),
     "tfpd_set_option": (_I, [_P, C.c_char_p, _I]),
+    "tfpd_draw_humans": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _I, _P]),
+    "tfpd_draw_decoded": (_I, [_P, _P, _I, _I, _P]),
 }
 
 _lib = None

@@ -48,6 +48,7 @@ struct tfpd_ctx {
     unsigned char *h_result = nullptr;  // pinned mirror of the result block
     float *d_k1d = nullptr;             // float32 separable factor (generic path)
     std::vector<double> s1d;
+    DevBuf draw_ids, draw_centers, draw_counts, draw_img;  // draw_humans scratch (lazily sized)
     DevBuf in_buf, dense_buf, gen_buf;  // lazily sized: host-call input, dense outputs, generic-path scratch
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     // host-buffer calls: H2D, kernels and D2H of successive frame chunks run on three streams
@@ -372,12 +373,76 @@ void tfpd_destroy(tfpd_ctx *ctx) {
     ctx->in_buf.release();
     ctx->dense_buf.release();
     ctx->gen_buf.release();
+    ctx->draw_ids.release();
+    ctx->draw_centers.release();
+    ctx->draw_counts.release();
+    ctx->draw_img.release();
     delete ctx;
 }
 
 int tfpd_set_profiling(tfpd_ctx *ctx, int on) {
     if (!ctx) return TFPD_ERR_INVALID;
     ctx->profiling = on != 0;
+    return TFPD_OK;
+}
+
+static int draw_reserve_ids(tfpd_ctx *ctx, size_t npix) {
+    const size_t had = ctx->draw_ids.bytes;
+    CUDA_TRY(ctx, ctx->draw_ids.reserve(npix * 4));
+    if (ctx->draw_ids.bytes != had) CUDA_TRY(ctx, cudaMemset(ctx->draw_ids.p, 0, ctx->draw_ids.bytes));   // the paint pass keeps it zero
+    return TFPD_OK;
+}
+
+int tfpd_draw_humans(tfpd_ctx *ctx, uint8_t *images, int on_device, int N, int img_h, int img_w,
+                     const int32_t *centers, const int32_t *counts, int max_h, void *stream) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!images || !centers || !counts) return fail(ctx, TFPD_ERR_INVALID, "draw_humans: null argument");
+    if (N < 1 || img_h < 1 || img_w < 1 || max_h < 1 || img_h > 32767 || img_w > 32767)
+        return fail(ctx, TFPD_ERR_INVALID, "draw_humans: bad dimensions");
+    for (int i = 0; i < N; ++i)
+        if (counts[i] < 0 || counts[i] > max_h) return fail(ctx, TFPD_ERR_INVALID, "draw_humans: counts[%d]=%d outside 0..%d", i, counts[i], max_h);
+    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    cudaStream_t s = on_device ? (cudaStream_t)stream : ctx->st_work;
+    const size_t npix = (size_t)N * img_h * img_w, cbytes = (size_t)N * max_h * 36 * 4;
+    int rc = draw_reserve_ids(ctx, npix);
+    if (rc != TFPD_OK) return rc;
+    CUDA_TRY(ctx, ctx->draw_centers.reserve(cbytes));
+    CUDA_TRY(ctx, ctx->draw_counts.reserve((size_t)N * 4));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->draw_centers.p, centers, cbytes, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->draw_counts.p, counts, (size_t)N * 4, cudaMemcpyHostToDevice, s));
+    unsigned char *d_img = images;
+    if (!on_device) {
+        CUDA_TRY(ctx, ctx->draw_img.reserve(npix * 3));
+        d_img = (unsigned char *)ctx->draw_img.p;
+        CUDA_TRY(ctx, cudaMemcpyAsync(d_img, images, npix * 3, cudaMemcpyHostToDevice, s));
+    }
+    if (launch_draw((const int *)ctx->draw_centers.p, (const int *)ctx->draw_counts.p, max_h, d_img, (int *)ctx->draw_ids.p,
+                    N, img_h, img_w, s) < 0)
+        return fail(ctx, TFPD_ERR_CUDA, "draw kernels failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (!on_device) CUDA_TRY(ctx, cudaMemcpyAsync(images, d_img, npix * 3, cudaMemcpyDeviceToHost, s));
+    // the host tables were read by asynchronous copies: they may be reused once this returns
+    CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    return TFPD_OK;
+}
+
+int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int img_w, void *stream) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!ctx->decoded) return fail(ctx, TFPD_ERR_STATE, "draw_decoded: no decode on this ctx yet");
+    if (!images || img_h < 1 || img_w < 1 || img_h > 32767 || img_w > 32767)
+        return fail(ctx, TFPD_ERR_INVALID, "draw_decoded: bad argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const int N = ctx->last_N, max_h = ctx->ws.max_humans;
+    int rc = draw_reserve_ids(ctx, (size_t)N * img_h * img_w);
+    if (rc != TFPD_OK) return rc;
+    CUDA_TRY(ctx, ctx->draw_centers.reserve((size_t)N * max_h * 36 * 4));
+    CUDA_TRY(ctx, ctx->draw_counts.reserve((size_t)N * 4));
+    if (s != ctx->last_stream) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->last_stream));     // the tables must exist
+    if (launch_centers_from_tables(ctx->ws, N, ctx->last_H, ctx->last_W, img_h, img_w, (int *)ctx->draw_centers.p,
+                                   (int *)ctx->draw_counts.p, s) < 0 ||
+        launch_draw((const int *)ctx->draw_centers.p, (const int *)ctx->draw_counts.p, max_h, images,
+                    (int *)ctx->draw_ids.p, N, img_h, img_w, s) < 0)
+        return fail(ctx, TFPD_ERR_CUDA, "draw kernels failed: %s", cudaGetErrorString(cudaGetLastError()));
     return TFPD_OK;
 }
 

@@ -115,5 +115,9 @@ int launch_limb_score(const Workspace &ws, int N, const PafSource &src, size_t f
                       const Thresholds &th, int sm_count, cudaStream_t s);
 int launch_assemble(const Workspace &ws, int N, const Thresholds &th, cudaStream_t s);
 size_t assemble_smem_bytes(const Workspace &ws);
+int launch_draw(const int *d_centers, const int *d_counts, int max_h, unsigned char *d_img, int *d_ids, int N, int H,
+                int W, cudaStream_t s);
+int launch_centers_from_tables(const Workspace &ws, int N, int map_h, int map_w, int img_h, int img_w, int *d_centers,
+                               int *d_counts, cudaStream_t s);
 
 }  // namespace tfpd

@@ -210,6 +210,73 @@ class PoseDecoder(object):
         res = self.fetch()
         return (res, self._host_maps) if self._host_maps is not None else res
 
+    # -- draw_humans (estimator.py:391-415) on a headless buffer ------------------------------
+    @staticmethod
+    def _centers_table(humans_per_image, image_h, image_w):
+        """int32 [N, max_h, 18, 2] of (x, y) = int(part.x * w + 0.5), int(part.y * h + 0.5) (estimator.py:404) and
+        counts[N]; an absent part has x == INT32_MIN."""
+        n = len(humans_per_image)
+        max_h = max(1, max((len(hs) for hs in humans_per_image), default=1))
+        centers = np.full((n, max_h, 18, 2), np.iinfo(np.int32).min, np.int32)
+        counts = np.zeros(n, np.int32)
+        for i, hs in enumerate(humans_per_image):
+            counts[i] = len(hs)
+            for j, human in enumerate(hs):
+                for k, bp in human.body_parts.items():
+                    if 0 <= k < 18:
+                        centers[i, j, k, 0] = int(bp.x * image_w + 0.5)
+                        centers[i, j, k, 1] = int(bp.y * image_h + 0.5)
+        return centers, counts, max_h
+
+    def draw_humans(self, images, humans_per_image, imgcopy=False):
+        """``images``: uint8 NumPy [N,H,W,3] / [H,W,3] (drawn in place unless ``imgcopy``) or a CUDA uint8 tensor
+        [N,H,W,3]; ``humans_per_image``: list (per image) of lists of ``Human`` (a flat list for one image).
+        Sets the pixels ``TfPoseEstimator.draw_humans`` would, bit for bit.  Returns the drawn array/tensor."""
+        is_numpy = isinstance(images, np.ndarray)
+        single = (images.ndim == 3)
+        if single:
+            humans_per_image = [humans_per_image]
+        if is_numpy:
+            if images.dtype != np.uint8 or images.shape[-1] != 3:
+                raise ValueError("images must be uint8 [N,H,W,3] or [H,W,3]")
+            src = images[None] if single else images
+            buf = np.array(src, dtype=np.uint8, order='C', copy=True) if imgcopy else np.ascontiguousarray(src)
+            n, h, w = buf.shape[:3]
+            ptr, on_device, stream = buf.ctypes.data, 0, None
+        else:
+            import torch
+            if images.dtype != torch.uint8 or images.shape[-1] != 3 or not images.is_cuda or not images.is_contiguous():
+                raise ValueError("CUDA images must be contiguous uint8 [N,H,W,3]")
+            buf = images.clone() if imgcopy else images
+            if single:
+                buf = buf.unsqueeze(0)
+            n, h, w = buf.shape[:3]
+            ptr, on_device = buf.data_ptr(), 1
+            stream = C.c_void_p(torch.cuda.current_stream(images.device).cuda_stream)
+        if len(humans_per_image) != n:
+            raise ValueError("%d images but humans for %d" % (n, len(humans_per_image)))
+        centers, counts, max_h = self._centers_table(humans_per_image, h, w)
+        self._check(self._L.tfpd_draw_humans(self._ctx, ptr, on_device, n, h, w, centers.ctypes.data,
+                                             counts.ctypes.data, max_h, stream))
+        if is_numpy and not imgcopy:
+            if not np.shares_memory(buf, images):
+                images[...] = buf[0] if single else buf      # non-contiguous input: write the result back
+            return images
+        return buf[0] if single else buf
+
+    def draw_decoded(self, images, stream=None):
+        """Draw the humans of the last decode on this decoder into the CUDA uint8 tensor ``images[N,H,W,3]``
+        straight from the device tables (nothing crosses PCIe).  Asynchronous on ``stream``."""
+        import torch
+        if not (isinstance(images, torch.Tensor) and images.is_cuda and images.dtype == torch.uint8
+                and images.dim() == 4 and images.shape[3] == 3 and images.is_contiguous()):
+            raise ValueError("images must be a contiguous CUDA uint8 [N,H,W,3] tensor")
+        if stream is None:
+            stream = torch.cuda.current_stream(images.device)
+        self._check(self._L.tfpd_draw_decoded(self._ctx, images.data_ptr(), int(images.shape[1]), int(images.shape[2]),
+                                              C.c_void_p(stream.cuda_stream)))
+        return images
+
     # -- introspection -------------------------------------------------------------------
     def peaks(self, frame=0):
         """dict(part, x, y, score) of int32/float32 arrays: the peak table of a frame."""

@@ -96,5 +96,10 @@ class TfPosePostProcessor(object):
         self.last_info = res.info[0]
         return res.humans(0)
 
+    def draw_humans(self, npimg, humans, imgcopy=False):
+        """``TfPoseEstimator.draw_humans(npimg, humans, imgcopy=False)`` (estimator.py:391-415), rasterised by the
+        CUDA kernels on a headless buffer: same pixels as the cv2.circle / cv2.line calls of the reference."""
+        return self._decoder.draw_humans(npimg, humans, imgcopy=imgcopy)
+
     def close(self):
         self._decoder.close()
