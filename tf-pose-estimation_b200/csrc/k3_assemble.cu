@@ -156,33 +156,61 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
         if ((keys[i] >> 24) == (keys[i - 1] >> 24)) atomicOr(&s_flags, TFPD_FLAG_SCORE_TIE);
     __syncthreads();
 
-    // ---- 2. greedy matching, one warp per limb (lane 0 walks; the walk is inherently serial) ----
+    // ---- 2. greedy matching (:98-124), one warp per limb ----
+    // The walk over the sorted candidates is serial only in the ACCEPTED ones: a window of 32 candidates is
+    // loaded one per lane, lanes whose end points are already taken (bitmaps, from earlier windows) drop out at
+    // once, and the warp then steps from one surviving candidate to the next in order -- the accepted candidate's
+    // end points are broadcast and every later lane sharing one of them drops out.  Same result as testing the
+    // candidates one by one, in (number of connections) steps instead of (number of candidates).
     int16_t *c1 = ws.conn_cid1 + (size_t)n * ws.max_cands;
     int16_t *c2 = ws.conn_cid2 + (size_t)n * ws.max_cands;
     float *cs = ws.conn_score + (size_t)n * ws.max_cands;
-    if (warp < kLimbs && lane == 0) {
+    if (warp < kLimbs) {
         const int limb = warp;
         const int beg = s_lstart[limb], end = s_lstart[limb + 1];
         uint32_t *ua = used + (size_t)limb * 2 * kBitmapWords, *ub = ua + kBitmapWords;
         const int fa = s_first[c_limb_part[limb][0]], fb = s_first[c_limb_part[limb][1]];
         int nconn = 0;
-        for (int i = beg; i < end; ++i) {
-            const unsigned long long key = keys[i];
-            const int a = (int)((key >> 12) & 0xfff), b = (int)(key & 0xfff);
-            if ((ua[a >> 5] >> (a & 31)) & 1u) continue;        // peak_id1 already assigned (:104-108)
-            if ((ub[b >> 5] >> (b & 31)) & 1u) continue;        // peak_id2 already assigned (:110-114)
-            ua[a >> 5] |= 1u << (a & 31);
-            ub[b >> 5] |= 1u << (b & 31);
-            c1[beg + nconn] = (int16_t)(fa + a);                // conn.cid1 = peak_a_list[idx1].id (:122)
-            c2[beg + nconn] = (int16_t)(fb + b);
-            const uint32_t sbits = 0xffffffffu - (uint32_t)((key >> 24) & 0xffffffffu);
-            cs[beg + nconn] = __uint_as_float(sbits);
-            // the same record for phase 3, packed over a key this walk has already consumed (beg+nconn <= i)
-            keys[beg + nconn] = ((unsigned long long)sbits << 32) | ((unsigned long long)(uint32_t)(fa + a) << 16) |
-                                (unsigned long long)(uint32_t)(fb + b);
-            ++nconn;
+        for (int w0 = beg; w0 < end; w0 += 32) {
+            const int i = w0 + lane;
+            unsigned long long key = 0ull;
+            int a = -1, b = -1;
+            bool alive = false;
+            if (i < end) {
+                key = keys[i];
+                a = (int)((key >> 12) & 0xfff);
+                b = (int)(key & 0xfff);
+                alive = !((ua[a >> 5] >> (a & 31)) & 1u) && !((ub[b >> 5] >> (b & 31)) & 1u);   // :104-114
+            }
+            __syncwarp();           // every key of the window is in a register before records are packed over them
+            unsigned live = __ballot_sync(0xffffffffu, alive);
+            while (live) {
+                const int j = __ffs(live) - 1;
+                const int ja = __shfl_sync(0xffffffffu, a, j), jb = __shfl_sync(0xffffffffu, b, j);
+                if (lane == j) {
+                    ua[a >> 5] |= 1u << (a & 31);
+                    ub[b >> 5] |= 1u << (b & 31);
+                    const uint32_t sbits = 0xffffffffu - (uint32_t)((key >> 24) & 0xffffffffu);
+                    // the connection record (score | cid1 | cid2; conn.cid = peak list id, :122), packed over a
+                    // key this walk has already consumed (beg + nconn <= w0 + j, the window is in registers)
+                    keys[beg + nconn] = ((unsigned long long)sbits << 32) |
+                                        ((unsigned long long)(uint32_t)(fa + a) << 16) |
+                                        (unsigned long long)(uint32_t)(fb + b);
+                }
+                ++nconn;
+                alive = alive && lane > j && a != ja && b != jb;
+                live = __ballot_sync(0xffffffffu, alive);
+            }
+            __syncwarp();           // bitmap updates visible to the next window
         }
-        s_ccount[limb] = nconn;
+        if (lane == 0) s_ccount[limb] = nconn;
+        // the global connection table (tfpd_fetch_connections) in one coalesced sweep, off the serial chain
+        for (int k = lane; k < nconn; k += 32) {
+            const unsigned long long rec = keys[beg + k];
+            c1[beg + k] = (int16_t)((rec >> 16) & 0xffffu);
+            c2[beg + k] = (int16_t)(rec & 0xffffu);
+            cs[beg + k] = __uint_as_float((uint32_t)(rec >> 32));
+        }
     }
     __syncthreads();
     if (ws.dbg_times && tid == 0 && n < 64) ws.dbg_times[2048 + n * 8 + 4] = clock64();
@@ -609,7 +637,12 @@ __global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Threshold
         ws.info[n].n_cands = cnt;
         ws.info[n].n_rows = nrows;
         ws.info[n].flags = flags;
-        if (ws.dbg_times && n < 64) ws.dbg_times[2048 + n * 8 + 6] = clock64();
+        if (ws.dbg_times && n < 64) {
+            ws.dbg_times[2048 + n * 8 + 6] = clock64();
+            int tc = 0;
+            for (int l = 0; l < kLimbs; ++l) tc += s_ccount[l];
+            ws.dbg_times[2048 + n * 8 + 7] = ((unsigned long long)tc << 32) | (unsigned)s_maxseg;   // connections | longest segment
+        }
     }
 }
 

@@ -29,4 +29,5 @@ for it in range(5):
         print("iter %d K3 %.1f us; cycles mean per phase: %s | slowest frame %d (%d rows, %d cands): %s total %d"
               % (it, dec.stage_ms()[3] * 1e3, dict(zip(names, d.mean(0).astype(int).tolist())), slow,
                  int(res.info["n_rows"][slow]), int(res.info["n_cands"][slow]), dict(zip(names, d[slow].tolist())), tot[slow]))
+        print("   slowest frame: %d connections, longest limb segment %d candidates" % (t[slow, 7] >> 32, t[slow, 7] & 0xffffffff))
 dec.close()
