@@ -344,3 +344,25 @@ def test_async_host_call_matches_the_synchronous_one(cuda):
         assert all(np.array_equal(a, b) for a, b in zip(mg, mw))
     for d in decs:
         d.close()
+
+
+def test_contexts_with_different_smoothers_do_not_interfere(cuda):
+    """Smoother weights are per context (kernel parameters, not a shared __constant__ symbol): creating a second
+    context with another sigma must not change what the first one computes."""
+    import torch
+    x = torch.from_numpy(synth.synth_batch(2, 46, 54, config_id=2, first_frame=950)).cuda()
+
+    def peaks_map(dec):
+        dense = tuple(torch.empty((2, 184, 216, c), device="cuda") for c in (19, 38, 19))
+        dec.decode(x, (184, 216), dense=dense)
+        return dense[2].cpu().numpy()
+
+    a = tp.PoseDecoder(max_batch=2, max_upsample=(184, 216))
+    before = peaks_map(a)
+    b = tp.PoseDecoder(max_batch=2, max_upsample=(184, 216), blur_sigma=1.5)
+    other = peaks_map(b)
+    after = peaks_map(a)
+    assert np.array_equal(before, after)
+    assert not np.array_equal(before, other)
+    a.close()
+    b.close()

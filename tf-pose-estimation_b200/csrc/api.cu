@@ -48,6 +48,7 @@ struct tfpd_ctx {
     unsigned char *h_result = nullptr;  // pinned mirror of the result block
     float *d_k1d = nullptr;             // float32 separable factor (generic path)
     std::vector<double> s1d;
+    float wp[4][8] = {};                // polyphase weights of the x4 fast path
     DevBuf draw_ids, draw_centers, draw_counts, draw_img;  // draw_humans scratch (lazily sized)
     DevBuf in_buf, dense_buf, gen_buf;  // lazily sized: host-call input, dense outputs, generic-path scratch
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -335,7 +336,7 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     for (size_t i = 0; i < s32.size(); ++i) s32[i] = (float)ctx->s1d[i];
     e = cudaMalloc((void **)&ctx->d_k1d, s32.size() * 4);
     if (e == cudaSuccess) e = cudaMemcpy(ctx->d_k1d, s32.data(), s32.size() * 4, cudaMemcpyHostToDevice);
-    if (e != cudaSuccess || (cfg->blur_ksize == 25 && upload_polyphase_weights(ctx->s1d.data(), 25) != 0)) {
+    if (e != cudaSuccess || (cfg->blur_ksize == 25 && polyphase_weights(ctx->s1d.data(), 25, ctx->wp) != 0)) {
         tfpd_destroy(ctx);
         return fail(nullptr, TFPD_ERR_CUDA, "smoother weight upload failed: %s", cudaGetErrorString(cudaGetLastError()));
     }
@@ -511,6 +512,7 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         p.copy_nchunks = (w + 31) / 32;                     // <= 32 cells (29 KB staged) per copy item
         p.copy_chunk = (w + p.copy_nchunks - 1) / p.copy_nchunks;
         p.thresh = ctx->cfg.thresh_heat;
+        memcpy(p.wp, ctx->wp, sizeof(p.wp));
         p.l2_knobs = ctx->k1_l2_knobs;
         p.debug_roles = ctx->k1_roles;
         p.dbg_times = ctx->d_k1_times;

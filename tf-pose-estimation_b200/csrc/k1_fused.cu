@@ -42,7 +42,6 @@ constexpr int kThreads = kBlurThreads + kCopyThreads;   // 640 -> 96 registers p
 // a warp pass owns at most 32*CPL-8 = 56 cells (see launch_k1_fused_f4: chunk_cells <= 56)
 constexpr int NPX = 4 * CPL;                // output pixels per lane per row
 
-__constant__ float c_wp[4][8];              // polyphase weights: phase p, low-res tap t (cell offset t-3)
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
@@ -336,9 +335,9 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
             float gv[CPL];
 #pragma unroll
             for (int k = 0; k < CPL; ++k) {
-                float a = c_wp[py][0] * win[k][0];
+                float a = p.wp[py][0] * win[k][0];
 #pragma unroll
-                for (int t = 1; t < 7; ++t) a = fmaf(c_wp[py][t], win[k][t], a);
+                for (int t = 1; t < 7; ++t) a = fmaf(p.wp[py][t], win[k][t], a);
                 gv[k] = a;
             }
             // window of gv over cells (own first cell - 3 .. own last cell + 3) via shuffles
@@ -357,9 +356,9 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
             for (int k = 0; k < CPL; ++k) {
 #pragma unroll
                 for (int px = 0; px < 4; ++px) {
-                    float a = c_wp[px][0] * Wn[k];
+                    float a = p.wp[px][0] * Wn[k];
 #pragma unroll
-                    for (int t = 1; t < 7; ++t) a = fmaf(c_wp[px][t], Wn[k + t], a);
+                    for (int t = 1; t < 7; ++t) a = fmaf(p.wp[px][t], Wn[k + t], a);
                     cur[k * 4 + px] = cin[k] ? a : NEG;
                 }
             }
@@ -572,9 +571,11 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
 
 }  // namespace
 
-int upload_polyphase_weights(const double *s1d, int ksize) {
+// Polyphase weights of the 25-tap separable factor over a x4-replicated signal: wp[p][t] = sum of the taps that
+// fall on low-res cell offset t-3 for output phase p, summed in float64.  They travel in the kernel parameters
+// (constant bank, and per context: two contexts may have different smoother parameters).
+int polyphase_weights(const double *s1d, int ksize, float wp[4][8]) {
     if (ksize != 25) return -1;
-    float wp[4][8];
     for (int p = 0; p < 4; ++p) {
         double acc[7] = {0, 0, 0, 0, 0, 0, 0};
         for (int q = 0; q < 25; ++q) {
@@ -585,7 +586,7 @@ int upload_polyphase_weights(const double *s1d, int ksize) {
         for (int t = 0; t < 7; ++t) wp[p][t] = (float)acc[t];
         wp[p][7] = 0.0f;
     }
-    return cudaMemcpyToSymbol(c_wp, wp, sizeof(wp)) == cudaSuccess ? 0 : -2;
+    return 0;
 }
 
 int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t s) {

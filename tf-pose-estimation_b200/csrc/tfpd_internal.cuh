@@ -96,6 +96,7 @@ struct K1Params {
     int chunk_cells, nchunks;                              // blur role: <= 56-cell column chunks
     int copy_chunk, copy_nchunks;                          // copy role: <= 32-cell row chunks (one lane per cell)
     float thresh;
+    float wp[4][8];                     // polyphase smoother weights: phase p, low-res tap t (cell offset t-3)
     int l2_knobs;                       // bit0 up-front L2 prefetch of X, bit1 evict_first stores, bit2 evict_last prefetch
     int debug_roles;                    // bit0 blur role, bit1 copy role (3 = normal; tuning/profiling only)
     int force_pr;                       // 0 = automatic; 2..4 = peak rows per store group (tuning knob)
@@ -104,7 +105,7 @@ struct K1Params {
 
 // launchers (each returns the number of kernel launches it issued, <0 on launch error)
 int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t s);
-int upload_polyphase_weights(const double *s1d, int ksize);     // F=4, ksize=25 fast path
+int polyphase_weights(const double *s1d, int ksize, float wp[4][8]);     // F=4, ksize=25 fast path
 int launch_generic_maps(const float *X, int N, int h, int w, int H, int W, const float *d_k1d, int ksize,
                         float *heat_up, float *paf_up, float *peaks, float *scratch, const Workspace &ws, float thr,
                         cudaStream_t s);
