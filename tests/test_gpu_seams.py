@@ -366,3 +366,18 @@ def test_contexts_with_different_smoothers_do_not_interfere(cuda):
     assert not np.array_equal(before, other)
     a.close()
     b.close()
+
+
+def test_post_processor_reused_map_buffers(cuda):
+    """reuse_map_buffers=True: same humans and maps as the default, from page-locked buffers."""
+    x = synth.synth_batch(2, 46, 54, config_id=2, first_frame=970)
+    a = tp.TfPosePostProcessor(target_size=(432, 368))
+    b = tp.TfPosePostProcessor(target_size=(432, 368), reuse_map_buffers=True)
+    for i in range(2):
+        ha = a.inference_from_output(x[i], upsample_size=4.0)
+        hb = b.inference_from_output(x[i], upsample_size=4.0)
+        assert [str(h) for h in ha] == [str(h) for h in hb] and [h.score for h in ha] == [h.score for h in hb]
+        assert np.array_equal(a.heatMat, b.heatMat) and np.array_equal(a.pafMat, b.pafMat)
+        assert np.array_equal(a.peaks, b.peaks)
+    a.close()
+    b.close()

@@ -55,9 +55,14 @@ class TfPosePostProcessor(object):
     """
 
     def __init__(self, target_size=(432, 368), device=0, mode="asbuilt", keep_maps=True, max_ratio=8.0,
-                 **overrides):
+                 reuse_map_buffers=False, **overrides):
+        """``reuse_map_buffers``: ``heatMat`` / ``pafMat`` / ``peaks`` of NumPy-input calls live in page-locked
+        buffers that the next call overwrites (several times faster than fresh pageable arrays; the reference
+        allocates new arrays per call, so this is opt-in)."""
         self.target_size = target_size
         self.keep_maps = keep_maps
+        self.reuse_map_buffers = reuse_map_buffers
+        self._pinned = {}
         H, W = upsample_size_for(target_size[0], target_size[1], max_ratio)
         self._decoder = PoseDecoder(max_batch=1, max_upsample=(H, W), device=device, mode=mode, **overrides)
         self.heatMat = self.pafMat = None
@@ -75,7 +80,16 @@ class TfPosePostProcessor(object):
             size = [int(input_hw[0] / 8 * upsample_size), int(input_hw[1] / 8 * upsample_size)]
         is_numpy = isinstance(net_out, np.ndarray)
         if is_numpy:
-            out = self._decoder.decode_host(net_out, size, want_dense=self.keep_maps)
+            bufs = None
+            if self.keep_maps and self.reuse_map_buffers:
+                n = 1 if net_out.ndim == 3 else net_out.shape[0]
+                key = (n, size[0], size[1])
+                if key not in self._pinned:
+                    import torch
+                    self._pinned = {key: tuple(torch.empty((n, size[0], size[1], c), dtype=torch.float32).pin_memory().numpy()
+                                               for c in (19, 38, 19))}
+                bufs = self._pinned[key]
+            out = self._decoder.decode_host(net_out, size, want_dense=self.keep_maps, out=bufs)
             if self.keep_maps:
                 res, (hu, pu, pk) = out
                 self.peaks, self.heatMat, self.pafMat = pk[0], hu[0], pu[0]
