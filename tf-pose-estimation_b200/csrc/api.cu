@@ -49,6 +49,9 @@ struct tfpd_ctx {
     float *d_k1d = nullptr;             // float32 separable factor (generic path)
     std::vector<double> s1d;
     float wp[4][8] = {};                // polyphase weights of the x4 fast path
+    std::vector<float> poly_host;       // host copy of the same (kernel-parameter weights of the fused pass)
+    DevBuf poly_buf;                    // per-phase smoother weights of the power-of-two path, for factor poly_log2f
+    int poly_log2f = -1, poly_T = 0;
     DevBuf draw_ids, draw_centers, draw_counts, draw_img;  // draw_humans scratch (lazily sized)
     DevBuf in_buf, dense_buf, gen_buf;  // lazily sized: host-call input, dense outputs, generic-path scratch
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -126,6 +129,17 @@ int next_pow2(int v) {
 }
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// log2 of the upsample factor when (h,w)->(H,W) is a power-of-two replication the polyphase path handles
+// (factor 2..16, at most 33 cell taps), else 0
+int pow2_factor(int h, int w, int H, int W, int ksize) {
+    for (int l = 1; l <= 4; ++l)
+        if (H == (h << l) && W == (w << l)) {
+            const int F = 1 << l, R = (ksize / 2 + F - 1) / F;
+            return (2 * R + 1 <= 33) ? l : 0;
+        }
+    return 0;
+}
 
 Thresholds thresholds_of(const tfpd_config &c) {
     Thresholds t;
@@ -374,6 +388,7 @@ void tfpd_destroy(tfpd_ctx *ctx) {
     ctx->in_buf.release();
     ctx->dense_buf.release();
     ctx->gen_buf.release();
+    ctx->poly_buf.release();
     ctx->draw_ids.release();
     ctx->draw_centers.release();
     ctx->draw_counts.release();
@@ -526,6 +541,42 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         src.chan = kNetC;
         src.chan_off = kHeatC;
         src.shift = 2;
+        src.H = H;
+        frame_stride = (size_t)h * w * kNetC;
+    } else if (int log2f = pow2_factor(h, w, H, W, ctx->cfg.blur_ksize)) {
+        // power-of-two replication other than the fused kernel's case: polyphase passes on the low-res rows
+        if (ctx->poly_log2f != log2f) {
+            const int F = 1 << log2f, pad = ctx->cfg.blur_ksize / 2, R = (pad + F - 1) / F, T = 2 * R + 1;
+            std::vector<float> wp((size_t)F * T);
+            for (int p = 0; p < F; ++p) {
+                std::vector<double> acc(T, 0.0);
+                for (int q = 0; q < ctx->cfg.blur_ksize; ++q) {
+                    const int d = p + q - pad;                       // upsampled offset relative to the cell start
+                    const int cell = (d >= 0) ? d / F : -((-d + F - 1) / F);
+                    acc[cell + R] += ctx->s1d[q];
+                }
+                for (int t = 0; t < T; ++t) wp[(size_t)p * T + t] = (float)acc[t];
+            }
+            CUDA_TRY(ctx, ctx->poly_buf.reserve(wp.size() * 4));
+            CUDA_TRY(ctx, cudaMemcpyAsync(ctx->poly_buf.p, wp.data(), wp.size() * 4, cudaMemcpyHostToDevice, s));
+            CUDA_TRY(ctx, cudaStreamSynchronize(s));                 // wp is a local; once per factor
+            ctx->poly_host = wp;
+            ctx->poly_log2f = log2f;
+            ctx->poly_T = T;
+        }
+        const size_t px = (size_t)N * H * W;
+        CUDA_TRY(ctx, ctx->gen_buf.reserve(((size_t)N * h * W + px) * kHeatC * 4));
+        int r = launch_pow2_maps(net_out, N, h, w, log2f, (const float *)ctx->poly_buf.p, ctx->poly_host.data(), ctx->poly_T,
+                                 want_dense ? dense->heat_up : nullptr, want_dense ? dense->paf_up : nullptr,
+                                 want_dense ? dense->peaks : nullptr, (float *)ctx->gen_buf.p, ws, ctx->cfg.thresh_heat, s);
+        if (r < 0) return fail(ctx, TFPD_ERR_CUDA, "power-of-two map kernels failed: %s", cudaGetErrorString(cudaGetLastError()));
+        ctx->launches += r;
+        src.base = net_out;
+        src.rows = h;
+        src.cols = w;
+        src.chan = kNetC;
+        src.chan_off = kHeatC;
+        src.shift = log2f;
         src.H = H;
         frame_stride = (size_t)h * w * kNetC;
     } else {

@@ -109,6 +109,9 @@ int polyphase_weights(const double *s1d, int ksize, float wp[4][8]);     // F=4,
 int launch_generic_maps(const float *X, int N, int h, int w, int H, int W, const float *d_k1d, int ksize,
                         float *heat_up, float *paf_up, float *peaks, float *scratch, const Workspace &ws, float thr,
                         cudaStream_t s);
+int launch_pow2_maps(const float *X, int N, int h, int w, int log2f, const float *d_wp, const float *h_wp, int T,
+                     float *heat_up, float *paf_up, float *peaks, float *scratch, const Workspace &ws, float thr,
+                     cudaStream_t s);
 int launch_scan_dense_peaks(const float *peaks, const float *heat, int N, int H, int W, float thresh,
                             const Workspace &ws, cudaStream_t s);
 int launch_sort_peaks(const Workspace &ws, int N, cudaStream_t s);
