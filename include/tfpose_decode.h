@@ -198,7 +198,10 @@ TFPD_API int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int im
  *                  148 SMs) leaves SMs on which the latency-bound scoring / assembly kernels of the previous
  *                  batch run concurrently.
  *   "host_chunks"  frame chunks tfpd_decode_host pipelines H2D / decode / D2H over; 0 = automatic.
- *   "k1_l2"        bit 0: prefetch the input into L2 up front, bit 1: evict-first stores (default 2).  */
+ *   "k1_l2"        bit 0: prefetch the input into L2 up front, bit 1: evict-first stores (default 2).
+ *   "pow2_path"    kernels for power-of-two upsample factors other than the x4 fast path (2, 8, 16): 1 automatic
+ *                  (default), 0 the general kernels, 2 fused, 3 fused with a separate horizontal pass, 4 unfused
+ *                  polyphase passes.  All give the same maps up to the order of additions; for tests and tuning.  */
 TFPD_API int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value);
 
 /* Introspection used by the tests and the bench. */

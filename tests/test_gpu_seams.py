@@ -182,6 +182,48 @@ def test_general_resize_area_ratios(cuda, oracle, ratio):
     dec.close()
 
 
+@pytest.mark.parametrize("ratio", [2, 8, 16])
+def test_pow2_paths_agree(cuda, ratio):
+    """Power-of-two factors other than 4 have three kernel variants (fused, fused after a separate
+    horizontal pass, unfused polyphase passes) that add in the same order: identical dense tensors and
+    tables; the general kernels (25-tap passes over the upsampled map) agree within the map tolerance.
+    Odd tile edges: w = 27 gives W*19 not divisible by the tile, and for ratio 2 by 4."""
+    import torch
+    from helpers import table_tuples as _tt
+
+    def table_tuples(r):
+        return [_tt(r, i) for i in range(3)]
+    for (h, w) in ((23, 27), (46, 54)):
+        x = torch.from_numpy(synth.synth_batch(3, h, w, config_id=2, first_frame=7)).cuda()
+        H, W = h * ratio, w * ratio
+        dec = tp.PoseDecoder(max_batch=3, max_upsample=(H, W), max_peaks=4096, max_cands=8192)
+        outs = {}
+        for path in (2, 3, 4, 0, 1):
+            dec.set_option("pow2_path", path)
+            dense = tuple(torch.empty((3, H, W, c), device="cuda") for c in (19, 38, 19))
+            res = dec.decode(x, (H, W), dense=dense)
+            res_min = dec.decode(x, (H, W))
+            assert np.array_equal(res.info, res_min.info), (ratio, path)
+            assert table_tuples(res) == table_tuples(res_min), (ratio, path)
+            outs[path] = (res, [d.cpu().numpy() for d in dense])
+        ref_res, ref_dense = outs[2]
+        for path in (3, 4, 1):
+            res, dense = outs[path]
+            for a, b in zip(dense, ref_dense):
+                assert np.array_equal(a, b), (ratio, path)
+            assert table_tuples(res) == table_tuples(ref_res), (ratio, path)
+        g_res, g_dense = outs[0]
+        assert np.array_equal(g_dense[0], ref_dense[0]) and np.array_equal(g_dense[1], ref_dense[1])
+        # the smoothed values differ in the last bits between a 25-tap and a polyphase sum, so a plateau pixel
+        # may be a maximum on one side only; above the peak threshold every such pixel is counted in near_ties
+        a, b = g_dense[2][..., :18], ref_dense[2][..., :18]
+        differ = ((a != 0) != (b != 0)) & (np.maximum(a, b) > 0.1)
+        assert differ.sum() <= int(g_res.info["near_ties"].sum()) + int(ref_res.info["near_ties"].sum())
+        both = (g_dense[2] != 0) & (ref_dense[2] != 0)
+        assert rel_err(g_dense[2][both], ref_dense[2][both], ref_dense[2]) <= 1e-5
+        dec.close()
+
+
 def test_decode_host_matches_device_call(cuda):
     """tfpd_decode_host (host buffers, copies inside) == tfpd_decode_device on the same data."""
     import torch

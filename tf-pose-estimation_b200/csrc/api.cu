@@ -58,6 +58,7 @@ struct tfpd_ctx {
     // host-buffer calls: H2D, kernels and D2H of successive frame chunks run on three streams
     cudaStream_t st_h2d = nullptr, st_work = nullptr, st_d2h = nullptr;
     std::vector<cudaEvent_t> ev_chunk;  // 2 per chunk: input landed / chunk decoded
+    int pow2_path = 1;                  // 0 generic kernels, 1 automatic, 2 fused, 3 fused + separate h pass, 4 unfused
     int host_chunks = 0;                // 0 = automatic (TFPD_HOST_CHUNKS overrides: tuning knob)
     int k1_pr = 0;                      // TFPD_K1_PR
     int k1_grid = 0;                    // TFPD_K1_GRID: CTAs of the fused map kernel (0 = one per SM)
@@ -470,6 +471,9 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
     } else if (!strcmp(name, "host_chunks")) {
         if (value < 0 || value > 4096) return fail(ctx, TFPD_ERR_INVALID, "host_chunks=%d out of range", value);
         ctx->host_chunks = value;
+    } else if (!strcmp(name, "pow2_path")) {
+        if (value < 0 || value > 4) return fail(ctx, TFPD_ERR_INVALID, "pow2_path=%d out of range", value);
+        ctx->pow2_path = value;
     } else if (!strcmp(name, "k1_l2")) {
         if (value < 0 || value > 7) return fail(ctx, TFPD_ERR_INVALID, "k1_l2=%d out of range", value);
         ctx->k1_l2_knobs = value;
@@ -543,7 +547,7 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         src.shift = 2;
         src.H = H;
         frame_stride = (size_t)h * w * kNetC;
-    } else if (int log2f = pow2_factor(h, w, H, W, ctx->cfg.blur_ksize)) {
+    } else if (int log2f = ctx->pow2_path ? pow2_factor(h, w, H, W, ctx->cfg.blur_ksize) : 0) {
         // power-of-two replication other than the fused kernel's case: polyphase passes on the low-res rows
         if (ctx->poly_log2f != log2f) {
             const int F = 1 << log2f, pad = ctx->cfg.blur_ksize / 2, R = (pad + F - 1) / F, T = 2 * R + 1;
@@ -567,6 +571,7 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         const size_t px = (size_t)N * H * W;
         CUDA_TRY(ctx, ctx->gen_buf.reserve(((size_t)N * h * W + px) * kHeatC * 4));
         int r = launch_pow2_maps(net_out, N, h, w, log2f, (const float *)ctx->poly_buf.p, ctx->poly_host.data(), ctx->poly_T,
+                                 ctx->pow2_path,
                                  want_dense ? dense->heat_up : nullptr, want_dense ? dense->paf_up : nullptr,
                                  want_dense ? dense->peaks : nullptr, (float *)ctx->gen_buf.p, ws, ctx->cfg.thresh_heat, s);
         if (r < 0) return fail(ctx, TFPD_ERR_CUDA, "power-of-two map kernels failed: %s", cudaGetErrorString(cudaGetLastError()));

@@ -414,7 +414,7 @@ int launch_generic_maps(const float *X, int N, int h, int w, int H, int W, const
 // over the LOW-RES rows (one per h rows, not per H) with per-phase cell weights, then a vertical pass with per-phase
 // row weights (T = 2*ceil(pad/F)+1 taps instead of ksize).  heat_up / paf_up are only materialised in dense mode.
 int launch_pow2_maps(const float *X, int N, int h, int w, int log2f, const float *d_wp, const float *h_wp, int T,
-                     float *heat_up, float *paf_up, float *peaks, float *scratch, const Workspace &ws, float thr,
+                     int path, float *heat_up, float *paf_up, float *peaks, float *scratch, const Workspace &ws, float thr,
                      cudaStream_t s) {
     const int H = h << log2f, W = w << log2f;
     const size_t nh = (size_t)N * H * W * kHeatC, np = (size_t)N * H * W * kPafC;
@@ -432,12 +432,11 @@ int launch_pow2_maps(const float *X, int N, int h, int w, int log2f, const float
         launches += 2;
     }
     // the usual smoother sizes have a fully fused kernel; anything else takes three passes through HBM
-    const bool fused = N <= 65535 && h <= 65535 &&
+    const bool fused = path != 4 && N <= 65535 && h <= 65535 &&
                        ((log2f == 3 && T == 5) || (log2f == 1 && T == 13) || (log2f == 4 && T == 3) || (log2f == 2 && T == 7));
     if (fused) {
-        static const int hb_knob = getenv("TFPD_POW2_HB") ? atoi(getenv("TFPD_POW2_HB")) : -1;
         // measured (tools/generic_ratio_times.py): the separate horizontal pass pays for F = 2 and 16, not for F = 8
-        const bool use_hb = hb_knob >= 0 ? hb_knob != 0 : log2f != 3;
+        const bool use_hb = path == 2 ? false : (path == 3 ? true : log2f != 3);
         if (use_hb) {
             k_hblur_lowres<<<grid_for(nhb), 256, 0, s>>>(X, N, h, w, log2f, d_wp, T, hb);
             ++launches;

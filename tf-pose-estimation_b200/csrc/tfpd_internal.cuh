@@ -110,7 +110,7 @@ int launch_generic_maps(const float *X, int N, int h, int w, int H, int W, const
                         float *heat_up, float *paf_up, float *peaks, float *scratch, const Workspace &ws, float thr,
                         cudaStream_t s);
 int launch_pow2_maps(const float *X, int N, int h, int w, int log2f, const float *d_wp, const float *h_wp, int T,
-                     float *heat_up, float *paf_up, float *peaks, float *scratch, const Workspace &ws, float thr,
+                     int path, float *heat_up, float *paf_up, float *peaks, float *scratch, const Workspace &ws, float thr,
                      cudaStream_t s);
 int launch_scan_dense_peaks(const float *peaks, const float *heat, int N, int H, int W, float thresh,
                             const Workspace &ws, cudaStream_t s);

@@ -17,6 +17,8 @@ for ratio in ratios:
     H, W = h * ratio, w * ratio
     dec = tp.PoseDecoder(max_batch=B, max_upsample=(H, W), max_peaks=4096, max_cands=8192)
     dec.set_profiling(True)
+    if os.environ.get("POW2_PATH"):
+        dec.set_option("pow2_path", int(os.environ["POW2_PATH"]))
     dense = tuple(torch.empty((B, H, W, c), device="cuda") for c in (19, 38, 19))
     for mode, d in (("dense", dense), ("minimal", None)):
         acc = []
