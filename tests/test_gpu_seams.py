@@ -182,7 +182,7 @@ def test_general_resize_area_ratios(cuda, oracle, ratio):
     dec.close()
 
 
-@pytest.mark.parametrize("ratio", [2, 8, 16])
+@pytest.mark.parametrize("ratio", [1, 2, 8, 16])
 def test_pow2_paths_agree(cuda, ratio):
     """Power-of-two factors other than 4 have three kernel variants (fused, fused after a separate
     horizontal pass, unfused polyphase passes) that add in the same order: identical dense tensors and

@@ -132,14 +132,14 @@ int next_pow2(int v) {
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 // log2 of the upsample factor when (h,w)->(H,W) is a power-of-two replication the polyphase path handles
-// (factor 2..16, at most 33 cell taps), else 0
+// (factor 1..16, at most 33 cell taps), else -1
 int pow2_factor(int h, int w, int H, int W, int ksize) {
-    for (int l = 1; l <= 4; ++l)
+    for (int l = 0; l <= 4; ++l)
         if (H == (h << l) && W == (w << l)) {
             const int F = 1 << l, R = (ksize / 2 + F - 1) / F;
-            return (2 * R + 1 <= 33) ? l : 0;
+            return (2 * R + 1 <= 33) ? l : -1;
         }
-    return 0;
+    return -1;
 }
 
 Thresholds thresholds_of(const tfpd_config &c) {
@@ -547,7 +547,7 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         src.shift = 2;
         src.H = H;
         frame_stride = (size_t)h * w * kNetC;
-    } else if (int log2f = ctx->pow2_path ? pow2_factor(h, w, H, W, ctx->cfg.blur_ksize) : 0) {
+    } else if (const int log2f = ctx->pow2_path ? pow2_factor(h, w, H, W, ctx->cfg.blur_ksize) : -1; log2f >= 0) {
         // power-of-two replication other than the fused kernel's case: polyphase passes on the low-res rows
         if (ctx->poly_log2f != log2f) {
             const int F = 1 << log2f, pad = ctx->cfg.blur_ksize / 2, R = (pad + F - 1) / F, T = 2 * R + 1;

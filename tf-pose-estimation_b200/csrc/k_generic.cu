@@ -205,6 +205,23 @@ __global__ void __launch_bounds__(256) k_replicate_pow2(const float *__restrict_
     replicate_rows<kPafC, kHeatC>(s_row, paf_up + row0 * pl, (int)(pl >> 2), F, s, pl);
 }
 
+// same replication one element per thread, for row lengths that are not a multiple of four floats
+__global__ void k_replicate_scalar(const float *__restrict__ X, int N, int h, int w, int s, int c_off, int C,
+                                   float *__restrict__ out) {
+    const int H = h << s, W = w << s;
+    const size_t total = (size_t)N * H * W * C;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (size_t)gridDim.x * blockDim.x) {
+        const int c = (int)(idx % C);
+        size_t pix = idx / C;
+        const int x = (int)(pix % W);
+        pix /= W;
+        const int y = (int)(pix % H);
+        const size_t n = pix / H;
+        out[idx] = __ldg(X + ((n * h + (y >> s)) * w + (x >> s)) * kNetC + c_off + c);
+    }
+}
+
 // Smoother (both polyphase passes) + 3x3 NMS + peak records in one kernel: a CTA owns kTileX upsampled columns and a
 // strip of low-res rows of one frame and walks down the strip.  One thread per (column, channel):
 //   * per low-res row it forms ONE horizontally smoothed value from T cells of the network output (its x-phase
@@ -426,14 +443,15 @@ int launch_pow2_maps(const float *X, int N, int h, int w, int log2f, const float
             k_replicate_pow2<<<dim3(kRepSplit, h, N), 256, w * kNetC * 4, s>>>(X, h, w, log2f, heat_up, paf_up);
             launches -= 1;
         } else {
-            k_resize_area<<<grid_for(nh), 256, 0, s>>>(X, N, h, w, 0, kHeatC, heat_up, H, W);
-            k_resize_area<<<grid_for(np), 256, 0, s>>>(X, N, h, w, kHeatC, kPafC, paf_up, H, W);
+            k_replicate_scalar<<<grid_for(nh), 256, 0, s>>>(X, N, h, w, log2f, 0, kHeatC, heat_up);
+            k_replicate_scalar<<<grid_for(np), 256, 0, s>>>(X, N, h, w, log2f, kHeatC, kPafC, paf_up);
         }
         launches += 2;
     }
     // the usual smoother sizes have a fully fused kernel; anything else takes three passes through HBM
     const bool fused = path != 4 && N <= 65535 && h <= 65535 &&
-                       ((log2f == 3 && T == 5) || (log2f == 1 && T == 13) || (log2f == 4 && T == 3) || (log2f == 2 && T == 7));
+                       ((log2f == 3 && T == 5) || (log2f == 1 && T == 13) || (log2f == 4 && T == 3) || (log2f == 2 && T == 7) ||
+                        (log2f == 0 && T == 25));
     if (fused) {
         // measured (tools/generic_ratio_times.py): the separate horizontal pass pays for F = 2 and 16, not for F = 8
         const bool use_hb = path == 2 ? false : (path == 3 ? true : log2f != 3);
@@ -445,6 +463,7 @@ int launch_pow2_maps(const float *X, int N, int h, int w, int log2f, const float
         if (log2f == 3) launch_pow2_fused<3, 5>(X, hbp, h_wp, d_wp, peaks, N, h, w, thr, ws, s);
         else if (log2f == 1) launch_pow2_fused<1, 13>(X, hbp, h_wp, d_wp, peaks, N, h, w, thr, ws, s);
         else if (log2f == 4) launch_pow2_fused<4, 3>(X, hbp, h_wp, d_wp, peaks, N, h, w, thr, ws, s);
+        else if (log2f == 0) launch_pow2_fused<0, 25>(X, hbp, h_wp, d_wp, peaks, N, h, w, thr, ws, s);
         else launch_pow2_fused<2, 7>(X, hbp, h_wp, d_wp, peaks, N, h, w, thr, ws, s);
         return cudaGetLastError() == cudaSuccess ? launches + 1 : -1;
     }

@@ -12,7 +12,7 @@ from tfpose_b200 import synth
 
 h, w, B = 46, 54, 16
 x = torch.from_numpy(synth.synth_batch(B, h, w, config_id=2)).cuda()
-ratios = [int(a) for a in sys.argv[1:]] or [4, 8, 2, 16, 3]
+ratios = [int(a) for a in sys.argv[1:]] or [4, 8, 2, 16, 1, 3]
 for ratio in ratios:
     H, W = h * ratio, w * ratio
     dec = tp.PoseDecoder(max_batch=B, max_upsample=(H, W), max_peaks=4096, max_cands=8192)
