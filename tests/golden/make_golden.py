@@ -215,9 +215,49 @@ def coco_golden(est_mod):
     print("coco writers:", len(recs), "humans x 3 image sizes")
 
 
+class _Msg:
+    """Stand-in for a genpy message class: attributes are whatever the caller sets, list fields start empty."""
+    _lists = ()
+
+    def __init__(self):
+        for n in self._lists:
+            setattr(self, n, [])
+
+
+def ros_golden(est_mod):
+    """Result of the reference's own humans_to_msg (scripts/broadcaster_ros.py:19-36) for random humans, with
+    rospy / cv_bridge / the generated tfpose_ros.msg classes stubbed (plain attribute bags)."""
+    class Persons(_Msg):
+        _lists = ("persons",)
+
+    class Person(_Msg):
+        _lists = ("body_part",)
+
+    class BodyPartElm(_Msg):
+        pass
+
+    names = ["rospy", "rospkg", "cv_bridge", "std_msgs", "std_msgs.msg", "sensor_msgs", "sensor_msgs.msg",
+             "tfpose_ros", "tfpose_ros.msg", "tf_pose", "tf_pose.estimator", "tf_pose.networks"]
+    stubs = {n: _Stub(n) for n in names}
+    stubs["tfpose_ros.msg"].Persons, stubs["tfpose_ros.msg"].Person = Persons, Person
+    stubs["tfpose_ros.msg"].BodyPartElm = BodyPartElm
+    ros = load_reference_module(os.path.join(REF, "scripts/broadcaster_ros.py"), "ref_broadcaster_ros", stubs)
+    humans = random_humans(est_mod, n=16, seed=31)
+    msg = ros.humans_to_msg(humans)
+    rec = {"humans": [{"parts": {str(k): [bp.x, bp.y, bp.score] for k, bp in hm.body_parts.items()},
+                       "score": hm.score} for hm in humans],
+           "persons": [[[b.part_id, b.x, b.y, b.confidence] for b in p.body_part] for p in msg.persons]}
+    with open(os.path.join(HERE, "ros_persons.json"), "w") as fh:
+        json.dump(rec, fh)
+    print("ros persons:", len(rec["persons"]), "persons,", sum(len(p) for p in rec["persons"]), "body parts")
+
+
 def main():
     if len(sys.argv) > 1 and sys.argv[1] == "boxes":
         boxes_golden(reference_estimator("asbuilt"))
+        return
+    if len(sys.argv) > 1 and sys.argv[1] == "ros":
+        ros_golden(reference_estimator("asbuilt"))
         return
     if len(sys.argv) > 1 and sys.argv[1] == "coco":
         coco_golden(reference_estimator("asbuilt"))

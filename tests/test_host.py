@@ -302,3 +302,69 @@ def test_coco_items_from_table_equal_the_per_human_writer():
     assert got == want
     kp = writers.table_to_keypoint_array(res, 1)
     assert kp.shape == (int(info["n_humans"][1]), 18, 3)
+
+
+def test_humans_to_msg_matches_reference_golden():
+    """tests/golden/ros_persons.json holds what the reference's own humans_to_msg
+    (scripts/broadcaster_ros.py:19-36) produced for random humans (make_golden.py ros)."""
+    import json
+    from tfpose_b200 import writers
+    rec = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ros_persons.json")))
+    humans = []
+    for i, h in enumerate(rec["humans"]):
+        hm = tp.Human([])
+        for k, (x, y, s) in h["parts"].items():
+            hm.body_parts[int(k)] = tp.BodyPart('%d-%s' % (i, k), int(k), x, y, s)
+        hm.score = h["score"]
+        humans.append(hm)
+    msg = writers.humans_to_msg(humans)
+    got = [[[b.part_id, b.x, b.y, b.confidence] for b in p.body_part] for p in msg.persons]
+    assert got == rec["persons"]
+    assert msg.image_w == 0 and msg.image_h == 0 and msg.header is None
+
+    class P:                                                 # caller-supplied message classes are used as given
+        def __init__(self):
+            self.persons = []
+
+    class Q:
+        def __init__(self):
+            self.body_part = []
+
+    class B:
+        pass
+    msg2 = writers.humans_to_msg(humans, (P, Q, B))
+    assert isinstance(msg2, P) and isinstance(msg2.persons[0], Q) and isinstance(msg2.persons[0].body_part[0], B)
+    assert [[[b.part_id, b.x, b.y, b.confidence] for b in p.body_part] for p in msg2.persons] == rec["persons"]
+
+
+def test_persons_records_from_table_equal_humans_to_msg():
+    """The packed BodyPartElm records built from the tfpd_human table hold what humans_to_msg over the Human
+    objects of the same table holds, after the float32 narrowing ROS serialisation applies."""
+    from tfpose_b200 import writers, _lib
+    from tfpose_b200.decoder import DecodeResult
+    rng = np.random.default_rng(9)
+    N, MH, H, W = 2, 5, 184, 216
+    info = np.zeros(N, _lib.INFO_DTYPE)
+    table = np.zeros((N, MH), _lib.HUMAN_DTYPE)
+    for i in range(N):
+        info["n_humans"][i] = MH - i
+        for j in range(int(info["n_humans"][i])):
+            present = rng.random(18) < 0.6
+            if j == 1:
+                present[:] = False
+            table["cid"][i, j] = np.where(present, rng.integers(0, 300, 18), -1)
+            table["x"][i, j] = np.where(present, rng.integers(0, W, 18), -1)
+            table["y"][i, j] = np.where(present, rng.integers(0, H, 18), -1)
+            table["part_score"][i, j] = np.where(present, rng.random(18), 0).astype(np.float32)
+            table["score"][i, j] = rng.random()
+    res = DecodeResult(info, table, H, W)
+    assert writers.BODY_PART_ELM_DTYPE.itemsize == 16
+    for i in range(N):
+        rec, counts = writers.persons_records_from_table(res, i)
+        msg = writers.humans_to_msg(res.humans(i))
+        assert counts.tolist() == [len(p.body_part) for p in msg.persons]
+        flat = [b for p in msg.persons for b in p.body_part]
+        assert rec["part_id"].tolist() == [b.part_id for b in flat]
+        assert rec["x"].tolist() == [float(np.float32(b.x)) for b in flat]
+        assert rec["y"].tolist() == [float(np.float32(b.y)) for b in flat]
+        assert rec["confidence"].tolist() == [float(np.float32(b.confidence)) for b in flat]

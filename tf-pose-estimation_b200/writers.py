@@ -8,6 +8,10 @@
   17-keypoint permutation of ariel_run.py:22-28,73-86 (``translate_op_top_coco`` there).
 * ``coco_items_from_table`` -- the same records built straight from the ``tfpd_human`` tables a decode
   returns (no ``Human`` objects in between), for whole batches.
+* ``humans_to_msg`` -- scripts/broadcaster_ros.py:19-36: ``Persons`` / ``Person`` / ``BodyPartElm`` objects
+  (msg/*.msg).  rospy's generated classes are passed in when ROS is there; plain stand-ins with the same
+  fields otherwise.  ``persons_records_from_table`` gives the same content as one packed array per frame
+  (``BODY_PART_ELM_DTYPE`` = the 16-byte little-endian wire layout of ``BodyPartElm``).
 """
 import numpy as np
 
@@ -98,3 +102,75 @@ def table_to_keypoint_array(result, frame):
     out[..., 1] = np.where(ok, rows["y"], 0)
     out[..., 2] = np.where(ok, rows["part_score"], 0)
     return out
+
+
+class _Msg:
+    """Field bag shaped like a genpy message (used when the ROS message classes are not importable)."""
+    __slots__ = ()
+
+    def __repr__(self):
+        return "%s(%s)" % (type(self).__name__, ", ".join("%s=%r" % (n, getattr(self, n)) for n in self.__slots__))
+
+
+class BodyPartElm(_Msg):                 # msg/BodyPartElm.msg
+    __slots__ = ("part_id", "x", "y", "confidence")
+
+    def __init__(self):
+        self.part_id, self.x, self.y, self.confidence = 0, 0.0, 0.0, 0.0
+
+
+class Person(_Msg):                      # msg/Person.msg
+    __slots__ = ("body_part",)
+
+    def __init__(self):
+        self.body_part = []
+
+
+class Persons(_Msg):                     # msg/Persons.msg
+    __slots__ = ("persons", "image_w", "image_h", "header")
+
+    def __init__(self):
+        self.persons, self.image_w, self.image_h, self.header = [], 0, 0, None
+
+
+def humans_to_msg(humans, msg_types=None):
+    """scripts/broadcaster_ros.py:19-36.  msg_types = (Persons, Person, BodyPartElm) classes of
+    ``tfpose_ros.msg`` when running under ROS; the caller sets image_w / image_h / header (:57-59)."""
+    P, Q, B = msg_types if msg_types is not None else (Persons, Person, BodyPartElm)
+    persons = P()
+    for human in humans:
+        person = Q()
+        for k in human.body_parts:
+            body_part = human.body_parts[k]
+            m = B()
+            m.part_id = body_part.part_idx
+            m.x = body_part.x
+            m.y = body_part.y
+            m.confidence = body_part.score
+            person.body_part.append(m)
+        persons.persons.append(person)
+    return persons
+
+
+# uint32 part_id, float32 x, float32 y, float32 confidence: the serialised form of one BodyPartElm
+BODY_PART_ELM_DTYPE = np.dtype([("part_id", "<u4"), ("x", "<f4"), ("y", "<f4"), ("confidence", "<f4")])
+
+
+def persons_records_from_table(result, frame):
+    """(records, counts) of one frame straight from the ``tfpd_human`` table: ``records`` is a packed
+    BODY_PART_ELM_DTYPE array with the body parts of all persons in ``humans_to_msg`` order (person by
+    person, ascending part index), ``counts[i]`` the number of parts of person i.  x, y are the float32
+    roundings of the Python floats ``px / W``, ``py / H`` the message fields get when serialised."""
+    n = int(result.info["n_humans"][frame])
+    rows = result.table[frame][:n]
+    ok = rows["cid"] >= 0
+    keep = ok.any(axis=1)                                  # estimate_paf's is_added (estimator.py:293)
+    rows, ok = rows[keep], ok[keep]
+    counts = ok.sum(axis=1).astype(np.int64)
+    rec = np.empty(int(counts.sum()), BODY_PART_ELM_DTYPE)
+    hi, pi = np.nonzero(ok)
+    rec["part_id"] = pi
+    rec["x"] = (rows["x"][hi, pi].astype(np.float64) / result.W).astype(np.float32)
+    rec["y"] = (rows["y"][hi, pi].astype(np.float64) / result.H).astype(np.float32)
+    rec["confidence"] = rows["part_score"][hi, pi]
+    return rec, counts
