@@ -224,6 +224,34 @@ def test_pow2_paths_agree(cuda, ratio):
         dec.close()
 
 
+@pytest.mark.parametrize("ratio", [1, 2, 3, 4, 8])
+def test_dense_outputs_stay_in_bounds(cuda, ratio):
+    """Guard words around the three dense output tensors survive a decode on every map path (the x4 TMA
+    kernel, the fused polyphase kernels, the general kernels), with frame sizes that leave partial tiles."""
+    import torch
+    for (h, w, N) in ((23, 27, 3), (46, 54, 2), (5, 3, 1)):
+        H, W = h * ratio, w * ratio
+        x = torch.from_numpy(synth.synth_batch(N, max(h, 12), max(w, 12), config_id=2)[:, :h, :w].copy()).cuda()
+        dec = tp.PoseDecoder(max_batch=N, max_upsample=(H, W), max_peaks=4096, max_cands=8192)
+        guard = 1024
+        sizes = [N * H * W * c for c in (19, 38, 19)]
+        flat = torch.full((sum(sizes) + 4 * guard + 16,), -12345.0, device="cuda")
+        dense, spans, off = [], [], guard
+        for sz, c in zip(sizes, (19, 38, 19)):
+            dense.append(flat[off:off + sz].view(N, H, W, c))
+            spans.append((off, off + sz))
+            off = (off + sz + guard + 3) // 4 * 4          # the C-ABI wants 16-byte aligned tensors
+        dec.decode(x, (H, W), dense=tuple(dense))
+        torch.cuda.synchronize()
+        inside = torch.zeros(flat.numel(), dtype=torch.bool, device="cuda")
+        for a, b in spans:
+            inside[a:b] = True
+        assert bool((flat[~inside] == -12345.0).all()), (ratio, h, w)
+        for d in dense:
+            assert not bool((d == -12345.0).any()), (ratio, h, w)
+        dec.close()
+
+
 def test_decode_host_matches_device_call(cuda):
     """tfpd_decode_host (host buffers, copies inside) == tfpd_decode_device on the same data."""
     import torch
