@@ -251,6 +251,12 @@ def run_ours(args, rank, world, local_rank):
     for d in decs[1:]:
         d.set_profiling(True)
         d.set_option("k1_ctas", args.k1_ctas)
+    if int(os.environ.get("K1_TURNSTILE", "1")):
+        for d in decs:
+            d.set_option("k1_turnstile", 1)
+    if os.environ.get("EARLY_FETCH"):
+        for d in decs:
+            d.set_option("early_fetch", int(os.environ["EARLY_FETCH"]))
     if args.pipe_streams > 1:
         streams = [stream] + [torch.cuda.Stream(dev) for _ in range(n_pipe - 1)]
     else:
@@ -268,7 +274,7 @@ def run_ours(args, rank, world, local_rank):
         near_ties += int(res.info["near_ties"].sum())
         k1_ms_pipe.append(d.stage_ms()[0])
 
-    def run_pipelined(steps, count):
+    def run_pipelined(steps, count, with_dense=True):
         inflight = []
         for i in range(steps):
             j = i % n_pipe
@@ -278,7 +284,8 @@ def run_ours(args, rank, world, local_rank):
                     collect(d)
                 else:
                     d.fetch()
-            decs[j].decode_async(x_dev[i % N_INPUT_SETS], (H, W), dense=denses[j], stream=streams[j])
+            decs[j].decode_async(x_dev[i % N_INPUT_SETS], (H, W), dense=denses[j] if with_dense else None,
+                                 stream=streams[j])
             inflight.append(decs[j])
         for d in inflight:
             if count:
@@ -297,11 +304,22 @@ def run_ours(args, rank, world, local_rank):
     ms_total = max_over_ranks(ev0.elapsed_time(ev1))
     ms_per_step = ms_total / args.steps
     value = world * B * args.steps / (ms_total * 1e-3)
+
+    # ---- the same pipeline in minimal mode (no dense tensors written; the fast path of SURVEY.md 8d) ----
+    run_pipelined(max(args.warmup, n_pipe), False, with_dense=False)
+    barrier()
+    ev0.record(stream)
+    run_pipelined(args.steps, False, with_dense=False)
+    for st_ in streams[1:]:
+        stream.wait_stream(st_)
+    ev1.record(stream)
+    barrier()
+    value_min_pipe = world * B * args.steps / (max_over_ranks(ev0.elapsed_time(ev1)) * 1e-3)
     for d in decs[1:]:
         d.close()
     del denses
 
-    # ---- minimal mode (no dense tensors written), device-resident ----
+    # ---- minimal mode, one call at a time, device-resident ----
     for i in range(args.warmup):
         dec.decode(x_dev[i % N_INPUT_SETS], (H, W))
     barrier()
@@ -413,6 +431,7 @@ def run_ours(args, rank, world, local_rank):
                          "k2_limbs": stage_acc[2] / args.steps, "k3_assemble": stage_acc[3] / args.steps},
             "value_one_call_at_a_time": value_serial, "k1_ms_in_pipelined_region": float(np.mean(k1_ms_pipe)),
             "value_minimal_mode": value_min,
+            "value_minimal_mode_pipelined": value_min_pipe,
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "call": "PoseDecoder.decode_host_async + fetch (tfpd_decode_host_async / tfpd_fetch_humans): pinned host input -> "
                             "human tables on host, two contexts alternating, dense maps left on device"},

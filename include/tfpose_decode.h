@@ -146,7 +146,8 @@ TFPD_API int tfpd_decode_host_async(tfpd_ctx *ctx, const float *net_out, int N, 
                            float *heat_up, float *paf_up, float *peaks);
 
 /* Waits for the decode, copies the per-frame tables to the host.
- * humans: [N * max_humans] (frame i at humans + i*max_humans), info: [N].  Either may be null.
+ * humans: [N * max_humans] (frame i at humans + i*max_humans; only the first info[i].n_humans records of a
+ * frame are written, the rest of the caller's block is left as it was), info: [N].  Either may be null.
  * Returns TFPD_ERR_CAPACITY if any frame overflowed a table (tables are still filled). */
 TFPD_API int tfpd_fetch_humans(tfpd_ctx *ctx, tfpd_human *humans, tfpd_frame_info *info);
 
@@ -199,6 +200,11 @@ TFPD_API int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int im
  *                  batch run concurrently.
  *   "host_chunks"  frame chunks tfpd_decode_host pipelines H2D / decode / D2H over; 0 = automatic.
  *   "k1_l2"        bit 0: prefetch the input into L2 up front, bit 1: evict-first stores (default 2).
+ *   "k1_turnstile" 1: the map kernels of all contexts on this device run one after the other (stream-ordered through
+ *                  a per-device event), whatever their streams.  With several contexts in flight this keeps a
+ *                  second HBM-bound map kernel from starting on the SMs "k1_ctas" leaves to the tail kernels.
+ *   "early_fetch"  when the tables start their way to the host: 0 in tfpd_fetch_humans (default), 1 right behind
+ *                  the last kernel on the same stream, 2 behind it on a side stream.
  *   "pow2_path"    kernels for power-of-two upsample factors other than the x4 fast path (2, 8, 16): 1 automatic
  *                  (default), 0 the general kernels, 2 fused, 3 fused with a separate horizontal pass, 4 unfused
  *                  polyphase passes.  All give the same maps up to the order of additions; for tests and tuning.  */

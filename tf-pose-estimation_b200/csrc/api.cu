@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <mutex>
 #include <vector>
 
 #include "tfpd_internal.cuh"
@@ -66,6 +67,12 @@ struct tfpd_ctx {
     unsigned long long *d_k1_times = nullptr;   // TFPD_K1_TIMES=1: per-CTA timestamps of the last K1 launch
     bool profiling = false, have_timing = false;
     cudaStream_t last_stream = nullptr;
+    bool result_enqueued = false;       // the D2H of the tables is already enqueued (on last_stream or st_res)
+    bool result_on_side = false;
+    int k1_turnstile = 0;               // serialise the map kernels of all contexts on this device
+    int early_fetch = 0;                // 0 copy the tables at fetch time, 1 right behind the last kernel, 2 on st_res
+    cudaStream_t st_res = nullptr;
+    cudaEvent_t ev_res = nullptr;
     int last_N = 0, last_H = 0, last_W = 0;
     int launches = 0;
     bool decoded = false, fetched = false, d2h_pending = false;
@@ -78,6 +85,9 @@ struct tfpd_ctx {
 };
 
 namespace {
+
+std::mutex g_k1_mu;
+cudaEvent_t g_k1_done[64] = {};        // per device: the last map kernel enqueued with k1_turnstile on
 
 int fail(tfpd_ctx *ctx, int code, const char *fmt, ...) {
     char buf[512];
@@ -206,6 +216,8 @@ void begin_call(tfpd_ctx *ctx, int N, int H, int W, cudaStream_t s) {
     ctx->decoded = false;
     ctx->fetched = false;
     ctx->d2h_pending = false;
+    ctx->result_enqueued = false;
+    ctx->result_on_side = false;
     ctx->getters_ready = false;
     ctx->have_timing = false;
 }
@@ -359,6 +371,8 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     cudaStreamCreateWithFlags(&ctx->st_h2d, cudaStreamNonBlocking);
     cudaStreamCreateWithFlags(&ctx->st_work, cudaStreamNonBlocking);
     cudaStreamCreateWithFlags(&ctx->st_d2h, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&ctx->st_res, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&ctx->ev_res, cudaEventDisableTiming);
     if (const char *e = getenv("TFPD_HOST_CHUNKS")) ctx->host_chunks = atoi(e);
     if (const char *e = getenv("TFPD_K1_L2")) ctx->k1_l2_knobs = atoi(e);
     if (const char *e = getenv("TFPD_K1_ROLES")) ctx->k1_roles = atoi(e);
@@ -380,7 +394,8 @@ void tfpd_destroy(tfpd_ctx *ctx) {
     for (auto &ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);
     for (auto &ev : ctx->ev_chunk) cudaEventDestroy(ev);
-    for (cudaStream_t st : {ctx->st_h2d, ctx->st_work, ctx->st_d2h})
+    if (ctx->ev_res) cudaEventDestroy(ctx->ev_res);
+    for (cudaStream_t st : {ctx->st_h2d, ctx->st_work, ctx->st_d2h, ctx->st_res})
         if (st) cudaStreamDestroy(st);
     if (ctx->ws_block) cudaFree(ctx->ws_block);
     if (ctx->h_result) cudaFreeHost(ctx->h_result);
@@ -471,6 +486,11 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
     } else if (!strcmp(name, "host_chunks")) {
         if (value < 0 || value > 4096) return fail(ctx, TFPD_ERR_INVALID, "host_chunks=%d out of range", value);
         ctx->host_chunks = value;
+    } else if (!strcmp(name, "k1_turnstile")) {
+        ctx->k1_turnstile = value != 0;
+    } else if (!strcmp(name, "early_fetch")) {
+        if (value < 0 || value > 2) return fail(ctx, TFPD_ERR_INVALID, "early_fetch=%d out of range", value);
+        ctx->early_fetch = value;
     } else if (!strcmp(name, "pow2_path")) {
         if (value < 0 || value > 4) return fail(ctx, TFPD_ERR_INVALID, "pow2_path=%d out of range", value);
         ctx->pow2_path = value;
@@ -500,6 +520,26 @@ int tfpd_last_stage_ms(tfpd_ctx *ctx, float stage_ms[4]) {
     if (!ctx->have_timing) return fail(ctx, TFPD_ERR_STATE, "no timing recorded (tfpd_set_profiling + decode first)");
     CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev[4]));
     for (int i = 0; i < 4; ++i) CUDA_TRY(ctx, cudaEventElapsedTime(&stage_ms[i], ctx->ev[i], ctx->ev[i + 1]));
+    return TFPD_OK;
+}
+
+// The tables of a decode start their way back to the page-locked result block as soon as the last kernel is
+// enqueued, so that tfpd_fetch_humans only has to wait for them (it used to start the copy itself).
+static int enqueue_result_copy(tfpd_ctx *ctx, int N, cudaStream_t s, bool at_fetch = false) {
+    if (!at_fetch && ctx->early_fetch == 0) return TFPD_OK;           // tfpd_fetch_humans starts the copy
+    cudaStream_t cs = s;
+    if (!at_fetch && ctx->early_fetch == 2) {                         // on a side stream, behind the last kernel
+        CUDA_TRY(ctx, cudaEventRecord(ctx->ev_res, s));
+        CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->st_res, ctx->ev_res, 0));
+        cs = ctx->st_res;
+        ctx->result_on_side = true;
+    }
+    const size_t info_bytes = align_up((size_t)ctx->cfg.max_batch * sizeof(tfpd_frame_info), 16);
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_result, ctx->d_info, (size_t)N * sizeof(tfpd_frame_info),
+                                  cudaMemcpyDeviceToHost, cs));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_result + info_bytes, ctx->ws.humans,
+                                  (size_t)N * ctx->ws.max_humans * sizeof(tfpd_human), cudaMemcpyDeviceToHost, cs));
+    ctx->result_enqueued = true;
     return TFPD_OK;
 }
 
@@ -536,7 +576,20 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         p.debug_roles = ctx->k1_roles;
         p.dbg_times = ctx->d_k1_times;
         p.force_pr = ctx->k1_pr;
-        int r = launch_k1_fused_f4(p, want_dense, ctx->k1_grid > 0 ? ctx->k1_grid : ctx->sm_count, s);
+        int r;
+        if (ctx->k1_turnstile) {
+            // One map kernel at a time per device, whatever the ctx and stream: it is HBM-bound, so two of them only
+            // dilute each other, and the early CTAs of the second one would take the SMs a reduced grid (k1_ctas)
+            // leaves to the scoring / assembly kernels of the batches before it.
+            std::lock_guard<std::mutex> lock(g_k1_mu);
+            cudaEvent_t &done = g_k1_done[ctx->cfg.device & 63];
+            if (done) CUDA_TRY(ctx, cudaStreamWaitEvent(s, done, 0));
+            else CUDA_TRY(ctx, cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+            r = launch_k1_fused_f4(p, want_dense, ctx->k1_grid > 0 ? ctx->k1_grid : ctx->sm_count, s);
+            if (r >= 0) CUDA_TRY(ctx, cudaEventRecord(done, s));
+        } else {
+            r = launch_k1_fused_f4(p, want_dense, ctx->k1_grid > 0 ? ctx->k1_grid : ctx->sm_count, s);
+        }
         if (r < 0) return fail(ctx, TFPD_ERR_CUDA, "k1_fused_f4 launch failed: %s", cudaGetErrorString(cudaGetLastError()));
         ctx->launches += r;
         src.base = net_out;
@@ -635,6 +688,7 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
     begin_call(ctx, N, H, W, s);
     int rc = enqueue_decode(ctx, ctx->ws, net_out, N, h, w, H, W, s, want_dense ? dense : nullptr, ctx->profiling);
     if (rc != TFPD_OK) return rc;
+    if ((rc = enqueue_result_copy(ctx, N, s)) != TFPD_OK) return rc;
     ctx->decoded = true;
     return TFPD_OK;
 }
@@ -646,13 +700,12 @@ int tfpd_fetch_humans(tfpd_ctx *ctx, tfpd_human *humans, tfpd_frame_info *info) 
     const size_t info_bytes = align_up((size_t)ctx->cfg.max_batch * sizeof(tfpd_frame_info), 16);
     if (!ctx->fetched) {
         CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
-        // info for N frames and humans for N frames: two contiguous ranges of the result block
-        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_result, ctx->d_info, (size_t)N * sizeof(tfpd_frame_info),
-                                      cudaMemcpyDeviceToHost, ctx->last_stream));
-        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->h_result + info_bytes, ctx->ws.humans,
-                                      (size_t)N * ctx->ws.max_humans * sizeof(tfpd_human), cudaMemcpyDeviceToHost,
-                                      ctx->last_stream));
+        if (!ctx->result_enqueued) {
+            int rc = enqueue_result_copy(ctx, N, ctx->last_stream, true);
+            if (rc != TFPD_OK) return rc;
+        }
         CUDA_TRY(ctx, cudaStreamSynchronize(ctx->last_stream));
+        if (ctx->result_on_side) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->st_res));
         if (ctx->d2h_pending) {         // dense maps of a host-buffer call still on their way back
             CUDA_TRY(ctx, cudaStreamSynchronize(ctx->st_d2h));
             ctx->d2h_pending = false;
@@ -661,7 +714,14 @@ int tfpd_fetch_humans(tfpd_ctx *ctx, tfpd_human *humans, tfpd_frame_info *info) 
     }
     const tfpd_frame_info *hi = (const tfpd_frame_info *)ctx->h_result;
     if (info) memcpy(info, hi, (size_t)N * sizeof(tfpd_frame_info));
-    if (humans) memcpy(humans, ctx->h_result + info_bytes, (size_t)N * ctx->ws.max_humans * sizeof(tfpd_human));
+    if (humans) {                       // only the records that exist: the rest of the caller's block stays untouched
+        const tfpd_human *src = (const tfpd_human *)(ctx->h_result + info_bytes);
+        const size_t MH = (size_t)ctx->ws.max_humans;
+        for (int i = 0; i < N; ++i) {
+            const size_t n = (size_t)std::min(std::max(hi[i].n_humans, 0), (int)MH);
+            if (n) memcpy(humans + i * MH, src + i * MH, n * sizeof(tfpd_human));
+        }
+    }
     const int ovf = TFPD_FLAG_PEAK_OVERFLOW | TFPD_FLAG_CAND_OVERFLOW | TFPD_FLAG_ROW_OVERFLOW | TFPD_FLAG_HUMAN_OVERFLOW;
     for (int i = 0; i < N; ++i)
         if (hi[i].flags & ovf)
@@ -801,6 +861,7 @@ int tfpd_decode_host_async(tfpd_ctx *ctx, const float *net_out, int N, int h, in
             CUDA_TRY(ctx, cudaMemcpyAsync(peaks + o19, d.peaks, (size_t)n * fpx * kHeatC * 4, cudaMemcpyDeviceToHost, ctx->st_d2h));
         }
     }
+    if (int rc = enqueue_result_copy(ctx, N, ctx->st_work)) return rc;
     ctx->decoded = true;
     ctx->d2h_pending = want_dense;
     return TFPD_OK;
@@ -840,6 +901,7 @@ int tfpd_process_paf_device(tfpd_ctx *ctx, int p1, int p2, int p3, const float *
     src.H = h1;
     int rc = run_tail(ctx, ctx->ws, 1, src, (size_t)p1 * p2 * kPafC, s, ctx->profiling);
     if (rc != TFPD_OK) return rc;
+    if ((rc = enqueue_result_copy(ctx, 1, s)) != TFPD_OK) return rc;
     ctx->decoded = true;
     return 0;
 }
