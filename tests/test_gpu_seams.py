@@ -371,7 +371,8 @@ def test_tuning_options_do_not_change_results(cuda):
     xd = torch.from_numpy(x).cuda()
     dec = tp.PoseDecoder(max_batch=6, max_upsample=(184, 216))
     outs = []
-    for name, val in (("k1_ctas", 0), ("k1_ctas", 128), ("k1_ctas", 7), ("k1_l2", 0), ("k1_l2", 3)):
+    for name, val in (("k1_ctas", 0), ("k1_ctas", 128), ("k1_ctas", 7), ("k1_l2", 0), ("k1_l2", 3),
+                      ("early_fetch", 1), ("early_fetch", 2), ("k1_turnstile", 1)):
         dec.set_option(name, val)
         dense = tuple(torch.full((6, 184, 216, c), 3.0, device="cuda") for c in (19, 38, 19))
         res = dec.decode(xd, (184, 216), dense=dense)
@@ -384,6 +385,36 @@ def test_tuning_options_do_not_change_results(cuda):
     with pytest.raises(tp.DecodeError):
         dec.set_option("k1_ctas", 100000)
     dec.close()
+
+
+def test_pipelined_contexts_with_turnstile(cuda):
+    """Three contexts on three streams, every table-copy mode, the map kernels serialised by the per-device
+    turnstile: each step returns what a plain synchronous decode of the same batch returns."""
+    import torch
+    from helpers import table_tuples
+    xs = [torch.from_numpy(synth.synth_batch(4, 46, 54, config_id=2, first_frame=900 + 4 * k)).cuda() for k in range(7)]
+    ref = tp.PoseDecoder(max_batch=4, max_upsample=(184, 216))
+    want = [[table_tuples(ref.decode(x, (184, 216)), i) for i in range(4)] for x in xs]
+    ref.close()
+    decs = [tp.PoseDecoder(max_batch=4, max_upsample=(184, 216)) for _ in range(3)]
+    streams = [torch.cuda.Stream() for _ in range(3)]
+    for j, d in enumerate(decs):
+        d.set_option("k1_turnstile", 1)
+        d.set_option("k1_ctas", 128)
+        d.set_option("early_fetch", j)
+    got, inflight = [], []
+    for k, x in enumerate(xs):
+        if len(inflight) == 3:
+            r = inflight.pop(0).fetch()
+            got.append([table_tuples(r, i) for i in range(4)])
+        decs[k % 3].decode_async(x, (184, 216), stream=streams[k % 3])
+        inflight.append(decs[k % 3])
+    for d in inflight:
+        r = d.fetch()
+        got.append([table_tuples(r, i) for i in range(4)])
+    assert got == want
+    for d in decs:
+        d.close()
 
 
 def test_async_host_call_matches_the_synchronous_one(cuda):
