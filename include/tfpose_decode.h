@@ -200,6 +200,9 @@ TFPD_API int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int im
  *                  batch run concurrently.
  *   "host_chunks"  frame chunks tfpd_decode_host pipelines H2D / decode / D2H over; 0 = automatic.
  *   "k1_l2"        bit 0: prefetch the input into L2 up front, bit 1: evict-first stores (default 2).
+ *   "graph"        1: tfpd_decode_device replays a CUDA graph of the whole decode (counter reset, the four kernels,
+ *                  the table copy) captured once per distinct argument set (x4 path, profiling off, up to 16
+ *                  cached): one launch instead of seven stream operations.  Same results.
  *   "k1_turnstile" 1: the map kernels of all contexts on this device run one after the other (stream-ordered through
  *                  a per-device event), whatever their streams.  With several contexts in flight this keeps a
  *                  second HBM-bound map kernel from starting on the SMs "k1_ctas" leaves to the tail kernels.

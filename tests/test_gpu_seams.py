@@ -372,7 +372,7 @@ def test_tuning_options_do_not_change_results(cuda):
     dec = tp.PoseDecoder(max_batch=6, max_upsample=(184, 216))
     outs = []
     for name, val in (("k1_ctas", 0), ("k1_ctas", 128), ("k1_ctas", 7), ("k1_l2", 0), ("k1_l2", 3),
-                      ("early_fetch", 1), ("early_fetch", 2), ("k1_turnstile", 1)):
+                      ("early_fetch", 1), ("early_fetch", 2), ("graph", 1), ("k1_turnstile", 1)):
         dec.set_option(name, val)
         dense = tuple(torch.full((6, 184, 216, c), 3.0, device="cuda") for c in (19, 38, 19))
         res = dec.decode(xd, (184, 216), dense=dense)
@@ -415,6 +415,40 @@ def test_pipelined_contexts_with_turnstile(cuda):
     assert got == want
     for d in decs:
         d.close()
+
+
+def test_graph_replay_matches_direct_launches(cuda):
+    """"graph" option: the decode captured once per argument set and replayed gives, for new data in the same
+    buffers, for dense and minimal mode and for more argument sets than the cache holds, what direct launches give."""
+    import torch
+    from helpers import table_tuples
+    ref = tp.PoseDecoder(max_batch=4, max_upsample=(184, 216))
+    dec = tp.PoseDecoder(max_batch=4, max_upsample=(184, 216))
+    dec.set_option("graph", 1)
+    st = torch.cuda.Stream()
+    xbuf = torch.empty((4, 46, 54, 57), device="cuda")
+    dense = tuple(torch.empty((4, 184, 216, c), device="cuda") for c in (19, 38, 19))
+    dense_ref = tuple(torch.empty_like(t) for t in dense)
+    for k in range(5):                                   # same buffers, new content: replay after the first step
+        xbuf.copy_(torch.from_numpy(synth.synth_batch(4, 46, 54, config_id=2, first_frame=40 * k)))
+        torch.cuda.synchronize()
+        for dn, dr in ((dense, dense_ref), (None, None)):
+            got = dec.decode(xbuf, (184, 216), dense=dn, stream=st if k % 2 else None)
+            want = ref.decode(xbuf, (184, 216), dense=dr)
+            assert [table_tuples(got, i) for i in range(4)] == [table_tuples(want, i) for i in range(4)]
+            assert got.info.tobytes() == want.info.tobytes()
+            if dn is not None:
+                torch.cuda.synchronize()
+                assert all(torch.equal(a, b) for a, b in zip(dn, dr))
+    assert dec.launch_count() == ref.launch_count()
+    others = [torch.from_numpy(synth.synth_batch(n, 46, 54, config_id=2, first_frame=7 * n)).cuda()
+              for n in (1, 2, 3, 4) for _ in range(5)]   # 20 argument sets > 16 cached graphs
+    for rep in range(2):
+        for x in others:
+            got, want = dec.decode(x, (184, 216)), ref.decode(x, (184, 216))
+            assert [table_tuples(got, i) for i in range(len(x))] == [table_tuples(want, i) for i in range(len(x))]
+    dec.close()
+    ref.close()
 
 
 def test_async_host_call_matches_the_synchronous_one(cuda):

@@ -37,6 +37,14 @@ print("decode, device input, minimal      %.1f us/frame" % timeit(lambda: dec.de
 print("   stages (ms):", ["%.4f" % v for v in dec.stage_ms()])
 print("decode, device input, dense maps   %.1f us/frame" % timeit(lambda: dec.decode(xd, (H, W), dense=dense)))
 print("   stages (ms):", ["%.4f" % v for v in dec.stage_ms()])
+dec.set_profiling(False)
+print("decode, minimal, profiling off     %.1f us/frame" % timeit(lambda: dec.decode(xd, (H, W))))
+dec.set_option("graph", 1)
+st = torch.cuda.Stream()
+print("decode, minimal, CUDA graph replay %.1f us/frame" % timeit(lambda: dec.decode(xd, (H, W), stream=st)))
+print("decode, dense, CUDA graph replay   %.1f us/frame" % timeit(lambda: dec.decode(xd, (H, W), dense=dense, stream=st)))
+dec.set_option("graph", 0)
+dec.set_profiling(True)
 print("decode_host, pinned input, minimal %.1f us/frame" % timeit(lambda: dec.decode_host(xp, (H, W))))
 print("decode + Human objects             %.1f us/frame" % timeit(lambda: dec.decode(xd, (H, W)).humans(0)))
 print("inference_from_output (numpy in, heatMat/pafMat out like inference()) %.1f us/frame"
