@@ -88,7 +88,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.002)
+            time.sleep(float(os.environ.get("BENCH_SAMPLE_PERIOD", "0.002")))
 
     def result(self):
         if not self.samples:

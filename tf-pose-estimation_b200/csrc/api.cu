@@ -579,7 +579,8 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         p.w = w;
         p.nchunks = (w + 55) / 56;
         p.chunk_cells = (w + p.nchunks - 1) / p.nchunks;
-        p.copy_nchunks = (w + 31) / 32;                     // <= 32 cells (29 KB staged) per copy item
+        static const int copy_cells = getenv("TFPD_K1_COPY_CELLS") ? atoi(getenv("TFPD_K1_COPY_CELLS")) : 32;
+        p.copy_nchunks = (w + copy_cells - 1) / copy_cells;  // <= 32 cells (29 KB staged) per copy item
         p.copy_chunk = (w + p.copy_nchunks - 1) / p.copy_nchunks;
         p.thresh = ctx->cfg.thresh_heat;
         memcpy(p.wp, ctx->wp, sizeof(p.wp));
