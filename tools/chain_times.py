@@ -39,7 +39,11 @@ for ctas in (0, 128):
                 per = e0.elapsed_time(e1) / R * 1e3
                 stages = np.array(dec.stage_ms()) * 1e3 if prof else None
                 dec.fetch()
-                print("k1_ctas %3d profiling %-5s graph %d %-7s %.1f us/step on the GPU%s"
-                      % (ctas, prof, graph, mode, per,
+                t0 = time.perf_counter()
+                for i in range(R):
+                    dec.decode(xs[i % 4], (H, W), dense=dense, stream=st)
+                sync_us = (time.perf_counter() - t0) / R * 1e6
+                print("k1_ctas %3d profiling %-5s graph %d %-7s %.1f us/step back to back, %.1f us per decode+fetch%s"
+                      % (ctas, prof, graph, mode, per, sync_us,
                          ("  stages %s sum %.1f" % (np.round(stages, 1), stages.sum())) if prof else ""))
             dec.close()
