@@ -550,7 +550,10 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
             u += it.nrows;
         }
         if (DENSE && tid == 0) bulk_wait_all();
-        if (p.dbg_times && tid == 0) p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
+        if (p.dbg_times && tid == 0) {
+            p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
+            p.dbg_times[3072 + blockIdx.x] = (unsigned long long)atomicAdd(&p.counters[0].k1_queue, 0);   // copy items handed out so far
+        }
         if (DENSE && (p.debug_roles & 2) && kHelperWarps > 0) {
             // The blur role of this CTA is done (measured: at ~65 % of the kernel) and its peak-row slots are
             // idle: the first kHelperWarps blur warps carve them into staging buffers and pull copy items from
