@@ -451,6 +451,43 @@ def test_graph_replay_matches_direct_launches(cuda):
     ref.close()
 
 
+def test_two_devices_in_one_process(cuda):
+    """One ctx per GPU driven by one thread per GPU of the SAME process (multi-GPU): per-device
+    state in the library (function attributes, the map-kernel turnstile) must not leak between devices."""
+    import threading
+    import torch
+    from helpers import table_tuples
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    x = synth.synth_batch(6, 46, 54, config_id=2, first_frame=1200)
+    out = {}
+
+    def work(dev):
+        try:
+            with torch.cuda.device(dev):
+                d = tp.PoseDecoder(max_batch=6, max_upsample=(184, 216), device=dev)
+                d.set_option("k1_turnstile", 1)
+                xd = torch.from_numpy(x).to("cuda:%d" % dev)
+                dense = tuple(torch.empty((6, 184, 216, c), device="cuda:%d" % dev) for c in (19, 38, 19))
+                res = None
+                for _ in range(5):
+                    res = d.decode(xd, (184, 216), dense=dense)
+                out[dev] = ([table_tuples(res, i) for i in range(6)], [t.cpu().numpy() for t in dense])
+                d.close()
+        except Exception as e:          # surfaced by the assertion below
+            out[dev] = e
+
+    threads = [threading.Thread(target=work, args=(dev,)) for dev in (0, 1)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not isinstance(out[0], Exception), out[0]
+    assert not isinstance(out[1], Exception), out[1]
+    assert out[0][0] == out[1][0]
+    assert all(np.array_equal(a, b) for a, b in zip(out[0][1], out[1][1]))
+
+
 def test_async_host_call_matches_the_synchronous_one(cuda):
     """tfpd_decode_host_async + tfpd_fetch_humans on two alternating contexts == tfpd_decode_host."""
     from helpers import table_tuples

@@ -637,12 +637,15 @@ int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t
     const size_t fixed = kCopyWarps * ns * (cslot + raw) + 24 * (kCopyWarps + kHelperWarps);
     K1Params q = p;
     q.copy_slots = ns;
-    static bool attr_set = false;
-    if (!attr_set) {
+    // function attributes are per device: one flag per device a ctx of this process may live on
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!attr_set[dev & 63]) {
         cudaFuncSetAttribute(k1_fused_f4<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
         cudaFuncSetAttribute(k1_fused_f4<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
         cudaFuncSetAttribute(k1_fused_f4<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(227 * 1024));
-        attr_set = true;
+        attr_set[dev & 63] = true;
     }
     // peak rows per TMA store group: as many as fit next to the copy warps' staging
     int pr = 4;

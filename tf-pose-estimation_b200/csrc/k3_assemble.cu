@@ -655,11 +655,13 @@ size_t assemble_smem_bytes(const Workspace &ws) {
 
 int launch_assemble(const Workspace &ws, int N, const Thresholds &th, cudaStream_t s) {
     size_t smem = assemble_smem_bytes(ws);
-    static size_t attr_smem = 0;
-    if (smem > 48 * 1024 && smem > attr_smem) {
+    static size_t attr_smem[64] = {};                  // per device: function attributes do not travel between devices
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (smem > 48 * 1024 && smem > attr_smem[dev & 63]) {
         if (cudaFuncSetAttribute(k_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
             return -1;
-        attr_smem = smem;
+        attr_smem[dev & 63] = smem;
     }
     k_assemble<<<N, kK3Threads, smem, s>>>(ws, th);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
