@@ -486,6 +486,13 @@ def test_two_devices_in_one_process(cuda):
     assert not isinstance(out[1], Exception), out[1]
     assert out[0][0] == out[1][0]
     assert all(np.array_equal(a, b) for a, b in zip(out[0][1], out[1][1]))
+    # API calls on a ctx of another device leave the caller's current device alone
+    torch.cuda.set_device(0)
+    d = tp.PoseDecoder(max_batch=6, max_upsample=(184, 216), device=1)
+    res = d.decode(torch.from_numpy(x).to("cuda:1"), (184, 216))
+    assert [table_tuples(res, i) for i in range(6)] == out[0][0]
+    d.close()
+    assert torch.cuda.current_device() == 0
 
 
 def test_async_host_call_matches_the_synchronous_one(cuda):

@@ -115,6 +115,24 @@ int fail(tfpd_ctx *ctx, int code, const char *fmt, ...) {
             return fail(ctx, TFPD_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e__));      \
     } while (0)
 
+// Makes the ctx's device current for the duration of an API call and puts the caller's device back afterwards.
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t err = cudaSuccess;
+    explicit DeviceGuard(int dev) {
+        err = cudaGetDevice(&prev);
+        if (err == cudaSuccess && prev != dev) err = cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+#define ON_CTX_DEVICE(ctx)                                                                          \
+    DeviceGuard device_guard__((ctx)->cfg.device);                                                  \
+    if (device_guard__.err != cudaSuccess)                                                          \
+        return fail(ctx, TFPD_ERR_CUDA, "cudaSetDevice(%d): %s", (ctx)->cfg.device, cudaGetErrorString(device_guard__.err))
+
 // Phi(x): scipy.stats.norm.cdf, used by Smoother.gauss_kernel (smoother.py:65)
 double std_normal_cdf(double x) { return 0.5 * erfc(-x / sqrt(2.0)); }
 
@@ -298,7 +316,8 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
         return fail(nullptr, TFPD_ERR_CUDA, "tfpd_create: no CUDA device (this library has no CPU path)");
     if (cfg->device < 0 || cfg->device >= ndev)
         return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: device %d of %d", cfg->device, ndev);
-    cudaError_t e = cudaSetDevice(cfg->device);
+    DeviceGuard device_guard__(cfg->device);
+    cudaError_t e = device_guard__.err;
     if (e != cudaSuccess) return fail(nullptr, TFPD_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
 
     tfpd_ctx *ctx = new tfpd_ctx();
@@ -397,7 +416,7 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
 
 void tfpd_destroy(tfpd_ctx *ctx) {
     if (!ctx) return;
-    cudaSetDevice(ctx->cfg.device);
+    DeviceGuard device_guard__(ctx->cfg.device);
     if (ctx->decoded) cudaStreamSynchronize(ctx->last_stream);
     for (auto &ev : ctx->ev)
         if (ev) cudaEventDestroy(ev);
@@ -442,7 +461,7 @@ int tfpd_draw_humans(tfpd_ctx *ctx, uint8_t *images, int on_device, int N, int i
         return fail(ctx, TFPD_ERR_INVALID, "draw_humans: bad dimensions");
     for (int i = 0; i < N; ++i)
         if (counts[i] < 0 || counts[i] > max_h) return fail(ctx, TFPD_ERR_INVALID, "draw_humans: counts[%d]=%d outside 0..%d", i, counts[i], max_h);
-    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    ON_CTX_DEVICE(ctx);
     cudaStream_t s = on_device ? (cudaStream_t)stream : ctx->st_work;
     const size_t npix = (size_t)N * img_h * img_w, cbytes = (size_t)N * max_h * 36 * 4;
     int rc = draw_reserve_ids(ctx, npix);
@@ -471,7 +490,7 @@ int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int img_w, void
     if (!ctx->decoded) return fail(ctx, TFPD_ERR_STATE, "draw_decoded: no decode on this ctx yet");
     if (!images || img_h < 1 || img_w < 1 || img_h > 32767 || img_w > 32767)
         return fail(ctx, TFPD_ERR_INVALID, "draw_decoded: bad argument");
-    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    ON_CTX_DEVICE(ctx);
     cudaStream_t s = (cudaStream_t)stream;
     const int N = ctx->last_N, max_h = ctx->ws.max_humans;
     int rc = draw_reserve_ids(ctx, (size_t)N * img_h * img_w);
@@ -519,7 +538,7 @@ int tfpd_last_launch_count(const tfpd_ctx *ctx) { return ctx ? ctx->launches : 0
 int tfpd_debug_k1_times(tfpd_ctx *ctx, uint64_t *out, int max_ctas) {
     if (!ctx || !out || max_ctas < 1) return TFPD_ERR_INVALID;
     if (!ctx->d_k1_times) return fail(ctx, TFPD_ERR_STATE, "per-CTA timestamps are off (create the ctx with TFPD_K1_TIMES=1)");
-    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    ON_CTX_DEVICE(ctx);
     CUDA_TRY(ctx, cudaDeviceSynchronize());
     const int n = max_ctas < 1024 ? max_ctas : 1024;
     CUDA_TRY(ctx, cudaMemcpy(out, ctx->d_k1_times, (size_t)n * 4 * 8, cudaMemcpyDeviceToHost));
@@ -697,7 +716,7 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
         return fail(ctx, TFPD_ERR_INVALID, "decode: dense outputs must be all set or all null");
     if (want_dense && ((((uintptr_t)dense->heat_up) | ((uintptr_t)dense->paf_up) | ((uintptr_t)dense->peaks)) & 15))
         return fail(ctx, TFPD_ERR_INVALID, "decode: dense output pointers must be 16-byte aligned");
-    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    ON_CTX_DEVICE(ctx);
     cudaStream_t s = (cudaStream_t)stream;
     begin_call(ctx, N, H, W, s);
     int rc;
@@ -755,7 +774,7 @@ int tfpd_fetch_humans(tfpd_ctx *ctx, tfpd_human *humans, tfpd_frame_info *info) 
     const int N = ctx->last_N;
     const size_t info_bytes = align_up((size_t)ctx->cfg.max_batch * sizeof(tfpd_frame_info), 16);
     if (!ctx->fetched) {
-        CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+        ON_CTX_DEVICE(ctx);
         if (!ctx->result_enqueued) {
             int rc = enqueue_result_copy(ctx, N, ctx->last_stream, true);
             if (rc != TFPD_OK) return rc;
@@ -792,7 +811,7 @@ int tfpd_fetch_peaks(tfpd_ctx *ctx, int frame, int cap, int *part, int *x, int *
     if (!ctx) return TFPD_ERR_INVALID;
     if (!ctx->decoded) return fail(ctx, TFPD_ERR_STATE, "fetch_peaks: no decode on this ctx yet");
     if (frame < 0 || frame >= ctx->last_N || cap < 0) return fail(ctx, TFPD_ERR_INVALID, "fetch_peaks: bad frame/cap");
-    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    ON_CTX_DEVICE(ctx);
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->last_stream));
     int first[20];
     CUDA_TRY(ctx, cudaMemcpy(first, ctx->ws.part_first + frame * 20, sizeof(first), cudaMemcpyDeviceToHost));
@@ -821,7 +840,7 @@ int tfpd_fetch_connections(tfpd_ctx *ctx, int frame, int cap, int *limb, int *ci
     if (!ctx) return TFPD_ERR_INVALID;
     if (!ctx->decoded) return fail(ctx, TFPD_ERR_STATE, "fetch_connections: no decode on this ctx yet");
     if (frame < 0 || frame >= ctx->last_N || cap < 0) return fail(ctx, TFPD_ERR_INVALID, "fetch_connections: bad frame/cap");
-    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    ON_CTX_DEVICE(ctx);
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->last_stream));
     int st[20], cc[20];
     CUDA_TRY(ctx, cudaMemcpy(st, ctx->ws.conn_start + frame * 20, sizeof(st), cudaMemcpyDeviceToHost));
@@ -857,7 +876,7 @@ int tfpd_decode_host_async(tfpd_ctx *ctx, const float *net_out, int N, int h, in
     const bool want_dense = heat_up || paf_up || peaks;
     if (want_dense && !(heat_up && paf_up && peaks))
         return fail(ctx, TFPD_ERR_INVALID, "decode_host: dense outputs must be all set or all null");
-    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    ON_CTX_DEVICE(ctx);
     const size_t frame_in = (size_t)h * w * kNetC * 4;      // multiple of 4; chunk offsets are kept 16-byte aligned below
     const size_t fpx = (size_t)H * W;
     CUDA_TRY(ctx, ctx->in_buf.reserve((size_t)N * frame_in));
@@ -939,7 +958,7 @@ int tfpd_process_paf_device(tfpd_ctx *ctx, int p1, int p2, int p3, const float *
     if (p1 < 1 || p2 < 1 || h1 != p1 || h2 != p2 || f1 != p1 || f2 != p2)
         return fail(ctx, TFPD_ERR_INVALID, "process_paf: the three arrays must share their spatial shape");
     if (p1 > 8191 || p2 > 16383) return fail(ctx, TFPD_ERR_INVALID, "process_paf: map larger than 8191x16383");
-    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    ON_CTX_DEVICE(ctx);
     cudaStream_t s = (cudaStream_t)stream;
     begin_call(ctx, 1, p1, p2, s);
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->ws.counters, 0, sizeof(FrameCounters), s));
@@ -968,7 +987,7 @@ int tfpd_process_paf(tfpd_ctx *ctx, int p1, int p2, int p3, const float *peaks, 
     if (!peaks || !heatmap || !pafmap) return fail(ctx, TFPD_ERR_INVALID, "process_paf: null array");
     if (p1 < 1 || p2 < 1 || p3 < 1 || h1 < 1 || h2 < 1 || h3 < 1 || f1 < 1 || f2 < 1 || f3 < 1)
         return fail(ctx, TFPD_ERR_INVALID, "process_paf: empty array");
-    CUDA_TRY(ctx, cudaSetDevice(ctx->cfg.device));
+    ON_CTX_DEVICE(ctx);
     const size_t np = (size_t)p1 * p2 * p3, nh = (size_t)h1 * h2 * h3, nf = (size_t)f1 * f2 * f3;
     CUDA_TRY(ctx, ctx->dense_buf.reserve((np + nh + nf) * 4));
     float *dp = (float *)ctx->dense_buf.p, *dh = dp + np, *df = dh + nh;
