@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtfpose_decode.so")
+# TFPOSE_DECODE_LIB: another build of the same library (A/B timing of kernel variants); default = the in-tree build
+LIB_PATH = os.environ.get("TFPOSE_DECODE_LIB") or os.path.join(_HERE, "libtfpose_decode.so")
 
 NUM_PARTS = 18
 OK, ERR_INVALID, ERR_CUDA, ERR_CAPACITY, ERR_STATE = 0, 1, 2, 3, 4

@@ -607,8 +607,6 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         p.debug_roles = ctx->k1_roles;
         p.dbg_times = ctx->d_k1_times;
         p.force_pr = ctx->k1_pr;
-        static const int copy_slots = getenv("TFPD_K1_COPY_SLOTS") ? atoi(getenv("TFPD_K1_COPY_SLOTS")) : 0;
-        p.copy_slots = copy_slots;
         int r;
         if (ctx->k1_turnstile) {
             // One map kernel at a time per device, whatever the ctx and stream: it is HBM-bound, so two of them only

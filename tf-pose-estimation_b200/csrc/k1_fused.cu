@@ -61,11 +61,6 @@ __device__ __forceinline__ uint64_t policy_evict_first() {
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
     return pol;
 }
-// start pulling [ptr, ptr+bytes) into L2 (bytes a multiple of 16, ptr 16-byte aligned)
-__device__ __forceinline__ void bulk_prefetch_l2(const void *ptr, uint32_t bytes, uint64_t pol) {
-    asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;" ::"l"(ptr), "r"(bytes), "l"(pol)
-                 : "memory");
-}
 __device__ __forceinline__ uint64_t policy_evict_last() {
     uint64_t pol;
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
@@ -82,7 +77,6 @@ __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.comm
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_read2() { asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory"); }
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
@@ -166,16 +160,15 @@ __device__ __forceinline__ void copy_prefetch(const K1Params &p, long long R, un
 // per-CTA finish times of a static split spread by +-20 % (measured, tools/k1_cta_times.py) because the
 // warp's pace is set by how fast ITS stores drain, so the split has to follow the pace.  The warp always
 // holds two grabbed items: the one it expands and the one whose bulk load is in flight.
-// ns = staging slots (and raw buffers) of this warp, 2 or 3: ns - 1 store groups may still be draining while the
-// next item is expanded.
 __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, unsigned char *raws, int raw_bytes,
-                          uint64_t *bars, int lane, int ns) {
+                          uint64_t *bars, int lane) {
     const int H = 4 * p.h, W = 4 * p.w;
     const size_t total_bytes = (size_t)p.N * p.h * p.w * (kNetC * 4);
     const long long Rend = (long long)p.N * p.h * p.copy_nchunks;
     int *queue = &p.counters[0].k1_queue;
     if (lane == 0) {
-        for (int i = 0; i < ns; ++i) mbar_init(&bars[i], 1);
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -188,22 +181,19 @@ __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, uns
     }
     R = __shfl_sync(0xffffffffu, R, 0);
     Rn = __shfl_sync(0xffffffffu, Rn, 0);
-    unsigned b = 0, phase = 0;                             // ring position, and how often it wrapped (mbarrier parity)
-    for (; R < Rend;) {
-        const unsigned bn = (b + 1 == (unsigned)ns) ? 0u : b + 1;
+    unsigned k = 0;
+    for (; R < Rend; ++k) {
+        const unsigned b = k & 1u;
         long long Rnn = 0;
         if (lane == 0) {
-            if (Rn < Rend) copy_prefetch(p, Rn, raws + (size_t)bn * raw_bytes, &bars[bn]);
+            if (Rn < Rend) copy_prefetch(p, Rn, raws + (size_t)(b ^ 1u) * raw_bytes, &bars[b ^ 1u]);
             Rnn = atomicAdd(queue, 1);                     // consumed at the end of this iteration
         }
         const CopyItem ci = copy_item(p, R);
         float *sh = cslots + (size_t)b * slot_floats;      // heat part: tc*76 floats
         float *sp = sh + ci.tc * 4 * kHeatC;               // paf part:  tc*152 floats
-        if (lane == 0) {                                   // the stores that last used THIS slot have drained
-            if (ns == 3) bulk_wait_read2();
-            else bulk_wait_read1();
-        }
-        mbar_wait(&bars[b], phase & 1u);                   // the chunk has landed in raw[b]
+        if (lane == 0) bulk_wait_read1();                  // the stores that last used THIS slot have drained
+        mbar_wait(&bars[b], (k >> 1) & 1u);                // the chunk has landed in raw[b]
         __syncwarp();
         const unsigned char *rawb = raws + (size_t)b * raw_bytes;
         const float *src = reinterpret_cast<const float *>(rawb + (ci.src_off & 15));
@@ -264,8 +254,6 @@ __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, uns
         }
         R = Rn;
         Rn = __shfl_sync(0xffffffffu, Rnn, 0);
-        if (bn == 0) ++phase;
-        b = bn;
     }
 }
 
@@ -518,8 +506,7 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
     const int raw_bytes = k1_raw_bytes(p.copy_chunk);
     float *pslots = smem;                                 // 2 peak-row slots (blur role)
     // per copy warp: 2 replication slots + 2 raw chunks; then 2 mbarriers per copy warp
-    const int ns = p.copy_slots;
-    const size_t cw_bytes = ns * ((size_t)cslot_floats * 4 + (size_t)raw_bytes);
+    const size_t cw_bytes = 2 * (size_t)cslot_floats * 4 + 2 * (size_t)raw_bytes;
     unsigned char *cbase = reinterpret_cast<unsigned char *>(smem + 2 * (size_t)pslot_floats);
     uint64_t *bars_all = reinterpret_cast<uint64_t *>(cbase + kCopyWarps * cw_bytes);
 
@@ -555,10 +542,7 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
             u += it.nrows;
         }
         if (DENSE && tid == 0) bulk_wait_all();
-        if (p.dbg_times && tid == 0) {
-            p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
-            p.dbg_times[3072 + blockIdx.x] = (unsigned long long)atomicAdd(&p.counters[0].k1_queue, 0);   // copy items handed out so far
-        }
+        if (p.dbg_times && tid == 0) p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
         if (DENSE && (p.debug_roles & 2) && kHelperWarps > 0) {
             // The blur role of this CTA is done (measured: at ~65 % of the kernel) and its peak-row slots are
             // idle: the first kHelperWarps blur warps carve them into staging buffers and pull copy items from
@@ -569,28 +553,16 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
             if (warp < kHelperWarps && warp < fit) {
                 float *hslots = reinterpret_cast<float *>(reinterpret_cast<unsigned char *>(pslots) + warp * cw_bytes_h);
                 unsigned char *hraws = reinterpret_cast<unsigned char *>(hslots + 2 * (size_t)cslot_floats);
-                copy_role(p, hslots, cslot_floats, hraws, raw_bytes, bars_all + 3 * (kCopyWarps + warp), lane, 2);
+                copy_role(p, hslots, cslot_floats, hraws, raw_bytes, bars_all + 2 * (kCopyWarps + warp), lane);
                 if (lane == 0) bulk_wait_all();
             }
         }
     } else {
         const int cw = warp - kBlurWarps;
-        if ((p.l2_knobs & 1) && cw == 0 && lane == 0) {
-            // Front-load the DRAM reads: this CTA's contiguous share of X goes to L2 now (evict-last, the 717 MB of
-            // output stream through with evict-first), so that the rest of the kernel is write-only for the DRAM --
-            // reads interleaved with the stores cost a read/write turnaround each (5.3 vs 6.2+ TB/s measured).
-            const size_t total = ((size_t)p.N * p.h * p.w * (kNetC * 4)) & ~(size_t)15;
-            size_t lo = (total * blockIdx.x / gridDim.x) & ~(size_t)15, hi = (total * (blockIdx.x + 1) / gridDim.x) & ~(size_t)15;
-            if (blockIdx.x == gridDim.x - 1) hi = total;
-            const uint64_t pol_last = policy_evict_last();
-            const unsigned char *base = reinterpret_cast<const unsigned char *>(p.X);
-            for (size_t o = lo; o < hi; o += 32768)
-                bulk_prefetch_l2(base + o, (uint32_t)min((size_t)32768, hi - o), pol_last);
-        }
         if (DENSE && (p.debug_roles & 2)) {
             float *cslots = reinterpret_cast<float *>(cbase + cw * cw_bytes);
-            unsigned char *raws = reinterpret_cast<unsigned char *>(cslots + ns * (size_t)cslot_floats);
-            copy_role(p, cslots, cslot_floats, raws, raw_bytes, bars_all + 3 * cw, lane, ns);
+            unsigned char *raws = reinterpret_cast<unsigned char *>(cslots + 2 * (size_t)cslot_floats);
+            copy_role(p, cslots, cslot_floats, raws, raw_bytes, bars_all + 2 * cw, lane);
             if (lane == 0) bulk_wait_all();
         }
         if (p.dbg_times && lane == 0 && cw == 0) p.dbg_times[blockIdx.x * 4 + 2] = global_ns();
@@ -629,14 +601,8 @@ int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t
     const size_t cslot = (size_t)p.copy_chunk * 4 * kNetC * 4;
     const size_t raw = (size_t)k1_raw_bytes(p.copy_chunk);
     const size_t prow = (size_t)p.chunk_cells * 4 * kHeatC * 4;     // one peaks row of a blur chunk
+    const size_t fixed = kCopyWarps * (2 * cslot + 2 * raw) + 16 * (kCopyWarps + kHelperWarps);
     const size_t limit = 227 * 1024 - 1024;
-    // a third staging slot for the dedicated copy warp (TFPD_K1_COPY_SLOTS=3) measured 1.5 % SLOWER than two
-    // (145 vs 143 us): the copy path is not short of stores in flight, HBM is the limit while both roles run
-    int ns = (p.copy_slots == 3) ? 3 : 2;
-    if (ns == 3 && 2 * 4 * prow + kCopyWarps * 3 * (cslot + raw) + 24 * (kCopyWarps + kHelperWarps) > limit) ns = 2;
-    const size_t fixed = kCopyWarps * ns * (cslot + raw) + 24 * (kCopyWarps + kHelperWarps);
-    K1Params q = p;
-    q.copy_slots = ns;
     // function attributes are per device: one flag per device a ctx of this process may live on
     static bool attr_set[64] = {};
     int dev = 0;
@@ -653,9 +619,9 @@ int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t
     while (pr > 2 && 2 * pr * prow + fixed > limit) --pr;
     const size_t smem = 2 * pr * prow + fixed;
     if (smem > limit) return -1;
-    if (pr == 4) k1_fused_f4<4, true><<<grid, kThreads, smem, s>>>(q);
-    else if (pr == 3) k1_fused_f4<3, true><<<grid, kThreads, smem, s>>>(q);
-    else k1_fused_f4<2, true><<<grid, kThreads, smem, s>>>(q);
+    if (pr == 4) k1_fused_f4<4, true><<<grid, kThreads, smem, s>>>(p);
+    else if (pr == 3) k1_fused_f4<3, true><<<grid, kThreads, smem, s>>>(p);
+    else k1_fused_f4<2, true><<<grid, kThreads, smem, s>>>(p);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -100,7 +100,6 @@ struct K1Params {
     int l2_knobs;                       // bit0 up-front L2 prefetch of X, bit1 evict_first stores, bit2 evict_last prefetch
     int debug_roles;                    // bit0 blur role, bit1 copy role (3 = normal; tuning/profiling only)
     int force_pr;
-    int copy_slots;     // staging slots of the dedicated copy warp: 2 (default, also for 0) or 3                       // 0 = automatic; 2..4 = peak rows per store group (tuning knob)
     unsigned long long *dbg_times;      // null, or [grid][4]: CTA start / blur role end / copy role end (ns), SM id
 };
 

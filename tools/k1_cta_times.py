@@ -23,27 +23,13 @@ NC = int(os.environ.get("K1_CTAS", "128"))
 dec.set_option("k1_ctas", NC)
 for it in range(6):
     dec.decode(x, (H, W), dense=dense)
-    full = dec.k1_cta_times(1024).astype(np.int64)
-    t = full[:NC]
-    qpos = full.reshape(-1)[3072:3072 + NC]
+    t = dec.k1_cta_times(NC).astype(np.int64)
     t0 = t[:, 0].min()
     start, blur, copy = (t[:, 0] - t0) / 1e3, (t[:, 1] - t0) / 1e3, (t[:, 2] - t0) / 1e3
     if it >= 3:
         q = lambda a: "min %.1f p10 %.1f med %.1f p90 %.1f max %.1f" % (a.min(), np.percentile(a, 10), np.median(a), np.percentile(a, 90), a.max())
         print("iter %d K1 %.1f us | start: %s | blur end: %s | copy end: %s" % (it, dec.stage_ms()[0] * 1e3, q(start), q(blur), q(copy)))
         if it == 5:
-            # the copy queue against time: (time a CTA's blur role ended, copy items handed out by then);
-            # one item = 27 cells x 57 channels x 16 replicas x 4 B = 98.5 KB of output
-            o = np.argsort(blur)
-            tb, qb = blur[o], qpos[o].astype(float)
-            total_items = B * h * 2
-            print("copy items handed out when the blur role of a CTA ended (time us: items of %d):" % total_items,
-                  " ".join("%.0f:%d" % (a, b) for a, b in zip(tb[::8], qb[::8])))
-            lo, hi = int(0.1 * NC), int(0.9 * NC)
-            rate = (qb[hi] - qb[lo]) / (tb[hi] - tb[lo])
-            print("queue slope between p10 and p90 of the blur ends: %.1f items/us = %.2f TB/s of copy output; "
-                  "mean rate from 0 to the median blur end: %.2f TB/s" %
-                  (rate, rate * 27 * 57 * 64 / 1e6, np.median(qb) * 27 * 57 * 64 / np.median(tb) / 1e6))
             order = np.argsort(np.maximum(blur, copy))
             print("slowest CTAs (cta, sm, blur_end, copy_end):", [(int(c), int(t[c, 3]), round(float(blur[c]), 1), round(float(copy[c]), 1)) for c in order[-8:]])
             print("fastest CTAs:", [(int(c), int(t[c, 3]), round(float(blur[c]), 1), round(float(copy[c]), 1)) for c in order[:8]])
