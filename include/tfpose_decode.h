@@ -201,6 +201,9 @@ TFPD_API int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int im
  *   "host_chunks"  frame chunks tfpd_decode_host pipelines H2D / decode / D2H over; 0 = automatic.
  *   "k1_l2"        bit 1: evict-first stores (default 2); bit 0 is reserved (a bulk L2 prefetch of the input at
  *                  kernel start measured slower and was taken out again).
+ *   "fuse_sort"    1 (default): the limb-scoring kernel ranks the unordered peak records itself (every CTA of a frame
+ *                  counts smaller keys in shared memory, CTA 0 writes the table); 0: a sort kernel of its own runs in
+ *                  front of it.  Same tables.
  *   "graph"        1: tfpd_decode_device replays a CUDA graph of the whole decode (counter reset, the four kernels,
  *                  the table copy) captured once per distinct argument set (x4 path, profiling off, up to 16
  *                  cached): one launch instead of seven stream operations.  Same results.

@@ -372,7 +372,8 @@ def test_tuning_options_do_not_change_results(cuda):
     dec = tp.PoseDecoder(max_batch=6, max_upsample=(184, 216))
     outs = []
     for name, val in (("k1_ctas", 0), ("k1_ctas", 128), ("k1_ctas", 7), ("k1_l2", 0), ("k1_l2", 3),
-                      ("early_fetch", 1), ("early_fetch", 2), ("graph", 1), ("k1_turnstile", 1)):
+                      ("early_fetch", 1), ("early_fetch", 2), ("fuse_sort", 0), ("fuse_sort", 1), ("graph", 1),
+                      ("k1_turnstile", 1)):
         dec.set_option(name, val)
         dense = tuple(torch.full((6, 184, 216, c), 3.0, device="cuda") for c in (19, 38, 19))
         res = dec.decode(xd, (184, 216), dense=dense)

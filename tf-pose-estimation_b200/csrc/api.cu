@@ -194,8 +194,10 @@ int run_tail(tfpd_ctx *ctx, const Workspace &ws, int N, const PafSource &src, si
              bool timed) {
     int r;
     if (timed) cudaEventRecord(ctx->ev[1], s);
-    if ((r = launch_sort_peaks(ws, N, s)) < 0) return fail(ctx, TFPD_ERR_CUDA, "k_sort_peaks launch failed");
-    ctx->launches += r;
+    if (!ws.k2_fused_sort) {
+        if ((r = launch_sort_peaks(ws, N, s)) < 0) return fail(ctx, TFPD_ERR_CUDA, "k_sort_peaks launch failed");
+        ctx->launches += r;
+    }
     if (timed) cudaEventRecord(ctx->ev[2], s);
     if ((r = launch_limb_score(ws, N, src, frame_stride, thresholds_of(ctx->cfg), ctx->sm_count, s)) < 0)
         return fail(ctx, TFPD_ERR_CUDA, "k_limb_score launch failed");
@@ -333,6 +335,7 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     w.max_rows = cfg->max_rows;
     w.max_humans = cfg->max_humans;
     w.k3_reg_rows = 128;
+    w.k2_fused_sort = 1;
     w.k3_warp_sort_max = 1024;
     w.k3_parallel_limbs = 1;
     if (const char *e = getenv("TFPD_K3_PARALLEL")) w.k3_parallel_limbs = atoi(e) != 0;
@@ -514,6 +517,8 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
     } else if (!strcmp(name, "host_chunks")) {
         if (value < 0 || value > 4096) return fail(ctx, TFPD_ERR_INVALID, "host_chunks=%d out of range", value);
         ctx->host_chunks = value;
+    } else if (!strcmp(name, "fuse_sort")) {
+        ctx->ws.k2_fused_sort = value != 0;
     } else if (!strcmp(name, "graph")) {
         ctx->use_graph = value != 0;
     } else if (!strcmp(name, "k1_turnstile")) {

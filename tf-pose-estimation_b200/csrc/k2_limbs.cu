@@ -31,8 +31,63 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
     __shared__ int s_tstart[kLimbs + 1];
     const int n = blockIdx.y;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    if (tid <= kHeatC) s_first[tid] = ws.part_first[n * 20 + tid];
-    __syncthreads();
+    if (ws.k2_fused_sort) {
+        // The peak table in Peak.id order (pafprocess.cpp:24-37: part-major, row-major) straight from the unordered
+        // records the map kernel left: keys (part, y, x) are unique, so a record's position is the number of
+        // smaller keys.  Every CTA of the frame ranks for itself (a few hundred peaks: cheaper than a sort kernel
+        // of its own in front of this one plus its launch gap); CTA 0 also writes the table for the assembly
+        // kernel and tfpd_fetch_peaks.
+        uint32_t *s_key = reinterpret_cast<uint32_t *>(k2_smem + (((size_t)ws.max_peaks * 4 + 15) & ~(size_t)15));
+        __shared__ int s_hist[kHeatC + 1];
+        const int raw = ws.counters[n].n_peak_rec;
+        const int cnt = min(raw, ws.max_peaks);
+        const int cnt4 = (cnt + 3) & ~3;
+        const uint32_t *gk = ws.rec_key + (size_t)n * ws.max_peaks;
+        for (int i = tid; i < cnt4; i += kK2Threads) s_key[i] = (i < cnt) ? gk[i] : 0xffffffffu;
+        if (tid <= kHeatC) s_hist[tid] = 0;
+        __syncthreads();
+        const uint4 *k4 = reinterpret_cast<const uint4 *>(s_key);
+        for (int i = tid; i < cnt; i += kK2Threads) {
+            const uint32_t k = s_key[i];
+            int r = 0;
+            for (int j = 0; j < (cnt4 >> 2); ++j) {
+                const uint4 v = k4[j];                  // same address for the whole warp: one broadcast
+                r += (int)(v.x < k) + (int)(v.y < k) + (int)(v.z < k) + (int)(v.w < k);
+            }
+            s_px[r] = (int16_t)key_x(k);
+            s_py[r] = (int16_t)key_y(k);
+            atomicAdd(&s_hist[key_part(k)], 1);
+            if (blockIdx.x == 0) {
+                ws.pk_x[(size_t)n * ws.max_peaks + r] = (int16_t)key_x(k);
+                ws.pk_y[(size_t)n * ws.max_peaks + r] = (int16_t)key_y(k);
+                ws.pk_score[(size_t)n * ws.max_peaks + r] = ws.rec_val[(size_t)n * ws.max_peaks + i];
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {                                 // first[p] = index of the first peak with part >= p
+            int acc = 0;
+            for (int pp = 0; pp <= kHeatC; ++pp) {
+                s_first[pp] = acc;
+                acc += s_hist[pp];
+            }
+            if (blockIdx.x == 0) {
+                ws.info[n].n_peaks = cnt;
+                ws.info[n].near_ties = ws.counters[n].near_ties;
+                if (raw > ws.max_peaks) atomicOr(&ws.counters[n].flags, TFPD_FLAG_PEAK_OVERFLOW);
+            }
+        }
+        __syncthreads();
+        if (blockIdx.x == 0 && tid <= kHeatC) ws.part_first[n * 20 + tid] = s_first[tid];
+    } else {
+        if (tid <= kHeatC) s_first[tid] = ws.part_first[n * 20 + tid];
+        const int16_t *gx = ws.pk_x + (size_t)n * ws.max_peaks, *gy = ws.pk_y + (size_t)n * ws.max_peaks;
+        __syncthreads();
+        const int npk = min(s_first[kParts], ws.max_peaks);
+        for (int i = tid; i < npk; i += kK2Threads) {
+            s_px[i] = gx[i];
+            s_py[i] = gy[i];
+        }
+    }
     if (tid == 0) {
         int acc = 0;
         for (int l = 0; l < kLimbs; ++l) {
@@ -41,14 +96,6 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
             acc += (s_first[pa + 1] - s_first[pa]) * (s_first[pb + 1] - s_first[pb]);
         }
         s_tstart[kLimbs] = acc;
-    }
-    {
-        const int npk = min(s_first[kParts], ws.max_peaks);
-        const int16_t *gx = ws.pk_x + (size_t)n * ws.max_peaks, *gy = ws.pk_y + (size_t)n * ws.max_peaks;
-        for (int i = tid; i < npk; i += kK2Threads) {
-            s_px[i] = gx[i];
-            s_py[i] = gy[i];
-        }
     }
     __syncthreads();
     const int total = s_tstart[kLimbs];
@@ -179,7 +226,7 @@ int launch_limb_score(const Workspace &ws, int N, const PafSource &src, size_t f
     int bpf = max(1, (6 * sm_count + N - 1) / N);
     if (bpf > 32) bpf = 32;
     dim3 grid(bpf, N);
-    k_limb_score<<<grid, kK2Threads, (size_t)ws.max_peaks * 4, s>>>(ws, src, frame_stride, th);
+    k_limb_score<<<grid, kK2Threads, (size_t)ws.max_peaks * 8 + 32, s>>>(ws, src, frame_stride, th);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
