@@ -496,6 +496,36 @@ def test_two_devices_in_one_process(cuda):
     assert torch.cuda.current_device() == 0
 
 
+def test_peak_table_paths_agree_on_many_peaks(cuda):
+    """The peak table (Peak.id order, pafprocess.cpp:24-37) from the ranking fused into the scoring kernel --
+    bucketed up to 1024 peaks per frame, all-pairs counting beyond -- and from the separate sort kernel: same
+    table, checked against a NumPy sort of the same records.  Noisy heat channels give ~100 to ~3000 peaks per
+    frame; the PAF is zero so that no candidate survives."""
+    import torch
+    rng = np.random.default_rng(77)
+    x = np.zeros((3, 60, 80, 57), np.float32)
+    x[0, :, :, :2] = 0.3 + 0.2 * rng.random((60, 80, 2), dtype=np.float32)          # a few hundred peaks
+    x[1, :, :, :18] = 0.3 + 0.2 * rng.random((60, 80, 18), dtype=np.float32)        # > 1024 peaks
+    x[2, 10:14, 10:14, 5] = 0.5 + 0.1 * rng.random((4, 4), dtype=np.float32)        # a handful
+    xd = torch.from_numpy(x).cuda()
+    tables = []
+    for fuse in (1, 0):
+        dec = tp.PoseDecoder(max_batch=3, max_upsample=(240, 320), max_peaks=4096, max_cands=8192)
+        dec.set_option("fuse_sort", fuse)
+        res = dec.decode(xd, (240, 320))
+        assert int(res.info["n_humans"].sum()) == 0
+        tables.append([dec.peaks(i) for i in range(3)])
+        assert [len(t["x"]) for t in tables[-1]] == [int(v) for v in res.info["n_peaks"]]
+        dec.close()
+    counts = [len(t["x"]) for t in tables[0]]
+    assert counts[0] > 64 and counts[1] > 1024 and 0 < counts[2] < 64, counts
+    for a, b in zip(*tables):
+        for k in ("part", "x", "y", "score"):
+            assert np.array_equal(a[k], b[k]), k
+        order = np.lexsort((a["x"], a["y"], a["part"]))
+        assert np.array_equal(order, np.arange(len(order)))            # part-major, then row-major
+
+
 def test_async_host_call_matches_the_synchronous_one(cuda):
     """tfpd_decode_host_async + tfpd_fetch_humans on two alternating contexts == tfpd_decode_host."""
     from helpers import table_tuples

@@ -37,44 +37,100 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
         // smaller keys.  Every CTA of the frame ranks for itself (a few hundred peaks: cheaper than a sort kernel
         // of its own in front of this one plus its launch gap); CTA 0 also writes the table for the assembly
         // kernel and tfpd_fetch_peaks.
-        uint32_t *s_key = reinterpret_cast<uint32_t *>(k2_smem + (((size_t)ws.max_peaks * 4 + 15) & ~(size_t)15));
+        const size_t mp4 = ((size_t)ws.max_peaks * 4 + 15) & ~(size_t)15;
+        uint32_t *s_key = reinterpret_cast<uint32_t *>(k2_smem + mp4);
+        uint16_t *s_idx = reinterpret_cast<uint16_t *>(k2_smem + 2 * mp4);
         __shared__ int s_hist[kHeatC + 1];
         const int raw = ws.counters[n].n_peak_rec;
         const int cnt = min(raw, ws.max_peaks);
-        const int cnt4 = (cnt + 3) & ~3;
         const uint32_t *gk = ws.rec_key + (size_t)n * ws.max_peaks;
-        for (int i = tid; i < cnt4; i += kK2Threads) s_key[i] = (i < cnt) ? gk[i] : 0xffffffffu;
+        const float *gv = ws.rec_val + (size_t)n * ws.max_peaks;
+        int16_t *ox = ws.pk_x + (size_t)n * ws.max_peaks, *oy = ws.pk_y + (size_t)n * ws.max_peaks;
+        float *os = ws.pk_score + (size_t)n * ws.max_peaks;
         if (tid <= kHeatC) s_hist[tid] = 0;
         __syncthreads();
-        const uint4 *k4 = reinterpret_cast<const uint4 *>(s_key);
-        for (int i = tid; i < cnt; i += kK2Threads) {
-            const uint32_t k = s_key[i];
-            int r = 0;
-            for (int j = 0; j < (cnt4 >> 2); ++j) {
-                const uint4 v = k4[j];                  // same address for the whole warp: one broadcast
-                r += (int)(v.x < k) + (int)(v.y < k) + (int)(v.z < k) + (int)(v.w < k);
+        constexpr int kPerThread = 4;
+        if (cnt <= kPerThread * kK2Threads) {
+            // bucket by part first (18 shared-memory counters), then rank inside the bucket: n*n/18 compares
+            uint32_t kk[kPerThread];
+            int sl[kPerThread];
+#pragma unroll
+            for (int e = 0; e < kPerThread; ++e) {
+                const int i = tid + e * kK2Threads;
+                kk[e] = 0u;
+                sl[e] = 0;
+                if (i < cnt) {
+                    kk[e] = gk[i];
+                    sl[e] = atomicAdd(&s_hist[key_part(kk[e])], 1);
+                }
             }
-            s_px[r] = (int16_t)key_x(k);
-            s_py[r] = (int16_t)key_y(k);
-            atomicAdd(&s_hist[key_part(k)], 1);
-            if (blockIdx.x == 0) {
-                ws.pk_x[(size_t)n * ws.max_peaks + r] = (int16_t)key_x(k);
-                ws.pk_y[(size_t)n * ws.max_peaks + r] = (int16_t)key_y(k);
-                ws.pk_score[(size_t)n * ws.max_peaks + r] = ws.rec_val[(size_t)n * ws.max_peaks + i];
+            __syncthreads();
+            if (tid == 0) {                             // first[p] = index of the first peak with part >= p
+                int acc = 0;
+                for (int pp = 0; pp <= kHeatC; ++pp) {
+                    s_first[pp] = acc;
+                    acc += s_hist[pp];
+                }
+            }
+            __syncthreads();
+#pragma unroll
+            for (int e = 0; e < kPerThread; ++e) {
+                const int i = tid + e * kK2Threads;
+                if (i < cnt) {
+                    const int pos = s_first[key_part(kk[e])] + sl[e];
+                    s_key[pos] = kk[e];
+                    s_idx[pos] = (uint16_t)i;
+                }
+            }
+            __syncthreads();
+            for (int j = tid; j < cnt; j += kK2Threads) {
+                const uint32_t k = s_key[j];
+                const int lo = s_first[key_part(k)], hi = s_first[key_part(k) + 1];
+                int r = lo;
+                for (int t = lo; t < hi; ++t) r += (int)(s_key[t] < k);
+                s_px[r] = (int16_t)key_x(k);
+                s_py[r] = (int16_t)key_y(k);
+                if (blockIdx.x == 0) {
+                    ox[r] = (int16_t)key_x(k);
+                    oy[r] = (int16_t)key_y(k);
+                    os[r] = gv[s_idx[j]];
+                }
+            }
+        } else {
+            // very many peaks: position = number of smaller keys among all of them
+            const int cnt4 = (cnt + 3) & ~3;
+            for (int i = tid; i < cnt4; i += kK2Threads) s_key[i] = (i < cnt) ? gk[i] : 0xffffffffu;
+            __syncthreads();
+            const uint4 *k4 = reinterpret_cast<const uint4 *>(s_key);
+            for (int i = tid; i < cnt; i += kK2Threads) {
+                const uint32_t k = s_key[i];
+                int r = 0;
+                for (int j = 0; j < (cnt4 >> 2); ++j) {
+                    const uint4 v = k4[j];              // same address for the whole warp: one broadcast
+                    r += (int)(v.x < k) + (int)(v.y < k) + (int)(v.z < k) + (int)(v.w < k);
+                }
+                s_px[r] = (int16_t)key_x(k);
+                s_py[r] = (int16_t)key_y(k);
+                atomicAdd(&s_hist[key_part(k)], 1);
+                if (blockIdx.x == 0) {
+                    ox[r] = (int16_t)key_x(k);
+                    oy[r] = (int16_t)key_y(k);
+                    os[r] = gv[i];
+                }
+            }
+            __syncthreads();
+            if (tid == 0) {
+                int acc = 0;
+                for (int pp = 0; pp <= kHeatC; ++pp) {
+                    s_first[pp] = acc;
+                    acc += s_hist[pp];
+                }
             }
         }
-        __syncthreads();
-        if (tid == 0) {                                 // first[p] = index of the first peak with part >= p
-            int acc = 0;
-            for (int pp = 0; pp <= kHeatC; ++pp) {
-                s_first[pp] = acc;
-                acc += s_hist[pp];
-            }
-            if (blockIdx.x == 0) {
-                ws.info[n].n_peaks = cnt;
-                ws.info[n].near_ties = ws.counters[n].near_ties;
-                if (raw > ws.max_peaks) atomicOr(&ws.counters[n].flags, TFPD_FLAG_PEAK_OVERFLOW);
-            }
+        if (tid == 0 && blockIdx.x == 0) {
+            ws.info[n].n_peaks = cnt;
+            ws.info[n].near_ties = ws.counters[n].near_ties;
+            if (raw > ws.max_peaks) atomicOr(&ws.counters[n].flags, TFPD_FLAG_PEAK_OVERFLOW);
         }
         __syncthreads();
         if (blockIdx.x == 0 && tid <= kHeatC) ws.part_first[n * 20 + tid] = s_first[tid];
@@ -226,7 +282,16 @@ int launch_limb_score(const Workspace &ws, int N, const PafSource &src, size_t f
     int bpf = max(1, (6 * sm_count + N - 1) / N);
     if (bpf > 32) bpf = 32;
     dim3 grid(bpf, N);
-    k_limb_score<<<grid, kK2Threads, (size_t)ws.max_peaks * 8 + 32, s>>>(ws, src, frame_stride, th);
+    const size_t smem = (size_t)ws.max_peaks * 10 + 64;     // sorted coordinates, keys, record indices
+    static size_t attr_smem[64] = {};                      // per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (smem > 48 * 1024 && smem > attr_smem[dev & 63]) {
+        if (cudaFuncSetAttribute(k_limb_score, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+            return -1;
+        attr_smem[dev & 63] = smem;
+    }
+    k_limb_score<<<grid, kK2Threads, smem, s>>>(ws, src, frame_stride, th);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
