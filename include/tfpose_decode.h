@@ -201,6 +201,7 @@ TFPD_API int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int im
  *   "host_chunks"  frame chunks tfpd_decode_host pipelines H2D / decode / D2H over; 0 = automatic.
  *   "k1_l2"        bit 1: evict-first stores (default 2); bit 0 is reserved (a bulk L2 prefetch of the input at
  *                  kernel start measured slower and was taken out again).
+ *   "k2_blocks"    CTAs of the limb-scoring kernel per frame; 0 = automatic (about 6 CTAs per SM over the batch).
  *   "fuse_sort"    1 (default): the limb-scoring kernel ranks the unordered peak records itself (every CTA of a frame
  *                  counts smaller keys in shared memory, CTA 0 writes the table); 0: a sort kernel of its own runs in
  *                  front of it.  Same tables.

@@ -336,6 +336,8 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     w.max_humans = cfg->max_humans;
     w.k3_reg_rows = 128;
     w.k2_fused_sort = 1;
+    w.k2_blocks_per_frame = 0;
+    if (const char *e = getenv("TFPD_K2_BPF")) w.k2_blocks_per_frame = atoi(e);
     w.k3_warp_sort_max = 1024;
     w.k3_parallel_limbs = 1;
     if (const char *e = getenv("TFPD_K3_PARALLEL")) w.k3_parallel_limbs = atoi(e) != 0;
@@ -517,6 +519,9 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
     } else if (!strcmp(name, "host_chunks")) {
         if (value < 0 || value > 4096) return fail(ctx, TFPD_ERR_INVALID, "host_chunks=%d out of range", value);
         ctx->host_chunks = value;
+    } else if (!strcmp(name, "k2_blocks")) {
+        if (value < 0 || value > 1024) return fail(ctx, TFPD_ERR_INVALID, "k2_blocks=%d out of range", value);
+        ctx->ws.k2_blocks_per_frame = value;
     } else if (!strcmp(name, "fuse_sort")) {
         ctx->ws.k2_fused_sort = value != 0;
     } else if (!strcmp(name, "graph")) {
