@@ -368,3 +368,20 @@ def test_persons_records_from_table_equal_humans_to_msg():
         assert rec["x"].tolist() == [float(np.float32(b.x)) for b in flat]
         assert rec["y"].tolist() == [float(np.float32(b.y)) for b in flat]
         assert rec["confidence"].tolist() == [float(np.float32(b.confidence)) for b in flat]
+
+
+def test_every_option_the_library_accepts_is_documented():
+    """tfpd_set_option names in api.cu == names described in include/tfpose_decode.h (and mentioned in
+    INTEGRATION.md), so that the header stays the reference for the tuning knobs."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    api = open(os.path.join(root, "tf-pose-estimation_b200", "csrc", "api.cu")).read()
+    body = api[api.index("int tfpd_set_option("):]
+    body = body[:body.index("\n}\n")]
+    accepted = set(re.findall(r'strcmp\(name, "([a-z0-9_]+)"\)', body))
+    header = open(os.path.join(root, "include", "tfpose_decode.h")).read()
+    doc = header[header.index("tfpd_set_option") - 4000:header.index("tfpd_set_option")]
+    documented = set(re.findall(r'\*\s+"([a-z0-9_]+)"\s', doc))
+    assert accepted and accepted == documented, (sorted(accepted - documented), sorted(documented - accepted))
+    integ = open(os.path.join(root, "INTEGRATION.md")).read()
+    assert all(("`%s`" % n) in integ for n in accepted), [n for n in accepted if ("`%s`" % n) not in integ]
