@@ -526,6 +526,34 @@ def test_peak_table_paths_agree_on_many_peaks(cuda):
         assert np.array_equal(order, np.arange(len(order)))            # part-major, then row-major
 
 
+def test_contexts_release_their_device_memory(cuda):
+    """Create / use / destroy many contexts (every internal buffer gets allocated: dense host path, general resize
+    path, draw buffers, graphs): free device memory comes back to where it started."""
+    import torch
+    x = synth.synth_batch(2, 46, 54, config_id=2, first_frame=3)
+    xd = torch.from_numpy(x).cuda()
+    img = torch.zeros((2, 120, 160, 3), dtype=torch.uint8, device="cuda")
+
+    def cycle():
+        d = tp.PoseDecoder(max_batch=2, max_upsample=(368, 432))
+        d.set_option("graph", 1)
+        d.decode(xd, (184, 216))
+        d.decode(xd, (368, 432))                       # power-of-two path buffers
+        d.decode(xd, (138, 162))                       # general path buffers
+        r, _ = d.decode_host(x, (184, 216), want_dense=True)
+        d.draw_decoded(img)
+        d.close()
+
+    cycle()
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for _ in range(25):
+        cycle()
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free0 - free1 < 8 << 20, (free0, free1)
+
+
 def test_async_host_call_matches_the_synchronous_one(cuda):
     """tfpd_decode_host_async + tfpd_fetch_humans on two alternating contexts == tfpd_decode_host."""
     from helpers import table_tuples
