@@ -23,6 +23,7 @@ frames: weak scaling); no collective on the data path, only the timing reduction
 gather of the human counts.
 """
 import argparse
+import gc
 import json
 import os
 import sys
@@ -224,6 +225,9 @@ def run_ours(args, rank, world, local_rank):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler = ClockSampler(local_rank)      # samples clocks / throttle reasons through every timed region below
     sampler.start()
+    # the timed regions are a few milliseconds long: keep the collector's pauses out of them
+    gc.collect()
+    gc.disable()
 
     # ---- device-resident, one call at a time (decode -> fetch): every kernel runs alone, so this region
     #      gives the per-kernel times (roofline of K1) and the unpipelined step time ----
@@ -363,6 +367,7 @@ def run_ours(args, rank, world, local_rank):
     e2e_humans = int(r.info["n_humans"].sum())
     sampler.stop_flag = True
     sampler.join()
+    gc.enable()
 
     # ---- end to end including the three dense maps back on the host (what sess.run returns) ----
     e2e_dense_value = None
