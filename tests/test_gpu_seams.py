@@ -619,3 +619,15 @@ def test_post_processor_reused_map_buffers(cuda):
         assert np.array_equal(a.peaks, b.peaks)
     a.close()
     b.close()
+
+
+def test_smoke_entry_point(cuda):
+    """__graft_entry__.smoke() is what the driver runs before the bench: keep it inside the GPU suite so that a
+    change of the launch sequence cannot leave it behind."""
+    import importlib
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    entry = importlib.import_module("__graft_entry__")
+    entry.smoke()
