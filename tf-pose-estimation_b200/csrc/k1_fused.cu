@@ -370,7 +370,17 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
         // 3x3 NMS of row Yc = Y-1: vertical max in registers, horizontal neighbours by shuffle
         const int Yc = Y - 1;
         const int j = Yc - 4 * it.iy0;     // candidate row inside the band
-        if (j >= 0 && j < 4 * it.nrows) {  // warp-uniform
+        // Minimal mode writes no peaks tensor: a row in which no pixel of this warp's channel comes near the heat
+        // threshold can neither yield a peak record (needs g > thresh) nor a near-tie count (both sides need
+        // g > thr_lo), so its whole NMS step is skipped -- exact, and most rows of most channels are like that.
+        bool row_live = true;
+        if (!DENSE) {
+            float hp = prev[0];
+#pragma unroll
+            for (int i = 1; i < NPX; ++i) hp = fmaxf(hp, prev[i]);
+            row_live = __any_sync(FULL, hp > thr_lo);
+        }
+        if (j >= 0 && j < 4 * it.nrows && row_live) {  // warp-uniform
             float v[NPX + 2];
 #pragma unroll
             for (int i = 0; i < NPX; ++i) v[i + 1] = fmaxf(vm[i], cur[i]);
