@@ -28,6 +28,7 @@
 #ifndef TFPOSE_DECODE_H_
 #define TFPOSE_DECODE_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -192,6 +193,20 @@ TFPD_API float tfpd_get_part_score(tfpd_ctx *ctx, int cid);
 TFPD_API int tfpd_draw_humans(tfpd_ctx *ctx, uint8_t *images, int on_device, int N, int img_h, int img_w,
                      const int32_t *centers, const int32_t *counts, int max_h, void *stream);
 TFPD_API int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int img_w, void *stream);
+
+/* Image pre-processing in front of the network (the step before the path).
+ *
+ * tfpd_resize_cubic_u8 replaces the cv2.resize(npimg, self.target_size, interpolation=cv2.INTER_CUBIC) of
+ *   TfPoseEstimator._get_scaled_img(npimg, None) (tf_pose/estimator.py:417-424; inference calls it at :534-535):
+ *   src [N,src_h,src_w,cn] uint8 -> dst [N,dst_h,dst_w,cn] uint8, cn = 1..4, the bytes OpenCV's own 8-bit bicubic
+ *   code produces (cv2 with IPP disabled; the closed-source IPP variant differs by 1 LSB on a few percent of the
+ *   pixels).  HOST pointers when on_device == 0 (copied in and out, synchronous); DEVICE pointers otherwise,
+ *   asynchronous on stream.
+ * tfpd_quantize_img replaces TfPoseEstimator._quantize_img (estimator.py:383-388) for float32 images:
+ *   dst[i] = (uint8)((src[i] + 1.0f) / (2.0f / 256)), truncated; count elements. */
+TFPD_API int tfpd_resize_cubic_u8(tfpd_ctx *ctx, const uint8_t *src, int on_device, int N, int src_h, int src_w, int cn,
+                         uint8_t *dst, int dst_h, int dst_w, void *stream);
+TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, size_t count, uint8_t *dst, void *stream);
 
 /* Tuning options, by name (unknown name or out-of-range value -> TFPD_ERR_INVALID):
  *   "k1_ctas"      CTAs of the fused upsample/smoother/NMS kernel; 0 = one per SM (default).  The kernel is

@@ -252,7 +252,35 @@ def ros_golden(est_mod):
     print("ros persons:", len(rec["persons"]), "persons,", sum(len(p) for p in rec["persons"]), "body parts")
 
 
+PREPROC_CASES = [  # (seed, src_h, src_w, cn, dst_w, dst_h)
+    (0, 480, 640, 3, 432, 368), (1, 720, 1280, 3, 432, 368), (2, 368, 432, 3, 656, 368), (3, 100, 75, 3, 432, 368),
+    (4, 333, 517, 3, 431, 367), (5, 50, 61, 1, 43, 37), (6, 64, 64, 4, 33, 129), (7, 7, 9, 3, 20, 20),
+    (8, 2, 2, 1, 9, 9), (9, 1, 5, 3, 4, 3), (10, 200, 300, 2, 101, 55)]
+
+
+def preproc_image(seed, sh, sw, cn):
+    return np.random.default_rng(9000 + seed).integers(0, 256, (sh, sw, cn), dtype=np.uint8)
+
+
+def preproc_golden():
+    """cv2.resize(INTER_CUBIC) itself (the call of estimator.py:423), IPP off = OpenCV's own code.  Stores the
+    sha256 of every output and one small output in full."""
+    import cv2
+    cv2.ipp.setUseIPP(False)
+    shas = []
+    for (seed, sh, sw, cn, dw, dh) in PREPROC_CASES:
+        out = cv2.resize(preproc_image(seed, sh, sw, cn), (dw, dh), interpolation=cv2.INTER_CUBIC)
+        shas.append(hashlib.sha256(np.ascontiguousarray(out).tobytes()).hexdigest())
+    small = cv2.resize(preproc_image(7, 7, 9, 3), (20, 20), interpolation=cv2.INTER_CUBIC)
+    np.savez_compressed(os.path.join(HERE, "preproc_cubic.npz"), cases=np.array(PREPROC_CASES, np.int64),
+                        sha256=np.array(shas), small=small, cv2_version=np.array(cv2.__version__))
+    print("preproc cubic", len(shas), "cases, cv2", cv2.__version__)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "preproc":
+        preproc_golden()
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "boxes":
         boxes_golden(reference_estimator("asbuilt"))
         return

@@ -1,0 +1,128 @@
+"""Image pre-processing in front of the network, SURVEY.md 8f rank 4: the bicubic resize of
+``TfPoseEstimator._get_scaled_img(npimg, None)`` (tf_pose/estimator.py:417-424) and ``_quantize_img`` (:383-388).
+
+Checker = oracle/preproc_oracle.py, itself pinned (CPU tests) against tests/golden/preproc_cubic.npz (outputs of
+``cv2.resize(..., INTER_CUBIC)`` with IPP off, made by tests/golden/make_golden.py preproc) and, where cv2 is
+importable, against cv2 live on random sizes.  GPU tests compare the CUDA kernels through the C-ABI, bit for bit."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import tfpose_b200 as tp
+from oracle import preproc_oracle as PO
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = np.load(os.path.join(HERE, "golden", "preproc_cubic.npz"))
+
+
+def golden_image(seed, sh, sw, cn):
+    return np.random.default_rng(9000 + seed).integers(0, 256, (sh, sw, cn), dtype=np.uint8)
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def test_oracle_matches_golden_cv2_outputs():
+    for (seed, sh, sw, cn, dw, dh), want in zip(GOLD["cases"].tolist(), GOLD["sha256"].tolist()):
+        out = PO.resize_cubic_u8(golden_image(seed, sh, sw, cn), dw, dh)
+        assert out.shape == (dh, dw, cn)
+        got = sha(out[:, :, 0] if cn == 1 else out)     # cv2 drops a single channel axis
+        assert got == want, (seed, sh, sw, cn, dw, dh)
+    assert np.array_equal(PO.resize_cubic_u8(golden_image(7, 7, 9, 3), 20, 20), GOLD["small"])
+
+
+def test_oracle_matches_cv2_live_on_random_sizes():
+    cv2 = pytest.importorskip("cv2")
+    had = cv2.ipp.useIPP()
+    cv2.ipp.setUseIPP(False)      # OpenCV's own code; the closed-source IPP path differs by 1 LSB on some sizes
+    try:
+        rng = np.random.default_rng(77)
+        for _ in range(25):
+            sh, sw, dw, dh = (int(v) for v in rng.integers(3, 200, 4))
+            cn = int(rng.choice([1, 3, 4]))
+            img = rng.integers(0, 256, (sh, sw, cn), dtype=np.uint8)
+            ref = cv2.resize(img, (dw, dh), interpolation=cv2.INTER_CUBIC).reshape(dh, dw, cn)
+            assert np.array_equal(PO.resize_cubic_u8(img, dw, dh), ref), (sh, sw, cn, dw, dh)
+    finally:
+        cv2.ipp.setUseIPP(had)
+
+
+def test_oracle_identity_and_quantize():
+    img = golden_image(3, 20, 30, 3)
+    assert PO.get_scaled_img(img, (30, 20))[0][0] is img               # same size: returned untouched (:420)
+    assert PO.get_scaled_img(img, (15, 10))[0][0].shape == (10, 15, 3)
+    assert PO.get_scaled_img(img, (15, 10))[1] == [(0.0, 0.0, 1.0, 1.0)]
+    x = np.array([-1.0, -0.5, 0.0, 0.4999, 0.99], np.float32)
+    assert PO.quantize_img(x).tolist() == [0, 64, 128, 191, 254]
+
+
+@pytest.fixture(scope="module")
+def decoder(cuda):
+    d = tp.PoseDecoder(max_batch=1, max_upsample=(184, 216))
+    yield d
+    d.close()
+
+
+@pytest.mark.gpu
+def test_resize_cubic_matches_oracle_and_golden(decoder):
+    for (seed, sh, sw, cn, dw, dh), want in zip(GOLD["cases"].tolist(), GOLD["sha256"].tolist()):
+        img = golden_image(seed, sh, sw, cn)
+        out = decoder.resize_cubic(img, (dw, dh))
+        assert out.shape == (dh, dw, cn) and out.dtype == np.uint8
+        assert np.array_equal(out, PO.resize_cubic_u8(img, dw, dh)), (seed, sh, sw, cn, dw, dh)
+        assert sha(out[:, :, 0] if cn == 1 else out) == want
+    g = golden_image(5, 50, 61, 1)[:, :, 0]
+    assert decoder.resize_cubic(g, (43, 37)).shape == (37, 43)         # 2-D in, 2-D out like cv2
+
+
+@pytest.mark.gpu
+def test_resize_cubic_batch_on_device(decoder):
+    import torch
+    rng = np.random.default_rng(5)
+    imgs = rng.integers(0, 256, (6, 480, 640, 3), dtype=np.uint8)
+    imgs[1] = 255
+    imgs[2] = 0
+    imgs[3, ::2] = 0
+    imgs[3, 1::2] = 255                                                 # overshoot: saturation on both sides
+    out = decoder.resize_cubic(torch.from_numpy(imgs).cuda(), (432, 368))
+    torch.cuda.synchronize()
+    out = out.cpu().numpy()
+    for i in range(len(imgs)):
+        assert np.array_equal(out[i], PO.resize_cubic_u8(imgs[i], 432, 368)), i
+    assert np.array_equal(decoder.resize_cubic(imgs, (432, 368)), out)  # host-pointer call, same bytes
+
+
+@pytest.mark.gpu
+def test_quantize_and_scaled_img_mirror(decoder, cuda):
+    import torch
+    rng = np.random.default_rng(6)
+    x = rng.uniform(-1.0, 1.0, (368, 432, 3)).astype(np.float32)
+    x[0, 0] = (-1.0, 0.0, 0.99999994)
+    want = PO.quantize_img(x)
+    assert np.array_equal(decoder.quantize_img(x), want)
+    assert np.array_equal(decoder.quantize_img(torch.from_numpy(x).cuda()).cpu().numpy(), want)
+    post = tp.TfPosePostProcessor(target_size=(432, 368))
+    try:
+        img = golden_image(0, 480, 640, 3)
+        rois, ratios = post._get_scaled_img(img, None)
+        assert ratios == [(0.0, 0.0, 1.0, 1.0)] and np.array_equal(rois[0], PO.resize_cubic_u8(img, 432, 368))
+        same = golden_image(1, 368, 432, 3)
+        assert post._get_scaled_img(same, None)[0][0] is same
+        assert np.array_equal(post._quantize_img(x), want)
+        with pytest.raises(NotImplementedError):
+            post._get_scaled_img(img, 1.0)
+    finally:
+        post.close()
+
+
+@pytest.mark.gpu
+def test_preproc_rejects_bad_arguments(decoder):
+    with pytest.raises(ValueError):
+        decoder.resize_cubic(np.zeros((4, 4, 3), np.float32), (8, 8))
+    with pytest.raises(Exception):
+        decoder.resize_cubic(np.zeros((4, 4, 5), np.uint8), (8, 8))    # 5 channels: TFPD_ERR_INVALID
+    with pytest.raises(ValueError):
+        decoder.quantize_img(np.zeros((4, 4), np.float64))

@@ -87,6 +87,8 @@ SIGNATURES = {
     "tfpd_set_option": (_I, [_P, C.c_char_p, _I]),
     "tfpd_draw_humans": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _I, _P]),
     "tfpd_draw_decoded": (_I, [_P, _P, _I, _I, _P]),
+    "tfpd_resize_cubic_u8": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _I, _I, _P]),
+    "tfpd_quantize_img": (_I, [_P, _P, _I, C.c_size_t, _P, _P]),
 }
 
 _lib = None

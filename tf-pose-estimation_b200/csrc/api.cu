@@ -54,6 +54,7 @@ struct tfpd_ctx {
     DevBuf poly_buf;                    // per-phase smoother weights of the power-of-two path, for factor poly_log2f
     int poly_log2f = -1, poly_T = 0;
     DevBuf draw_ids, draw_centers, draw_counts, draw_img;  // draw_humans scratch (lazily sized)
+    DevBuf pre_src, pre_dst;            // host-pointer calls of the image pre-processing (lazily sized)
     DevBuf in_buf, dense_buf, gen_buf;  // lazily sized: host-call input, dense outputs, generic-path scratch
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     // host-buffer calls: H2D, kernels and D2H of successive frame chunks run on three streams
@@ -442,6 +443,8 @@ void tfpd_destroy(tfpd_ctx *ctx) {
     ctx->draw_centers.release();
     ctx->draw_counts.release();
     ctx->draw_img.release();
+    ctx->pre_src.release();
+    ctx->pre_dst.release();
     delete ctx;
 }
 
@@ -508,6 +511,59 @@ int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int img_w, void
         launch_draw((const int *)ctx->draw_centers.p, (const int *)ctx->draw_counts.p, max_h, images,
                     (int *)ctx->draw_ids.p, N, img_h, img_w, s) < 0)
         return fail(ctx, TFPD_ERR_CUDA, "draw kernels failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return TFPD_OK;
+}
+
+int tfpd_resize_cubic_u8(tfpd_ctx *ctx, const uint8_t *src, int on_device, int N, int src_h, int src_w, int cn,
+                         uint8_t *dst, int dst_h, int dst_w, void *stream) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!src || !dst) return fail(ctx, TFPD_ERR_INVALID, "resize_cubic_u8: null argument");
+    if (N < 1 || N > 65535 || src_h < 1 || src_w < 1 || dst_h < 1 || dst_w < 1 || dst_h > 65535 || src_h > 32767 ||
+        src_w > 32767 || dst_w > 32767)
+        return fail(ctx, TFPD_ERR_INVALID, "resize_cubic_u8: bad dimensions %dx%d -> %dx%d, N=%d", src_h, src_w, dst_h, dst_w, N);
+    if (cn < 1 || cn > 4) return fail(ctx, TFPD_ERR_INVALID, "resize_cubic_u8: %d channels (1..4 supported)", cn);
+    ON_CTX_DEVICE(ctx);
+    cudaStream_t s = on_device ? (cudaStream_t)stream : ctx->st_work;
+    const size_t in_bytes = (size_t)N * src_h * src_w * cn, out_bytes = (size_t)N * dst_h * dst_w * cn;
+    const unsigned char *d_src = src;
+    unsigned char *d_dst = dst;
+    if (!on_device) {
+        CUDA_TRY(ctx, ctx->pre_src.reserve(in_bytes));
+        CUDA_TRY(ctx, ctx->pre_dst.reserve(out_bytes));
+        d_src = (const unsigned char *)ctx->pre_src.p;
+        d_dst = (unsigned char *)ctx->pre_dst.p;
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pre_src.p, src, in_bytes, cudaMemcpyHostToDevice, s));
+    }
+    if (launch_resize_cubic_u8(d_src, d_dst, N, src_h, src_w, cn, dst_h, dst_w, s) < 0)
+        return fail(ctx, TFPD_ERR_CUDA, "resize kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (!on_device) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(dst, d_dst, out_bytes, cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    }
+    return TFPD_OK;
+}
+
+int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, size_t count, uint8_t *dst, void *stream) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!src || !dst) return fail(ctx, TFPD_ERR_INVALID, "quantize_img: null argument");
+    if (count == 0) return TFPD_OK;
+    ON_CTX_DEVICE(ctx);
+    cudaStream_t s = on_device ? (cudaStream_t)stream : ctx->st_work;
+    const float *d_src = src;
+    unsigned char *d_dst = dst;
+    if (!on_device) {
+        CUDA_TRY(ctx, ctx->pre_src.reserve(count * 4));
+        CUDA_TRY(ctx, ctx->pre_dst.reserve(count));
+        d_src = (const float *)ctx->pre_src.p;
+        d_dst = (unsigned char *)ctx->pre_dst.p;
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pre_src.p, src, count * 4, cudaMemcpyHostToDevice, s));
+    }
+    if (launch_quantize_img(d_src, d_dst, count, ctx->sm_count, s) < 0)
+        return fail(ctx, TFPD_ERR_CUDA, "quantize kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
+    if (!on_device) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(dst, d_dst, count, cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(ctx, cudaStreamSynchronize(s));
+    }
     return TFPD_OK;
 }
 

@@ -264,6 +264,55 @@ class PoseDecoder(object):
             return images
         return buf[0] if single else buf
 
+    # -- image pre-processing in front of the network (estimator.py:383-388, :417-424) ---------
+    def resize_cubic(self, images, target_size):
+        """``cv2.resize(img, target_size, interpolation=cv2.INTER_CUBIC)`` for uint8 images: NumPy [H,W], [H,W,C] or
+        [N,H,W,C] (host in, host out) or a contiguous CUDA uint8 tensor [N,H,W,C] (device in, device out,
+        asynchronous on the current stream).  ``target_size = (w, h)`` as cv2 and the reference ctor take it.
+        The bytes are those of OpenCV's own bicubic code (cv2 with IPP off)."""
+        dw, dh = int(target_size[0]), int(target_size[1])
+        if isinstance(images, np.ndarray):
+            if images.dtype != np.uint8 or images.ndim not in (2, 3, 4):
+                raise ValueError("images must be uint8 [H,W], [H,W,C] or [N,H,W,C]")
+            src = np.ascontiguousarray(images)
+            shp = src.shape
+            if src.ndim == 2:
+                src = src[None, :, :, None]
+            elif src.ndim == 3:
+                src = src[None]
+            n, sh, sw, cn = src.shape
+            dst = np.empty((n, dh, dw, cn), np.uint8)
+            self._check(self._L.tfpd_resize_cubic_u8(self._ctx, src.ctypes.data, 0, n, sh, sw, cn, dst.ctypes.data,
+                                                     dh, dw, None))
+            return dst[0, :, :, 0] if len(shp) == 2 else (dst[0] if len(shp) == 3 else dst)
+        import torch
+        if images.dtype != torch.uint8 or images.dim() != 4 or not images.is_cuda or not images.is_contiguous():
+            raise ValueError("CUDA images must be contiguous uint8 [N,H,W,C]")
+        n, sh, sw, cn = (int(v) for v in images.shape)
+        dst = torch.empty((n, dh, dw, cn), dtype=torch.uint8, device=images.device)
+        stream = C.c_void_p(torch.cuda.current_stream(images.device).cuda_stream)
+        self._check(self._L.tfpd_resize_cubic_u8(self._ctx, images.data_ptr(), 1, n, sh, sw, cn, dst.data_ptr(),
+                                                 dh, dw, stream))
+        return dst
+
+    def quantize_img(self, npimg):
+        """``TfPoseEstimator._quantize_img`` (estimator.py:383-388) for float32 input: NumPy array (host) or a
+        contiguous CUDA float32 tensor (device, asynchronous on the current stream); same shape, uint8."""
+        if isinstance(npimg, np.ndarray):
+            if npimg.dtype != np.float32:
+                raise ValueError("quantize_img takes float32 images")
+            src = np.ascontiguousarray(npimg)
+            dst = np.empty(src.shape, np.uint8)
+            self._check(self._L.tfpd_quantize_img(self._ctx, src.ctypes.data, 0, src.size, dst.ctypes.data, None))
+            return dst
+        import torch
+        if npimg.dtype != torch.float32 or not npimg.is_cuda or not npimg.is_contiguous():
+            raise ValueError("CUDA images must be contiguous float32")
+        dst = torch.empty(npimg.shape, dtype=torch.uint8, device=npimg.device)
+        stream = C.c_void_p(torch.cuda.current_stream(npimg.device).cuda_stream)
+        self._check(self._L.tfpd_quantize_img(self._ctx, npimg.data_ptr(), 1, npimg.numel(), dst.data_ptr(), stream))
+        return dst
+
     def draw_decoded(self, images, stream=None):
         """Draw the humans of the last decode on this decoder into the CUDA uint8 tensor ``images[N,H,W,3]``
         straight from the device tables (nothing crosses PCIe).  Asynchronous on ``stream``."""

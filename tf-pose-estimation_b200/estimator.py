@@ -115,5 +115,21 @@ class TfPosePostProcessor(object):
         CUDA kernels on a headless buffer: same pixels as the cv2.circle / cv2.line calls of the reference."""
         return self._decoder.draw_humans(npimg, humans, imgcopy=imgcopy)
 
+    def _quantize_img(self, npimg):
+        """``TfPoseEstimator._quantize_img`` (estimator.py:383-388; a staticmethod there, it needs the GPU
+        context here)."""
+        return self._decoder.quantize_img(npimg)
+
+    def _get_scaled_img(self, npimg, scale=None):
+        """``TfPoseEstimator._get_scaled_img(npimg, None)`` (estimator.py:417-424), the only form ``inference``
+        uses (:534-535): bicubic resize to ``target_size`` unless the image already has it.  The sliding-window
+        forms (float / tuple ``scale``, :425-500) feed a multi-scale merge the reference never implemented and
+        need the absent ``slidingwindow`` package: not provided."""
+        if scale is not None:
+            raise NotImplementedError("only scale=None (the form inference() uses) is provided")
+        if npimg.shape[:2] != (self.target_size[1], self.target_size[0]):
+            npimg = self._decoder.resize_cubic(npimg, self.target_size)
+        return [npimg], [(0.0, 0.0, 1.0, 1.0)]
+
     def close(self):
         self._decoder.close()

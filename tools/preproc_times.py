@@ -1,0 +1,53 @@
+"""Times the pre-processing kernels (k_resize_cubic_u8, k_quantize_img) on device tensors with CUDA events.
+usage: python tools/preproc_times.py [batch] [src_h src_w]"""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import tfpose_b200 as tp  # noqa: E402
+
+
+def timed(fn, reps=50, warm=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+
+def main():
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+    sh, sw = (int(sys.argv[2]), int(sys.argv[3])) if len(sys.argv) > 3 else (480, 640)
+    d = tp.PoseDecoder(max_batch=1, max_upsample=(184, 216))
+    # 8 rotating batches of source images: 8 x n x 0.92 MB, beyond the 126 MB L2 for n = 64
+    srcs = [torch.randint(0, 256, (n, sh, sw, 3), dtype=torch.uint8, device="cuda") for _ in range(8)]
+    i = [0]
+
+    def resize():
+        i[0] += 1
+        return d.resize_cubic(srcs[i[0] % 8], (432, 368))
+
+    ms = timed(resize)
+    by = n * (sh * sw * 3 + 368 * 432 * 3)
+    print("resize_cubic %dx%dx3 -> 368x432x3, batch %d: %.3f ms, %.0f frames/s, %.0f GB/s algorithmic" %
+          (sh, sw, n, ms, n / ms * 1e3, by / ms / 1e6))
+    xs = [torch.rand((n, 368, 432, 3), device="cuda") * 2 - 1 for _ in range(4)]
+
+    def quant():
+        i[0] += 1
+        return d.quantize_img(xs[i[0] % 4])
+
+    ms = timed(quant)
+    print("quantize_img batch %d: %.3f ms, %.0f GB/s" % (n, ms, n * 368 * 432 * 3 * 5 / ms / 1e6))
+    d.close()
+
+
+if __name__ == "__main__":
+    main()
