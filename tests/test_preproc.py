@@ -67,13 +67,20 @@ def decoder(cuda):
 
 
 @pytest.mark.gpu
-def test_resize_cubic_matches_oracle_and_golden(decoder):
-    for (seed, sh, sw, cn, dw, dh), want in zip(GOLD["cases"].tolist(), GOLD["sha256"].tolist()):
-        img = golden_image(seed, sh, sw, cn)
-        out = decoder.resize_cubic(img, (dw, dh))
-        assert out.shape == (dh, dw, cn) and out.dtype == np.uint8
-        assert np.array_equal(out, PO.resize_cubic_u8(img, dw, dh)), (seed, sh, sw, cn, dw, dh)
-        assert sha(out[:, :, 0] if cn == 1 else out) == want
+@pytest.mark.parametrize("path", [0, 1, 2, 3])       # automatic / tiled / one thread per output pixel / strip
+def test_resize_cubic_matches_oracle_and_golden(decoder, path):
+    decoder.set_option("resize_path", path)
+    try:
+        for (seed, sh, sw, cn, dw, dh), want in zip(GOLD["cases"].tolist(), GOLD["sha256"].tolist()):
+            img = golden_image(seed, sh, sw, cn)
+            out = decoder.resize_cubic(img, (dw, dh))
+            assert out.shape == (dh, dw, cn) and out.dtype == np.uint8
+            assert np.array_equal(out, PO.resize_cubic_u8(img, dw, dh)), (seed, sh, sw, cn, dw, dh)
+            assert sha(out[:, :, 0] if cn == 1 else out) == want
+        big = golden_image(11, 900, 700, 3)                         # x7 / x9 down-scale: tall source tiles
+        assert np.array_equal(decoder.resize_cubic(big, (100, 100)), PO.resize_cubic_u8(big, 100, 100))
+    finally:
+        decoder.set_option("resize_path", 0)
     g = golden_image(5, 50, 61, 1)[:, :, 0]
     assert decoder.resize_cubic(g, (43, 37)).shape == (37, 43)         # 2-D in, 2-D out like cv2
 
@@ -93,6 +100,11 @@ def test_resize_cubic_batch_on_device(decoder):
     for i in range(len(imgs)):
         assert np.array_equal(out[i], PO.resize_cubic_u8(imgs[i], 432, 368)), i
     assert np.array_equal(decoder.resize_cubic(imgs, (432, 368)), out)  # host-pointer call, same bytes
+    for shift in (1, 2, 3):                                             # source not 4-byte aligned: word loads realign
+        flat = torch.zeros(imgs[:2].size + 8, dtype=torch.uint8, device="cuda")
+        view = flat[shift:shift + imgs[:2].size].view(2, 480, 640, 3)
+        view.copy_(torch.from_numpy(imgs[:2]))
+        assert np.array_equal(decoder.resize_cubic(view, (432, 368)).cpu().numpy(), out[:2]), shift
 
 
 @pytest.mark.gpu
@@ -104,6 +116,12 @@ def test_quantize_and_scaled_img_mirror(decoder, cuda):
     want = PO.quantize_img(x)
     assert np.array_equal(decoder.quantize_img(x), want)
     assert np.array_equal(decoder.quantize_img(torch.from_numpy(x).cuda()).cpu().numpy(), want)
+    odd = x.ravel()[:1001]                                              # count not a multiple of 4: scalar tail
+    assert np.array_equal(decoder.quantize_img(odd), PO.quantize_img(odd))
+    shifted = torch.from_numpy(x).cuda().ravel()[1:1000].contiguous()
+    assert np.array_equal(decoder.quantize_img(shifted.clone()).cpu().numpy(), PO.quantize_img(x.ravel()[1:1000]))
+    assert np.array_equal(decoder.quantize_img(torch.from_numpy(x).cuda().ravel()[1:1000]).cpu().numpy(),
+                          PO.quantize_img(x.ravel()[1:1000]))           # 4-byte aligned only: unvectorised path
     post = tp.TfPosePostProcessor(target_size=(432, 368))
     try:
         img = golden_image(0, 480, 640, 3)

@@ -54,6 +54,7 @@ struct tfpd_ctx {
     DevBuf poly_buf;                    // per-phase smoother weights of the power-of-two path, for factor poly_log2f
     int poly_log2f = -1, poly_T = 0;
     DevBuf draw_ids, draw_centers, draw_counts, draw_img;  // draw_humans scratch (lazily sized)
+    int resize_path = 0;                // 0 auto (= 3), 1 tiled, 2 one thread per output pixel, 3 strip
     DevBuf pre_src, pre_dst;            // host-pointer calls of the image pre-processing (lazily sized)
     DevBuf in_buf, dense_buf, gen_buf;  // lazily sized: host-call input, dense outputs, generic-path scratch
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -534,7 +535,7 @@ int tfpd_resize_cubic_u8(tfpd_ctx *ctx, const uint8_t *src, int on_device, int N
         d_dst = (unsigned char *)ctx->pre_dst.p;
         CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pre_src.p, src, in_bytes, cudaMemcpyHostToDevice, s));
     }
-    if (launch_resize_cubic_u8(d_src, d_dst, N, src_h, src_w, cn, dst_h, dst_w, s) < 0)
+    if (launch_resize_cubic_u8(d_src, d_dst, N, src_h, src_w, cn, dst_h, dst_w, ctx->resize_path, s) < 0)
         return fail(ctx, TFPD_ERR_CUDA, "resize kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
     if (!on_device) {
         CUDA_TRY(ctx, cudaMemcpyAsync(dst, d_dst, out_bytes, cudaMemcpyDeviceToHost, s));
@@ -590,6 +591,9 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
     } else if (!strcmp(name, "pow2_path")) {
         if (value < 0 || value > 4) return fail(ctx, TFPD_ERR_INVALID, "pow2_path=%d out of range", value);
         ctx->pow2_path = value;
+    } else if (!strcmp(name, "resize_path")) {
+        if (value < 0 || value > 3) return fail(ctx, TFPD_ERR_INVALID, "resize_path=%d out of range", value);
+        ctx->resize_path = value;
     } else if (!strcmp(name, "k1_l2")) {
         if (value < 0 || value > 7) return fail(ctx, TFPD_ERR_INVALID, "k1_l2=%d out of range", value);
         ctx->k1_l2_knobs = value;

@@ -34,10 +34,13 @@ def main():
         i[0] += 1
         return d.resize_cubic(srcs[i[0] % 8], (432, 368))
 
-    ms = timed(resize)
     by = n * (sh * sw * 3 + 368 * 432 * 3)
-    print("resize_cubic %dx%dx3 -> 368x432x3, batch %d: %.3f ms, %.0f frames/s, %.0f GB/s algorithmic" %
-          (sh, sw, n, ms, n / ms * 1e3, by / ms / 1e6))
+    for path, name in ((3, "strip"), (1, "tiled"), (2, "per-pixel")):
+        d.set_option("resize_path", path)
+        ms = timed(resize)
+        print("resize_cubic %s %dx%dx3 -> 368x432x3, batch %d: %.3f ms, %.0f frames/s, %.0f GB/s algorithmic" %
+              (name, sh, sw, n, ms, n / ms * 1e3, by / ms / 1e6))
+    d.set_option("resize_path", 0)
     xs = [torch.rand((n, 368, 432, 3), device="cuda") * 2 - 1 for _ in range(4)]
 
     def quant():
