@@ -94,11 +94,20 @@ __global__ void __launch_bounds__(128) k_resize_cubic_u8(const unsigned char *__
 // of their source rows, so a source row's horizontal pass runs once per strip instead of once per output row that
 // reads it, and the column taps are computed once per strip; the strip's row taps sit in shared memory.  The kernel
 // is issue-bound (ALU, not L1 wavefronts: fetching the taps as realigned 32-bit words measured slower), so the
-// instruction count per output pixel is what counts.  (A word-load form of the per-pixel kernel measured 0.170 ms
-// against 0.152 ms per 64 frames 640x480 -> 432x368.)
+// instruction count per output pixel is what counts.  Measured per 64 frames 640x480x3 -> 432x368x3: per-pixel form
+// 0.152 ms (0.170 with word loads), tiled 0.173, this one 0.084 (0.093 with word loads; CTA widths that leave fewer
+// idle lanes across the 432 columns change nothing).
 constexpr int kStrip = 16;
 
-template <int CN>
+// int <-> float through the 1.5*2^23 constant: exact for |v| < 2^22 (horizontal sums stay below 2^20; the vertical
+// sum is a pixel value), round-half-even like cvtps2dq / __float2int_rn, and full-rate FADD/IADD instead of the
+// quarter-rate conversion pipe (ncu r01j: the conversions were a third of the strip kernel's issue slots).
+__device__ __forceinline__ float exact_i2f(int v) { return __fadd_rn(__int_as_float(v + 0x4B400000), -12582912.0f); }
+__device__ __forceinline__ int round_f2i(float v) { return __float_as_int(__fadd_rn(v, 12582912.0f)) - 0x4B400000; }
+
+// TAIL: the row length dw*CN is not a multiple of 8, so the last elements take the fixed-point cast and the integer
+// sums have to be kept beside their float copies.
+template <int CN, bool TAIL>
 __global__ void __launch_bounds__(128) k_resize_cubic_u8_strip(const unsigned char *__restrict__ src,
                                                                 unsigned char *__restrict__ dst, int sh, int sw, int dh,
                                                                 int dw, double scale_x, double scale_y) {
@@ -116,23 +125,28 @@ __global__ void __launch_bounds__(128) k_resize_cubic_u8_strip(const unsigned ch
     __syncthreads();
     if (x >= dw) return;
     const CubicTap tx = cubic_tap(x, scale_x);
-    int col[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) col[k] = max(0, min(sw - 1, tx.ofs - 1 + k)) * CN;
+    // the four tap columns as pointers into row 0 of this image; a source row adds one 32-bit offset
     const unsigned char *img = src + (size_t)n * sh * (size_t)sw * CN;
-    auto hrow = [&](int u, int (&out)[CN]) {      // horizontal sums of source row clamp(u)
-        const unsigned char *p = img + (size_t)max(0, min(sh - 1, u)) * sw * CN;
+    const unsigned char *pc0 = img + max(0, min(sw - 1, tx.ofs - 1)) * CN, *pc1 = img + max(0, min(sw - 1, tx.ofs)) * CN,
+                        *pc2 = img + max(0, min(sw - 1, tx.ofs + 1)) * CN, *pc3 = img + max(0, min(sw - 1, tx.ofs + 2)) * CN;
+    const unsigned pitch = (unsigned)sw * CN;
+    auto hrow = [&](int u, int (&hi)[CN], float (&hf)[CN]) {      // horizontal sums of source row clamp(u)
+        const unsigned off = (unsigned)max(0, min(sh - 1, u)) * pitch;     // < 2^32: sh, sw <= 32767, CN <= 4 (checked by the API)
 #pragma unroll
-        for (int c = 0; c < CN; ++c)
-            out[c] = (int)__ldg(p + col[0] + c) * tx.c[0] + (int)__ldg(p + col[1] + c) * tx.c[1] +
-                     (int)__ldg(p + col[2] + c) * tx.c[2] + (int)__ldg(p + col[3] + c) * tx.c[3];
+        for (int c = 0; c < CN; ++c) {
+            const int v = (int)__ldg(pc0 + off + c) * tx.c[0] + (int)__ldg(pc1 + off + c) * tx.c[1] +
+                          (int)__ldg(pc2 + off + c) * tx.c[2] + (int)__ldg(pc3 + off + c) * tx.c[3];
+            hi[c] = v;
+            hf[c] = exact_i2f(v);
+        }
     };
-    int h0[CN], h1[CN], h2[CN], h3[CN];
+    int i0[CN], i1[CN], i2[CN], i3[CN];
+    float h0[CN], h1[CN], h2[CN], h3[CN];
     int base = yofs[0] - 1;                       // window = unclamped source rows base .. base+3
-    hrow(base, h0);
-    hrow(base + 1, h1);
-    hrow(base + 2, h2);
-    hrow(base + 3, h3);
+    hrow(base, i0, h0);
+    hrow(base + 1, i1, h1);
+    hrow(base + 2, i2, h2);
+    hrow(base + 3, i3, h3);
     const float sc = 1.0f / (2048.0f * 2048.0f);
     const int simd_end = (dw * CN) & ~7;
     unsigned char *q = dst + (((size_t)n * dh + y0) * dw + x) * CN;
@@ -140,10 +154,10 @@ __global__ void __launch_bounds__(128) k_resize_cubic_u8_strip(const unsigned ch
         const int nb = yofs[yl] - 1;              // uniform over the CTA: no divergence in the window update
         if (nb - base >= 4) {
             base = nb;
-            hrow(base, h0);
-            hrow(base + 1, h1);
-            hrow(base + 2, h2);
-            hrow(base + 3, h3);
+            hrow(base, i0, h0);
+            hrow(base + 1, i1, h1);
+            hrow(base + 2, i2, h2);
+            hrow(base + 3, i3, h3);
         } else {
             for (; base < nb; ++base) {
 #pragma unroll
@@ -151,8 +165,13 @@ __global__ void __launch_bounds__(128) k_resize_cubic_u8_strip(const unsigned ch
                     h0[c] = h1[c];
                     h1[c] = h2[c];
                     h2[c] = h3[c];
+                    if (TAIL) {
+                        i0[c] = i1[c];
+                        i1[c] = i2[c];
+                        i2[c] = i3[c];
+                    }
                 }
-                hrow(base + 4, h3);
+                hrow(base + 4, i3, h3);
             }
         }
         const int c0 = ycoef[yl][0], c1 = ycoef[yl][1], c2 = ycoef[yl][2], c3 = ycoef[yl][3];
@@ -160,14 +179,14 @@ __global__ void __launch_bounds__(128) k_resize_cubic_u8_strip(const unsigned ch
 #pragma unroll
         for (int c = 0; c < CN; ++c) {
             int v;
-            if (x * CN + c < simd_end) {
-                float acc = __fmul_rn((float)h3[c], b3);
-                acc = __fadd_rn(__fmul_rn((float)h2[c], b2), acc);
-                acc = __fadd_rn(__fmul_rn((float)h1[c], b1), acc);
-                acc = __fadd_rn(__fmul_rn((float)h0[c], b0), acc);
-                v = __float2int_rn(acc);
+            if (!TAIL || x * CN + c < simd_end) {
+                float acc = __fmul_rn(h3[c], b3);
+                acc = __fadd_rn(__fmul_rn(h2[c], b2), acc);
+                acc = __fadd_rn(__fmul_rn(h1[c], b1), acc);
+                acc = __fadd_rn(__fmul_rn(h0[c], b0), acc);
+                v = round_f2i(fminf(fmaxf(acc, -1024.0f), 1024.0f));      // clamp first: the rounding trick needs |acc| < 2^22
             } else {
-                v = (h0[c] * c0 + h1[c] * c1 + h2[c] * c2 + h3[c] * c3 + (1 << 21)) >> 22;
+                v = (i0[c] * c0 + i1[c] * c1 + i2[c] * c2 + i3[c] * c3 + (1 << 21)) >> 22;
             }
             q[c] = (unsigned char)max(0, min(255, v));
         }
@@ -299,8 +318,12 @@ int launch_resize_cubic_u8(const unsigned char *src, unsigned char *dst, int N, 
             k_resize_cubic_u8_tiled<CN><<<dim3(parts, (dh + kTY - 1) / kTY, N), kPreThreads, smem, s>>>(                \
                 src, dst, sh, sw, dh, dw, scale_x, scale_y, tile_w, max_rows);                                         \
         } else if (strip) {                                                                                            \
-            k_resize_cubic_u8_strip<CN><<<dim3((dw + 127) / 128, (dh + kStrip - 1) / kStrip, N), 128, 0, s>>>(          \
-                src, dst, sh, sw, dh, dw, scale_x, scale_y);                                                           \
+            if ((dw * CN) & 7)                                                                                         \
+                k_resize_cubic_u8_strip<CN, true><<<dim3((dw + 127) / 128, (dh + kStrip - 1) / kStrip, N), 128, 0, s>>>( \
+                    src, dst, sh, sw, dh, dw, scale_x, scale_y);                                                       \
+            else                                                                                                       \
+                k_resize_cubic_u8_strip<CN, false><<<dim3((dw + 127) / 128, (dh + kStrip - 1) / kStrip, N), 128, 0, s>>>( \
+                    src, dst, sh, sw, dh, dw, scale_x, scale_y);                                                       \
         } else {                                                                                                       \
             k_resize_cubic_u8<CN><<<dim3((dw + 127) / 128, dh, N), 128, 0, s>>>(src, dst, sh, sw, dh, dw, scale_x,      \
                                                                                scale_y);                               \

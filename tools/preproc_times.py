@@ -50,6 +50,21 @@ def main():
     ms = timed(quant)
     print("quantize_img batch %d: %.3f ms, %.0f GB/s" % (n, ms, n * 368 * 432 * 3 * 5 / ms / 1e6))
     d.close()
+    try:                                            # the reference's own call on this box's host cores
+        import time
+
+        import cv2
+        imgs = srcs[0].cpu().numpy()
+        for ipp in (True, False):
+            cv2.ipp.setUseIPP(ipp)
+            t = time.perf_counter()
+            for im in imgs:
+                cv2.resize(im, (432, 368), interpolation=cv2.INTER_CUBIC)
+            dt = time.perf_counter() - t
+            print("cv2.resize INTER_CUBIC on the host (%d threads, IPP %s): %.3f ms per frame, %.0f frames/s" %
+                  (cv2.getNumThreads(), "on" if ipp else "off", dt / n * 1e3, n / dt))
+    except ImportError:
+        pass
 
 
 if __name__ == "__main__":
