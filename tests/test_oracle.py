@@ -85,6 +85,42 @@ def test_blur_is_the_direct_convolution(oracle):
     assert abs(acc - g64[Y, X, 1]) < 1e-12
 
 
+def test_maps_restatement_agrees_with_independent_torch_ops(oracle):
+    """TensorFlow is unavailable (parity of this half stays unpinned), but the op definitions the graph uses
+    (estimator.py:326-337, smoother.py:91) also exist as independent CPU code in PyTorch: adaptive average pooling
+    is the area resize for integer factors, conv2d(groups=C, padding=12) is the SAME-padded depthwise convolution,
+    max_pool2d(3, 1, 1) pads with -inf = the clipped 3x3 window.  The C restatement must agree with them."""
+    import torch
+    import torch.nn.functional as F
+    torch.set_num_threads(2)
+    k2d, _ = oracle.gauss_kernel()
+    x = synth.synth_frame(46, 54, synth.frame_seed(2, 3))
+    heat, paf = oracle.split(x)
+    assert np.array_equal(heat, x[:, :, :19]) and np.array_equal(paf, x[:, :, 19:])
+    for f in (1, 2, 4):
+        H, W = 46 * f, 54 * f
+        th = torch.from_numpy(heat).permute(2, 0, 1)[None]                         # NCHW
+        up_t = F.interpolate(th, size=(H, W), mode="area")
+        up_o = oracle.resize_area(heat, H, W)
+        assert np.array_equal(up_t[0].permute(1, 2, 0).numpy(), up_o), f          # replication: bit-exact
+        w = torch.from_numpy(k2d)[None, None].repeat(19, 1, 1, 1)
+        g_t = F.conv2d(up_t, w, padding=12, groups=19)
+        g64 = F.conv2d(up_t.double(), w.double(), padding=12, groups=19)[0].permute(1, 2, 0).numpy()
+        g_o = oracle.blur(up_o, k2d)
+        scale = np.abs(g64).max()
+        assert np.abs(g_o - g64).max() / scale < 5e-6, f                           # the oracle against float64 truth
+        assert np.abs(g_t[0].permute(1, 2, 0).numpy() - g64).max() / scale < 5e-6  # and so is torch's float32
+        # NMS on the SAME smoothed map: equality with the pooled maximum, bit for bit
+        g_in = torch.from_numpy(g_o).permute(2, 0, 1)[None]
+        m = F.max_pool2d(g_in, 3, 1, 1)
+        pk_t = torch.where(g_in == m, g_in, torch.zeros_like(g_in))[0].permute(1, 2, 0).numpy()
+        assert np.array_equal(pk_t, oracle.nms(g_o)), f
+    # integer down-scale: the area resize is the block mean
+    small = oracle.resize_area(heat[:44, :54], 22, 27)
+    ref = F.interpolate(torch.from_numpy(heat[:44, :54].copy()).permute(2, 0, 1)[None], size=(22, 27), mode="area")
+    assert np.abs(small - ref[0].permute(1, 2, 0).numpy()).max() < 1e-6
+
+
 @pytest.mark.skipif(not HAVE_REF, reason="oracle/_ref (reference pafprocess.cpp) not built")
 @pytest.mark.parametrize("mode", ["asbuilt", "upstream"])
 def test_paf_restatement_matches_reference_binary(oracle, mode):
