@@ -184,10 +184,12 @@ def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     import tfpose_b200 as tp
-    from tfpose_b200 import synth, _lib
+    from tfpose_b200 import synth, _lib, shard
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # before any host buffer exists: pinned inputs on the GPU's own NUMA node (matters with 8 ranks on two sockets)
+    numa = shard.bind_host_to_gpu_node(local_rank) if not args.no_numa else {"node": -1, "mempolicy": False, "cpus": 0}
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     h, w, f = H_LOW, W_LOW, FACTOR
@@ -392,6 +394,7 @@ def run_ours(args, rank, world, local_rank):
             humans_total = int(sum(int(g.item()) for g in gathered))
 
     cpu_base = None
+    shard.unbind_host(numa)          # the CPU leg below forks one worker per host core
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = host_cores()
         per = max(cores, 8)
@@ -421,6 +424,7 @@ def run_ours(args, rank, world, local_rank):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD % B,
                        "batch_per_gpu": B, "global_batch": B * world, "sharding": "by image, no collective",
+                       "host_numa": {k: numa[k] for k in ("node", "mempolicy", "cpus")},
                        "l2": "outputs 773 MB/step exceed the 126 MB L2; %d rotating input batches" % N_INPUT_SETS,
                        "mode": "asbuilt",
                        "pipeline": "%d contexts round-robin on %d stream(s): later steps are enqueued before step i's "
@@ -479,6 +483,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa", action="store_true", help="leave host memory policy and CPU affinity alone")
     ap.add_argument("--pipeline", type=int, default=3, help="contexts in flight in the device-resident timed region")
     ap.add_argument("--k1-ctas", type=int, default=128, help="CTAs of the fused map kernel (0 = one per SM)")
     ap.add_argument("--pipe-streams", type=int, default=2, help="1: all contexts on one stream, 2: one stream each")

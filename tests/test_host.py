@@ -385,3 +385,17 @@ def test_every_option_the_library_accepts_is_documented():
     assert accepted and accepted == documented, (sorted(accepted - documented), sorted(documented - accepted))
     integ = open(os.path.join(root, "INTEGRATION.md")).read()
     assert all(("`%s`" % n) in integ for n in accepted), [n for n in accepted if ("`%s`" % n) not in integ]
+
+
+def test_gpu_numa_node_lookup_and_unbind(tmp_path):
+    """shard.bind_host_to_gpu_node reads the GPU's NUMA node from sysfs; best effort, never raises."""
+    from tfpose_b200 import shard
+    dev = tmp_path / "bus" / "pci" / "devices" / "0000:1b:00.0"
+    dev.mkdir(parents=True)
+    (dev / "numa_node").write_text("1\n")
+    assert shard.gpu_numa_node(0, 0x1b, 0, sysfs=str(tmp_path)) == 1
+    assert shard.gpu_numa_node(0, 0x2c, 0, sysfs=str(tmp_path)) == -1
+    assert shard._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    done = shard.bind_host_to_gpu_node(0, sysfs=str(tmp_path))       # no CUDA device here: nothing done, no raise
+    assert done["node"] == -1 and not done["mempolicy"]
+    shard.unbind_host(done)

@@ -3,6 +3,10 @@ decodes the contiguous slice [g*N/G, (g+1)*N/G) on its own GPU with its own cont
 collective touches the data path; the only communication is the final gather of the per-frame
 human tables (a few hundred bytes per frame) to rank 0, done with ``torch.distributed``
 (NCCL on the GPU box, gloo in the CPU tests)."""
+import ctypes
+import os
+import platform
+
 import numpy as np
 
 from . import _lib
@@ -67,3 +71,74 @@ def split_records(counts, records):
         out.append(records[o:o + int(c)])
         o += int(c)
     return out
+
+
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def gpu_numa_node(pci_domain, pci_bus, pci_device, sysfs="/sys"):
+    """NUMA node the GPU's PCIe slot hangs off (``/sys/bus/pci/devices/<id>/numa_node``), or -1 if unknown."""
+    path = os.path.join(sysfs, "bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (pci_domain, pci_bus, pci_device))
+    try:
+        with open(path) as fh:
+            return int(fh.read().strip())
+    except (OSError, ValueError):
+        return -1
+
+
+def bind_host_to_gpu_node(device_index, sysfs="/sys"):
+    """One process per GPU on a multi-socket host: page-locked input buffers that live on the other socket reach
+    the GPU through the inter-socket link, and with eight ranks reading one socket's memory the host side, not
+    PCIe, bounds the host-to-device copies.  Call this first thing in a rank: it prefers the GPU's NUMA node for
+    every later host allocation of this process (``set_mempolicy(MPOL_PREFERRED)``, so the pinned buffers land
+    there) and moves the process onto that node's CPUs where the cpuset allows.  Best effort: returns a dict saying
+    what was done (``node``, ``mempolicy``, ``cpus``), never raises.  ``unbind_host`` undoes it."""
+    done = {"node": -1, "mempolicy": False, "cpus": 0, "prev_cpus": None}
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(device_index)
+        node = gpu_numa_node(p.pci_domain_id, p.pci_bus_id, p.pci_device_id, sysfs)
+    except Exception:
+        return done
+    done["node"] = node
+    if node < 0:
+        return done
+    try:
+        with open(os.path.join(sysfs, "devices/system/node/node%d/cpulist" % node)) as fh:
+            local = _parse_cpulist(fh.read()) & os.sched_getaffinity(0)
+        if local:
+            done["prev_cpus"] = sorted(os.sched_getaffinity(0))
+            os.sched_setaffinity(0, local)
+            done["cpus"] = len(local)
+    except (OSError, ValueError):
+        pass
+    nr = {"x86_64": 238, "aarch64": 237}.get(platform.machine())
+    if nr is not None and node < 1024:
+        try:
+            libc = ctypes.CDLL(None, use_errno=True)
+            mask = (ctypes.c_ulong * 16)()
+            mask[node // 64] = 1 << (node % 64)
+            MPOL_PREFERRED = 1
+            done["mempolicy"] = libc.syscall(nr, MPOL_PREFERRED, mask, 1025) == 0
+        except Exception:
+            pass
+    return done
+
+
+def unbind_host(done):
+    """Back to the default memory policy and the CPU set the process had before ``bind_host_to_gpu_node``."""
+    try:
+        if done.get("prev_cpus"):
+            os.sched_setaffinity(0, set(done["prev_cpus"]))
+        nr = {"x86_64": 238, "aarch64": 237}.get(platform.machine())
+        if done.get("mempolicy") and nr is not None:
+            ctypes.CDLL(None, use_errno=True).syscall(nr, 0, None, 0)      # MPOL_DEFAULT
+    except Exception:
+        pass
