@@ -108,6 +108,23 @@ def test_resize_cubic_batch_on_device(decoder):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("target", [(432, 368), (656, 368), (1312, 736)])      # network inputs of BASELINE.json's configs
+def test_resize_cubic_camera_frames_to_network_inputs(decoder, target):
+    import torch
+    rng = np.random.default_rng(target[0])
+    # smooth content + noise + saturated patches, 1920x1080 like a camera frame
+    yy, xx = np.mgrid[0:1080, 0:1920]
+    base = 127.5 + 100.0 * np.sin(xx / 37.0) * np.cos(yy / 23.0)
+    imgs = np.stack([np.clip(base[:, :, None] + rng.normal(0, 30, (1080, 1920, 3)), 0, 255).astype(np.uint8)
+                     for _ in range(2)])
+    imgs[0, 100:200, 300:500] = 255
+    imgs[1, 900:, :64] = 0
+    out = decoder.resize_cubic(torch.from_numpy(imgs).cuda(), target).cpu().numpy()
+    for i in range(2):
+        assert np.array_equal(out[i], PO.resize_cubic_u8(imgs[i], target[0], target[1])), (target, i)
+
+
+@pytest.mark.gpu
 def test_quantize_and_scaled_img_mirror(decoder, cuda):
     import torch
     rng = np.random.default_rng(6)
