@@ -161,3 +161,36 @@ def test_preproc_rejects_bad_arguments(decoder):
         decoder.resize_cubic(np.zeros((4, 4, 5), np.uint8), (8, 8))    # 5 channels: TFPD_ERR_INVALID
     with pytest.raises(ValueError):
         decoder.quantize_img(np.zeros((4, 4), np.float64))
+
+
+@pytest.mark.gpu
+def test_inference_shaped_chain_stays_on_the_device(cuda, oracle):
+    """The steps of ``TfPoseEstimator.inference`` + ``draw_humans`` around the (out-of-scope) network, all on the
+    device and chained on one stream: camera frame -> bicubic resize to the network input (estimator.py:534-535) ->
+    [network output: synthetic] -> decode (:536-551) -> skeletons drawn into the resized frame (:391-415).  Checked
+    against the CPU chain: resize oracle (= cv2's bytes), decode oracle, cv2 drawing."""
+    import torch
+    from helpers import humans_equal
+    from test_draw import reference_draw
+    from tfpose_b200 import synth
+    rng = np.random.default_rng(21)
+    n = 3
+    frames = rng.integers(0, 256, (n, 480, 640, 3), dtype=np.uint8)
+    x = synth.synth_batch(n, 46, 54, config_id=2, first_frame=700)
+    dec = tp.PoseDecoder(max_batch=n, max_upsample=(184, 216))
+    try:
+        d_net_in = dec.resize_cubic(torch.from_numpy(frames).cuda(), (432, 368))
+        res = dec.decode(torch.from_numpy(x).cuda(), (184, 216))
+        dec.draw_decoded(d_net_in)
+        torch.cuda.synchronize()
+        got = d_net_in.cpu().numpy()
+        assert sum(len(res.humans(i)) for i in range(n)) > 0
+        for i in range(n):
+            R, _ = oracle.decode_frame(x[i], 184, 216)
+            if int(res.info["near_ties"][i]) == 0:
+                ok, why = humans_equal(res.humans(i), R.humans_as_tuples(), 184, 216)
+                assert ok, (i, why)
+            want = reference_draw(PO.resize_cubic_u8(frames[i], 432, 368), res.humans(i))
+            assert np.array_equal(got[i], want), i
+    finally:
+        dec.close()
