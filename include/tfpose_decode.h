@@ -202,10 +202,15 @@ TFPD_API int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int im
  *   code produces (cv2 with IPP disabled; the closed-source IPP variant differs by 1 LSB on a few percent of the
  *   pixels).  HOST pointers when on_device == 0 (copied in and out, synchronous); DEVICE pointers otherwise,
  *   asynchronous on stream.
+ * tfpd_resize_cubic_u8_fxfy is the cv2.resize(npimg, dsize=None, fx=s, fy=s, interpolation=cv2.INTER_CUBIC) form of
+ *   _get_scaled_img's scaled variants (estimator.py:428,452,482): the sampling step is 1/fx, 1/fy (not src/dst) and
+ *   dst must have the size cv2 derives, dst_w = round_half_even(src_w*fx), dst_h likewise (else TFPD_ERR_INVALID).
  * tfpd_quantize_img replaces TfPoseEstimator._quantize_img (estimator.py:383-388) for float32 images:
  *   dst[i] = (uint8)((src[i] + 1.0f) / (2.0f / 256)), truncated; count elements. */
 TFPD_API int tfpd_resize_cubic_u8(tfpd_ctx *ctx, const uint8_t *src, int on_device, int N, int src_h, int src_w, int cn,
                          uint8_t *dst, int dst_h, int dst_w, void *stream);
+TFPD_API int tfpd_resize_cubic_u8_fxfy(tfpd_ctx *ctx, const uint8_t *src, int on_device, int N, int src_h, int src_w, int cn,
+                              double fx, double fy, uint8_t *dst, int dst_h, int dst_w, void *stream);
 TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, size_t count, uint8_t *dst, void *stream);
 
 /* Tuning options, by name (unknown name or out-of-range value -> TFPD_ERR_INVALID):

@@ -42,10 +42,11 @@ def _cubic_coeffs(x):
     return np.array([c0, c1, c2, c3], dtype=f32)
 
 
-def axis_table(ssize, dsize):
+def axis_table(ssize, dsize, f=None):
     """Per output index: first-tap source offset (tap k reads clamp(ofs-1+k)) and the four 11-bit coefficients.
-    ``scale = 1/(dsize/ssize)`` in double as cv::resize -> hal::resize computes it."""
-    scale = 1.0 / (float(dsize) / float(ssize))
+    ``scale = 1/(dsize/ssize)`` in double as cv::resize -> hal::resize computes it; ``1/f`` when the size came
+    from a scale factor (``dsize=None, fx=f``)."""
+    scale = 1.0 / (float(dsize) / float(ssize)) if f is None else 1.0 / float(f)
     ofs = np.zeros(dsize, np.int64)
     coef = np.zeros((dsize, 4), np.int64)
     for d in range(dsize):
@@ -58,14 +59,20 @@ def axis_table(ssize, dsize):
     return ofs, coef
 
 
-def resize_cubic_u8(img, dst_w, dst_h):
+def resize_cubic_u8_fxfy(img, fx, fy):
+    """``cv2.resize(img, dsize=None, fx=fx, fy=fy, interpolation=cv2.INTER_CUBIC)`` (estimator.py:428,452,482):
+    dsize = round-half-even(src * f), sampling step 1/f."""
+    return resize_cubic_u8(img, int(round(img.shape[1] * fx)), int(round(img.shape[0] * fy)), fx, fy)
+
+
+def resize_cubic_u8(img, dst_w, dst_h, fx=None, fy=None):
     """``cv2.resize(img, (dst_w, dst_h), interpolation=cv2.INTER_CUBIC)`` for uint8 [H,W] or [H,W,C] (IPP off)."""
     squeeze = img.ndim == 2
     if squeeze:
         img = img[:, :, None]
     sh, sw, cn = img.shape
-    xo, xa = axis_table(sw, dst_w)
-    yo, ya = axis_table(sh, dst_h)
+    xo, xa = axis_table(sw, dst_w, fx)
+    yo, ya = axis_table(sh, dst_h, fy)
     S = img.astype(np.int64)
     H = np.zeros((sh, dst_w, cn), np.int64)
     for k in range(4):
@@ -89,8 +96,68 @@ def resize_cubic_u8(img, dst_w, dst_h):
     return out[:, :, 0] if squeeze else out
 
 
-def get_scaled_img(npimg, target_size):
-    """``_get_scaled_img(npimg, None)`` (estimator.py:417-424): resize to ``target_size = (w, h)`` unless equal."""
-    if npimg.shape[:2] != (target_size[1], target_size[0]):
-        npimg = resize_cubic_u8(npimg, target_size[0], target_size[1])
-    return [npimg], [(0.0, 0.0, 1.0, 1.0)]
+def sliding_windows(width, height, win_w, win_h, overlap):
+    """Window enumeration of the third-party ``slidingwindow`` package (``setup.py:28`` asks for >= 0.0.13; the
+    5-argument ``sw.generate(data, dimOrder, maxW, maxH, overlap)`` call of estimator.py:437,461 needs the later
+    signature), restated from its published algorithm -- the package is not in this image: PARITY UNPINNED for
+    this function.  Returns [(x, y, w, h)] in the package's order (x outer, y inner)."""
+    ww, wh = min(win_w, width), min(win_h, height)
+    step_x, step_y = ww - int(np.floor(ww * overlap)), wh - int(np.floor(wh * overlap))
+    last_x, last_y = width - ww, height - wh
+    xs, ys = list(range(0, last_x + 1, step_x)), list(range(0, last_y + 1, step_y))
+    if not xs or xs[-1] != last_x:
+        xs.append(last_x)
+    if not ys or ys[-1] != last_y:
+        ys.append(last_y)
+    return [(x, y, ww, wh) for x in xs for y in ys]
+
+
+def crop_roi(npimg, target_size, ratio_x, ratio_y):
+    """estimator.py:502-516 as written: the padded branch builds ``npblank`` and falls off the end (returns None)."""
+    target_w, target_h = target_size
+    h, w = npimg.shape[:2]
+    x = max(int(w * ratio_x - .5), 0)
+    y = max(int(h * ratio_y - .5), 0)
+    cropped = npimg[y:y + target_h, x:x + target_w]
+    if cropped.shape[1] < target_w or cropped.shape[0] < target_h:
+        return None
+    return cropped
+
+
+def get_scaled_img(npimg, target_size, scale=None):
+    """``_get_scaled_img(npimg, scale)`` (estimator.py:417-500), every form of ``scale``."""
+    tw, th = target_size
+    img_h, img_w = npimg.shape[:2]
+    if scale is None:
+        if npimg.shape[:2] != (th, tw):
+            npimg = resize_cubic_u8(npimg, tw, th)
+        return [npimg], [(0.0, 0.0, 1.0, 1.0)]
+
+    def base_scale(s):
+        return max(tw / float(img_h), th / float(img_w)) * s          # :418 as written (w over h, h over w)
+
+    if isinstance(scale, float) or (isinstance(scale, tuple) and len(scale) == 2):
+        s, step = (scale, 0.2) if isinstance(scale, float) else scale
+        f = base_scale(s)
+        npimg = resize_cubic_u8_fxfy(npimg, f, f)
+        o_h, o_w = npimg.shape[:2]
+        if o_h < th or o_w < tw:
+            big = np.zeros((max(th, o_h), max(tw, o_w), 3), np.uint8)
+            big[:o_h, :o_w, :] = npimg
+            npimg = big
+        rois, ratios = [], []
+        for (x, y, w, h) in sliding_windows(npimg.shape[1], npimg.shape[0], tw, th, step):
+            rois.append(npimg[y:y + h, x:x + w])
+            ratios.append((float(x) / o_w, float(y) / o_h, float(w) / o_w, float(h) / o_h))
+        return rois, ratios
+    if isinstance(scale, tuple) and len(scale) == 3:
+        f = base_scale(scale[2])
+        npimg = resize_cubic_u8_fxfy(npimg, f, f)
+        ratio_w, ratio_h = tw / float(npimg.shape[1]), th / float(npimg.shape[0])
+        ratio_x, ratio_y = max(scale[0] - ratio_w / 2., 0.0), max(scale[1] - ratio_h / 2., 0.0)
+        if ratio_x + ratio_w > 1.0:
+            ratio_x = 1. - ratio_w
+        if ratio_y + ratio_h > 1.0:
+            ratio_y = 1. - ratio_h
+        return [crop_roi(npimg, target_size, ratio_x, ratio_y)], [(ratio_x, ratio_y, ratio_w, ratio_h)]
+    return None

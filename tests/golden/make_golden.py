@@ -277,7 +277,54 @@ def preproc_golden():
     print("preproc cubic", len(shas), "cases, cv2", cv2.__version__)
 
 
+SCALED_CASES = [  # (seed, img_h, img_w, target (w, h), scale)
+    (20, 300, 400, (216, 184), None), (21, 184, 216, (216, 184), None), (22, 300, 400, (216, 184), 1.0),
+    (23, 300, 400, (216, 184), 1.5), (24, 200, 150, (216, 184), 0.7), (25, 300, 400, (216, 184), (1.2, 0.3)),
+    (26, 300, 400, (216, 184), (0.5, 0.5, 1.5)), (27, 300, 400, (216, 184), (0.05, 0.95, 2.0)),
+    (28, 300, 400, (216, 184), (0.5, 0.5, 0.8))]
+
+
+def scaled_img_golden():
+    """The reference's OWN ``TfPoseEstimator._get_scaled_img`` / ``_crop_roi`` (estimator.py:417-516) run on real
+    cv2 (IPP off).  Its ``slidingwindow`` dependency is not in the image: a stand-in module with the restated window
+    enumeration (oracle/preproc_oracle.sliding_windows) is injected, so everything but that enumeration is pinned."""
+    import cv2
+    from oracle import preproc_oracle as PO
+    cv2.ipp.setUseIPP(False)
+    est = reference_estimator("asbuilt")
+    est.cv2 = cv2
+
+    class _Win(object):
+        def __init__(self, x, y, w, h):
+            self.x, self.y, self.w, self.h = x, y, w, h
+
+        def indices(self):
+            return (slice(self.y, self.y + self.h), slice(self.x, self.x + self.w))
+
+    fake_sw = types.SimpleNamespace(
+        DimOrder=types.SimpleNamespace(HeightWidthChannel=0),
+        generate=lambda data, order, mw, mh, ov: [_Win(*t) for t in
+                                                  PO.sliding_windows(data.shape[1], data.shape[0], mw, mh, ov)])
+    est.sw = fake_sw
+    out = []
+    for (seed, ih, iw, target, scale) in SCALED_CASES:
+        me = types.SimpleNamespace(target_size=target)
+        me._crop_roi = lambda img, rx, ry, me=me: est.TfPoseEstimator._crop_roi(me, img, rx, ry)
+        rois, ratios = est.TfPoseEstimator._get_scaled_img(me, preproc_image(seed, ih, iw, 3), scale)
+        out.append({"seed": seed, "h": ih, "w": iw, "target": list(target),
+                    "scale": list(scale) if isinstance(scale, tuple) else scale,
+                    "rois": [None if r is None else [list(r.shape), hashlib.sha256(np.ascontiguousarray(r).tobytes()).hexdigest()]
+                             for r in rois],
+                    "ratios": [list(map(float, r)) for r in ratios]})
+        print("scaled", scale, len(rois), [None if r is None else r.shape for r in rois][:3])
+    with open(os.path.join(HERE, "scaled_img.json"), "w") as fh:
+        json.dump(out, fh)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "scaled":
+        scaled_img_golden()
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "preproc":
         preproc_golden()
         return

@@ -59,6 +59,52 @@ def test_oracle_identity_and_quantize():
     assert PO.quantize_img(x).tolist() == [0, 64, 128, 191, 254]
 
 
+def test_oracle_fxfy_matches_cv2_live():
+    cv2 = pytest.importorskip("cv2")
+    had = cv2.ipp.useIPP()
+    cv2.ipp.setUseIPP(False)
+    try:
+        rng = np.random.default_rng(78)
+        for i in range(16):
+            sh, sw = (int(v) for v in rng.integers(5, 200, 2))
+            fx = float(rng.uniform(0.3, 2.5))
+            fy = fx if i % 2 == 0 else float(rng.uniform(0.3, 2.5))
+            img = rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8)
+            ref = cv2.resize(img, dsize=None, fx=fx, fy=fy, interpolation=cv2.INTER_CUBIC)
+            out = PO.resize_cubic_u8_fxfy(img, fx, fy)
+            assert out.shape == ref.shape and np.array_equal(out, ref), (sh, sw, fx, fy)
+    finally:
+        cv2.ipp.setUseIPP(had)
+
+
+def scaled_cases():
+    import json
+    with open(os.path.join(HERE, "golden", "scaled_img.json")) as fh:
+        return json.load(fh)
+
+
+def check_scaled(case, rois, ratios):
+    assert len(rois) == len(case["rois"]) and len(ratios) == len(case["ratios"]), case["scale"]
+    for r, want in zip(rois, case["rois"]):
+        if want is None:
+            assert r is None
+        else:
+            assert list(r.shape) == want[0] and sha(r) == want[1], case["scale"]
+    for got, want in zip(ratios, case["ratios"]):
+        assert [float(v) for v in got] == want, case["scale"]
+
+
+def test_oracle_get_scaled_img_matches_the_reference_method():
+    """tests/golden/scaled_img.json holds what the reference's own _get_scaled_img / _crop_roi returned (real cv2,
+    IPP off; stand-in slidingwindow module)."""
+    for case in scaled_cases():
+        scale = tuple(case["scale"]) if isinstance(case["scale"], list) else case["scale"]
+        img = golden_image(case["seed"], case["h"], case["w"], 3)
+        check_scaled(case, *PO.get_scaled_img(img, tuple(case["target"]), scale))
+    assert PO.sliding_windows(500, 184, 216, 184, 0.2) == [(0, 0, 216, 184), (173, 0, 216, 184), (284, 0, 216, 184)]
+    assert PO.sliding_windows(100, 100, 216, 184, 0.2) == [(0, 0, 100, 100)]
+
+
 @pytest.fixture(scope="module")
 def decoder(cuda):
     d = tp.PoseDecoder(max_batch=1, max_upsample=(184, 216))
@@ -147,8 +193,6 @@ def test_quantize_and_scaled_img_mirror(decoder, cuda):
         same = golden_image(1, 368, 432, 3)
         assert post._get_scaled_img(same, None)[0][0] is same
         assert np.array_equal(post._quantize_img(x), want)
-        with pytest.raises(NotImplementedError):
-            post._get_scaled_img(img, 1.0)
     finally:
         post.close()
 
@@ -194,3 +238,27 @@ def test_inference_shaped_chain_stays_on_the_device(cuda, oracle):
             assert np.array_equal(got[i], want), i
     finally:
         dec.close()
+
+
+@pytest.mark.gpu
+def test_get_scaled_img_every_form_matches_the_reference_method(cuda):
+    for case in scaled_cases():
+        scale = tuple(case["scale"]) if isinstance(case["scale"], list) else case["scale"]
+        post = tp.TfPosePostProcessor(target_size=tuple(case["target"]))
+        try:
+            check_scaled(case, *post._get_scaled_img(golden_image(case["seed"], case["h"], case["w"], 3), scale))
+            assert post._get_scaled_img(golden_image(1, 8, 8, 3), "bad") is None
+        finally:
+            post.close()
+
+
+@pytest.mark.gpu
+def test_resize_fxfy_rejects_a_size_cv2_would_not_make(decoder):
+    import ctypes as C
+    img = golden_image(2, 40, 50, 3)
+    out = decoder.resize_cubic(img, None, fx=1.3, fy=0.7)
+    assert np.array_equal(out, PO.resize_cubic_u8_fxfy(img, 1.3, 0.7))
+    dst = np.empty((1, 29, 65, 3), np.uint8)                # cv2 makes 28 x 65 from 40 x 50 at fy = 0.7
+    rc = decoder._L.tfpd_resize_cubic_u8_fxfy(decoder._ctx, img.ctypes.data, 0, 1, 40, 50, 3, C.c_double(1.3),
+                                              C.c_double(0.7), dst.ctypes.data, 29, 65, None)
+    assert rc == 1                                           # TFPD_ERR_INVALID

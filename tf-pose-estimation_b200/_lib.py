@@ -88,6 +88,7 @@ SIGNATURES = {
     "tfpd_draw_humans": (_I, [_P, _P, _I, _I, _I, _I, _P, _P, _I, _P]),
     "tfpd_draw_decoded": (_I, [_P, _P, _I, _I, _P]),
     "tfpd_resize_cubic_u8": (_I, [_P, _P, _I, _I, _I, _I, _I, _P, _I, _I, _P]),
+    "tfpd_resize_cubic_u8_fxfy": (_I, [_P, _P, _I, _I, _I, _I, _I, C.c_double, C.c_double, _P, _I, _I, _P]),
     "tfpd_quantize_img": (_I, [_P, _P, _I, C.c_size_t, _P, _P]),
 }
 

@@ -515,8 +515,27 @@ int tfpd_draw_decoded(tfpd_ctx *ctx, uint8_t *images, int img_h, int img_w, void
     return TFPD_OK;
 }
 
+static int resize_cubic_impl(tfpd_ctx *ctx, const uint8_t *src, int on_device, int N, int src_h, int src_w, int cn,
+                             uint8_t *dst, int dst_h, int dst_w, double fx, double fy, void *stream);
+
 int tfpd_resize_cubic_u8(tfpd_ctx *ctx, const uint8_t *src, int on_device, int N, int src_h, int src_w, int cn,
                          uint8_t *dst, int dst_h, int dst_w, void *stream) {
+    return resize_cubic_impl(ctx, src, on_device, N, src_h, src_w, cn, dst, dst_h, dst_w, 0.0, 0.0, stream);
+}
+
+int tfpd_resize_cubic_u8_fxfy(tfpd_ctx *ctx, const uint8_t *src, int on_device, int N, int src_h, int src_w, int cn,
+                              double fx, double fy, uint8_t *dst, int dst_h, int dst_w, void *stream) {
+    if (!ctx) return TFPD_ERR_INVALID;
+    if (!(fx > 0) || !(fy > 0)) return fail(ctx, TFPD_ERR_INVALID, "resize_cubic_u8_fxfy: fx, fy must be positive");
+    // cv::resize with an empty dsize: dsize = saturate_cast<int>(src * f) = round half to even
+    const double ew = nearbyint(src_w * fx), eh = nearbyint(src_h * fy);
+    if ((double)dst_w != ew || (double)dst_h != eh)
+        return fail(ctx, TFPD_ERR_INVALID, "resize_cubic_u8_fxfy: dst is %dx%d, cv2 makes %.0fx%.0f from fx=%g fy=%g", dst_h, dst_w, eh, ew, fx, fy);
+    return resize_cubic_impl(ctx, src, on_device, N, src_h, src_w, cn, dst, dst_h, dst_w, fx, fy, stream);
+}
+
+static int resize_cubic_impl(tfpd_ctx *ctx, const uint8_t *src, int on_device, int N, int src_h, int src_w, int cn,
+                             uint8_t *dst, int dst_h, int dst_w, double fx, double fy, void *stream) {
     if (!ctx) return TFPD_ERR_INVALID;
     if (!src || !dst) return fail(ctx, TFPD_ERR_INVALID, "resize_cubic_u8: null argument");
     if (N < 1 || N > 65535 || src_h < 1 || src_w < 1 || dst_h < 1 || dst_w < 1 || dst_h > 65535 || src_h > 32767 ||
@@ -535,7 +554,7 @@ int tfpd_resize_cubic_u8(tfpd_ctx *ctx, const uint8_t *src, int on_device, int N
         d_dst = (unsigned char *)ctx->pre_dst.p;
         CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pre_src.p, src, in_bytes, cudaMemcpyHostToDevice, s));
     }
-    if (launch_resize_cubic_u8(d_src, d_dst, N, src_h, src_w, cn, dst_h, dst_w, ctx->resize_path, s) < 0)
+    if (launch_resize_cubic_u8(d_src, d_dst, N, src_h, src_w, cn, dst_h, dst_w, fx, fy, ctx->resize_path, s) < 0)
         return fail(ctx, TFPD_ERR_CUDA, "resize kernel failed: %s", cudaGetErrorString(cudaGetLastError()));
     if (!on_device) {
         CUDA_TRY(ctx, cudaMemcpyAsync(dst, d_dst, out_bytes, cudaMemcpyDeviceToHost, s));

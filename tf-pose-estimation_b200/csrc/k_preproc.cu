@@ -298,9 +298,10 @@ __global__ void k_quantize_img(const float *__restrict__ src, unsigned char *__r
 }  // namespace
 
 int launch_resize_cubic_u8(const unsigned char *src, unsigned char *dst, int N, int sh, int sw, int cn, int dh, int dw,
-                           int path, cudaStream_t s) {
-    // cv::resize: inv_scale = (double)dsize/ssize; hal::resize: scale = 1./inv_scale
-    const double scale_x = 1.0 / ((double)dw / (double)sw), scale_y = 1.0 / ((double)dh / (double)sh);
+                           double fx, double fy, int path, cudaStream_t s) {
+    // cv::resize: inv_scale = (double)dsize/ssize when dsize is given, fx / fy themselves when it is derived from them;
+    // hal::resize: scale = 1./inv_scale
+    const double scale_x = 1.0 / (fx > 0 ? fx : (double)dw / (double)sw), scale_y = 1.0 / (fy > 0 ? fy : (double)dh / (double)sh);
     // tiled form: tile width = dw cut into equal parts of <= 128 columns; source rows of a tile bounded from scale_y
     const int parts = (dw + 127) / 128, tile_w = (dw + parts - 1) / parts;
     const int max_rows = (int)ceil((kTY - 1) * scale_y) + 5;

@@ -126,7 +126,7 @@ int launch_draw(const int *d_centers, const int *d_counts, int max_h, unsigned c
 int launch_centers_from_tables(const Workspace &ws, int N, int map_h, int map_w, int img_h, int img_w, int *d_centers,
                                int *d_counts, cudaStream_t s);
 int launch_resize_cubic_u8(const unsigned char *src, unsigned char *dst, int N, int sh, int sw, int cn, int dh, int dw,
-                           int path, cudaStream_t s);
+                           double fx, double fy, int path, cudaStream_t s);
 int launch_quantize_img(const float *src, unsigned char *dst, size_t n, int sm_count, cudaStream_t s);
 
 }  // namespace tfpd

@@ -265,12 +265,29 @@ class PoseDecoder(object):
         return buf[0] if single else buf
 
     # -- image pre-processing in front of the network (estimator.py:383-388, :417-424) ---------
-    def resize_cubic(self, images, target_size):
-        """``cv2.resize(img, target_size, interpolation=cv2.INTER_CUBIC)`` for uint8 images: NumPy [H,W], [H,W,C] or
+    def resize_cubic(self, images, target_size=None, fx=None, fy=None):
+        """``cv2.resize(img, target_size, interpolation=cv2.INTER_CUBIC)`` -- or, with ``target_size=None``,
+        ``cv2.resize(img, dsize=None, fx=fx, fy=fy, ...)`` -- for uint8 images: NumPy [H,W], [H,W,C] or
         [N,H,W,C] (host in, host out) or a contiguous CUDA uint8 tensor [N,H,W,C] (device in, device out,
         asynchronous on the current stream).  ``target_size = (w, h)`` as cv2 and the reference ctor take it.
         The bytes are those of OpenCV's own bicubic code (cv2 with IPP off)."""
-        dw, dh = int(target_size[0]), int(target_size[1])
+        if target_size is None:
+            if fx is None or fy is None:
+                raise ValueError("give target_size or fx and fy")
+            shp = images.shape
+            sh_, sw_ = (shp[0], shp[1]) if len(shp) < 4 else (shp[1], shp[2])
+            dw, dh = int(round(sw_ * float(fx))), int(round(sh_ * float(fy)))     # cv2: round half to even
+            scaled = True
+        else:
+            dw, dh = int(target_size[0]), int(target_size[1])
+            scaled = False
+
+        def call(src_ptr, on_device, n, sh, sw, cn, dst_ptr, stream):
+            if scaled:
+                return self._L.tfpd_resize_cubic_u8_fxfy(self._ctx, src_ptr, on_device, n, sh, sw, cn, float(fx), float(fy),
+                                                         dst_ptr, dh, dw, stream)
+            return self._L.tfpd_resize_cubic_u8(self._ctx, src_ptr, on_device, n, sh, sw, cn, dst_ptr, dh, dw, stream)
+
         if isinstance(images, np.ndarray):
             if images.dtype != np.uint8 or images.ndim not in (2, 3, 4):
                 raise ValueError("images must be uint8 [H,W], [H,W,C] or [N,H,W,C]")
@@ -282,8 +299,7 @@ class PoseDecoder(object):
                 src = src[None]
             n, sh, sw, cn = src.shape
             dst = np.empty((n, dh, dw, cn), np.uint8)
-            self._check(self._L.tfpd_resize_cubic_u8(self._ctx, src.ctypes.data, 0, n, sh, sw, cn, dst.ctypes.data,
-                                                     dh, dw, None))
+            self._check(call(src.ctypes.data, 0, n, sh, sw, cn, dst.ctypes.data, None))
             return dst[0, :, :, 0] if len(shp) == 2 else (dst[0] if len(shp) == 3 else dst)
         import torch
         if images.dtype != torch.uint8 or images.dim() != 4 or not images.is_cuda or not images.is_contiguous():
@@ -291,8 +307,7 @@ class PoseDecoder(object):
         n, sh, sw, cn = (int(v) for v in images.shape)
         dst = torch.empty((n, dh, dw, cn), dtype=torch.uint8, device=images.device)
         stream = C.c_void_p(torch.cuda.current_stream(images.device).cuda_stream)
-        self._check(self._L.tfpd_resize_cubic_u8(self._ctx, images.data_ptr(), 1, n, sh, sw, cn, dst.data_ptr(),
-                                                 dh, dw, stream))
+        self._check(call(images.data_ptr(), 1, n, sh, sw, cn, dst.data_ptr(), stream))
         return dst
 
     def quantize_img(self, npimg):

@@ -16,6 +16,20 @@ from .decoder import PoseDecoder, upsample_size_for
 from .humans import BodyPart, Human
 
 
+def _sliding_windows(width, height, win_w, win_h, overlap):
+    """``slidingwindow.generate(data, DimOrder.HeightWidthChannel, win_w, win_h, overlap)`` (estimator.py:437,461) as
+    [(x, y, w, h)]: windows clipped to the data, step = size - floor(size*overlap), a last window flush with the far
+    edge, x outer / y inner."""
+    ww, wh = min(win_w, width), min(win_h, height)
+    step_x, step_y = ww - int(ww * overlap), wh - int(wh * overlap)
+    xs, ys = list(range(0, width - ww + 1, step_x)), list(range(0, height - wh + 1, step_y))
+    if not xs or xs[-1] != width - ww:
+        xs.append(width - ww)
+    if not ys or ys[-1] != height - wh:
+        ys.append(height - wh)
+    return [(x, y, ww, wh) for x in xs for y in ys]
+
+
 class PoseEstimator(object):
     def __init__(self):
         pass
@@ -121,15 +135,54 @@ class TfPosePostProcessor(object):
         return self._decoder.quantize_img(npimg)
 
     def _get_scaled_img(self, npimg, scale=None):
-        """``TfPoseEstimator._get_scaled_img(npimg, None)`` (estimator.py:417-424), the only form ``inference``
-        uses (:534-535): bicubic resize to ``target_size`` unless the image already has it.  The sliding-window
-        forms (float / tuple ``scale``, :425-500) feed a multi-scale merge the reference never implemented and
-        need the absent ``slidingwindow`` package: not provided."""
-        if scale is not None:
-            raise NotImplementedError("only scale=None (the form inference() uses) is provided")
-        if npimg.shape[:2] != (self.target_size[1], self.target_size[0]):
-            npimg = self._decoder.resize_cubic(npimg, self.target_size)
-        return [npimg], [(0.0, 0.0, 1.0, 1.0)]
+        """``TfPoseEstimator._get_scaled_img(npimg, scale)`` (estimator.py:417-500) with the bicubic resizes on the
+        GPU: ``None`` (the form ``inference`` uses, :534-535) resizes to ``target_size`` unless the image already has
+        it; a float or ``(scale, step)`` resizes by ``base_scale`` and cuts overlapping ``target_size`` windows
+        (overlap 0.2 / ``step``); ``(want_x, want_y, scale_ratio)`` resizes and crops one window around a point.
+        Returns ``(rois, ratios)`` like the reference.  The window enumeration restates the third-party
+        ``slidingwindow`` package's ``generate`` (not in this image; parity unpinned for that part alone)."""
+        tw, th = self.target_size
+        img_h, img_w = npimg.shape[:2]
+        if scale is None:
+            if npimg.shape[:2] != (th, tw):
+                npimg = self._decoder.resize_cubic(npimg, self.target_size)
+            return [npimg], [(0.0, 0.0, 1.0, 1.0)]
+        base = max(tw / float(img_h), th / float(img_w))          # get_base_scale as written (:418)
+        if isinstance(scale, float) or (isinstance(scale, tuple) and len(scale) == 2):
+            factor, overlap = (scale, 0.2) if isinstance(scale, float) else scale
+            npimg = self._decoder.resize_cubic(npimg, None, fx=base * factor, fy=base * factor)
+            o_h, o_w = npimg.shape[:2]
+            if o_h < th or o_w < tw:                              # pad bottom/right with zeros up to a full window
+                padded = np.zeros((max(th, o_h), max(tw, o_w), 3), dtype=np.uint8)
+                padded[:o_h, :o_w, :] = npimg
+                npimg = padded
+            rois, ratios = [], []
+            for (x, y, w, h) in _sliding_windows(npimg.shape[1], npimg.shape[0], tw, th, overlap):
+                rois.append(npimg[y:y + h, x:x + w])
+                ratios.append((float(x) / o_w, float(y) / o_h, float(w) / o_w, float(h) / o_h))
+            return rois, ratios
+        if isinstance(scale, tuple) and len(scale) == 3:
+            factor = base * scale[2]
+            npimg = self._decoder.resize_cubic(npimg, None, fx=factor, fy=factor)
+            ratio_w, ratio_h = tw / float(npimg.shape[1]), th / float(npimg.shape[0])
+            ratio_x, ratio_y = max(scale[0] - ratio_w / 2., 0.0), max(scale[1] - ratio_h / 2., 0.0)
+            if ratio_x + ratio_w > 1.0:
+                ratio_x = 1. - ratio_w
+            if ratio_y + ratio_h > 1.0:
+                ratio_y = 1. - ratio_h
+            return [self._crop_roi(npimg, ratio_x, ratio_y)], [(ratio_x, ratio_y, ratio_w, ratio_h)]
+        return None                                               # any other ``scale``: the reference falls through
+
+    def _crop_roi(self, npimg, ratio_x, ratio_y):
+        """``TfPoseEstimator._crop_roi`` (estimator.py:502-516) as written: a crop that comes out smaller than
+        ``target_size`` is centred in a blank image which is then dropped -- the method returns None for it."""
+        tw, th = self.target_size
+        h, w = npimg.shape[:2]
+        x, y = max(int(w * ratio_x - .5), 0), max(int(h * ratio_y - .5), 0)
+        cropped = npimg[y:y + th, x:x + tw]
+        if cropped.shape[1] < tw or cropped.shape[0] < th:
+            return None
+        return cropped
 
     def close(self):
         self._decoder.close()
