@@ -20,9 +20,12 @@
  *
  * Every function that can fail returns an int status (TFPD_OK == 0); tfpd_last_error()
  * gives the message.  A context (ctx) owns its device workspace and its results; results
- * stay valid until the next decode/process call on that ctx.  Calls on different contexts
- * are independent (the reference keeps its results in module globals,
- * pafprocess.cpp:12-13, and is not re-entrant).  There is no CPU fallback anywhere: without
+ * stay valid until the next decode/process call on that ctx.  ONE call is in flight per ctx:
+ * a decode/process call issued before the previous one was fetched is stream-ordered behind
+ * it (whatever streams the two use) and replaces its results, as the next process_paf
+ * replaces the reference's module globals (pafprocess.cpp:12-13,39,128); to overlap batches
+ * use one ctx per batch in flight.  Calls on different contexts are independent (the
+ * reference is not re-entrant).  There is no CPU fallback anywhere: without
  * a CUDA device tfpd_create fails with TFPD_ERR_CUDA.
  */
 #ifndef TFPOSE_DECODE_H_

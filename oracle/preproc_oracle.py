@@ -97,10 +97,10 @@ def resize_cubic_u8(img, dst_w, dst_h, fx=None, fy=None):
 
 
 def sliding_windows(width, height, win_w, win_h, overlap):
-    """Window enumeration of the third-party ``slidingwindow`` package (``setup.py:28`` asks for >= 0.0.13; the
-    5-argument ``sw.generate(data, dimOrder, maxW, maxH, overlap)`` call of estimator.py:437,461 needs the later
-    signature), restated from its published algorithm -- the package is not in this image: PARITY UNPINNED for
-    this function.  Returns [(x, y, w, h)] in the package's order (x outer, y inner)."""
+    """Window enumeration of the ``slidingwindow`` package as the reference vendors it
+    (tf_pose/slidingwindow/SlidingWindow.py:100-146 ``generateForSize``, called through ``sw.generate`` at
+    estimator.py:439,467).  PINNED: tests/golden/scaled_img.json holds window lists produced by that vendored code
+    (make_golden.py scaled).  Returns [(x, y, w, h)] in the package's order (x outer, y inner)."""
     ww, wh = min(win_w, width), min(win_h, height)
     step_x, step_y = ww - int(np.floor(ww * overlap)), wh - int(np.floor(wh * overlap))
     last_x, last_y = width - ww, height - wh

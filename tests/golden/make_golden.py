@@ -284,28 +284,43 @@ SCALED_CASES = [  # (seed, img_h, img_w, target (w, h), scale)
     (28, 300, 400, (216, 184), (0.5, 0.5, 0.8))]
 
 
+def reference_slidingwindow():
+    """The reference's VENDORED copy of the third-party ``slidingwindow`` package
+    (tf_pose/slidingwindow/SlidingWindow.py:87-110 ``generate`` / ``generateForSize``), imported from where it lies
+    under the name estimator.py:4 imports it by."""
+    pkg_dir = os.path.join(REF, "tf_pose", "slidingwindow")
+    spec = importlib.util.spec_from_file_location("slidingwindow", os.path.join(pkg_dir, "__init__.py"),
+                                                  submodule_search_locations=[pkg_dir])
+    mod = importlib.util.module_from_spec(spec)
+    saved = sys.modules.get("slidingwindow")
+    sys.modules["slidingwindow"] = mod
+    try:
+        spec.loader.exec_module(mod)
+    finally:
+        if saved is None:
+            sys.modules.pop("slidingwindow", None)
+        else:
+            sys.modules["slidingwindow"] = saved
+    return mod
+
+
+SLIDING_CASES = [  # (width, height, win_w, win_h, overlap): data smaller / equal / larger than the window, exact and
+    (216, 184, 216, 184, 0.2), (400, 300, 216, 184, 0.2), (600, 450, 216, 184, 0.2), (600, 450, 216, 184, 0.3),   # ragged steps
+    (150, 100, 216, 184, 0.2), (432, 368, 216, 184, 0.5), (433, 369, 216, 184, 0.5), (1000, 184, 216, 184, 0.0),
+    (217, 185, 216, 184, 0.9), (656, 368, 432, 368, 0.2), (1312, 736, 432, 368, 0.25), (5, 5, 3, 2, 0.34)]
+
+
 def scaled_img_golden():
     """The reference's OWN ``TfPoseEstimator._get_scaled_img`` / ``_crop_roi`` (estimator.py:417-516) run on real
-    cv2 (IPP off).  Its ``slidingwindow`` dependency is not in the image: a stand-in module with the restated window
-    enumeration (oracle/preproc_oracle.sliding_windows) is injected, so everything but that enumeration is pinned."""
+    cv2 (IPP off) over the reference's own vendored ``slidingwindow`` package: every piece of the scaled forms,
+    window enumeration included, is what the reference computes.  Also stores the bare window lists of
+    ``slidingwindow.generateForSize`` for a set of sizes (``sliding_windows``)."""
     import cv2
-    from oracle import preproc_oracle as PO
     cv2.ipp.setUseIPP(False)
     est = reference_estimator("asbuilt")
     est.cv2 = cv2
-
-    class _Win(object):
-        def __init__(self, x, y, w, h):
-            self.x, self.y, self.w, self.h = x, y, w, h
-
-        def indices(self):
-            return (slice(self.y, self.y + self.h), slice(self.x, self.x + self.w))
-
-    fake_sw = types.SimpleNamespace(
-        DimOrder=types.SimpleNamespace(HeightWidthChannel=0),
-        generate=lambda data, order, mw, mh, ov: [_Win(*t) for t in
-                                                  PO.sliding_windows(data.shape[1], data.shape[0], mw, mh, ov)])
-    est.sw = fake_sw
+    sw = reference_slidingwindow()
+    est.sw = sw
     out = []
     for (seed, ih, iw, target, scale) in SCALED_CASES:
         me = types.SimpleNamespace(target_size=target)
@@ -317,8 +332,15 @@ def scaled_img_golden():
                              for r in rois],
                     "ratios": [list(map(float, r)) for r in ratios]})
         print("scaled", scale, len(rois), [None if r is None else r.shape for r in rois][:3])
+    wins = []
+    for (width, height, ww, wh, ov) in SLIDING_CASES:
+        got = sw.generateForSize(width, height, sw.DimOrder.HeightWidthChannel, ww, wh, ov)
+        wins.append({"width": width, "height": height, "win_w": ww, "win_h": wh, "overlap": ov,
+                     "windows": [list(map(int, w_.getRect())) for w_ in got]})
+        print("windows", (width, height, ww, wh, ov), len(got))
     with open(os.path.join(HERE, "scaled_img.json"), "w") as fh:
-        json.dump(out, fh)
+        json.dump({"cases": out, "sliding_windows": wins,
+                   "source": "reference estimator.py:417-516 over the vendored tf_pose/slidingwindow package, cv2 %s IPP off" % cv2.__version__}, fh)
 
 
 def main():

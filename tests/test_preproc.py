@@ -77,10 +77,14 @@ def test_oracle_fxfy_matches_cv2_live():
         cv2.ipp.setUseIPP(had)
 
 
-def scaled_cases():
+def scaled_golden():
     import json
     with open(os.path.join(HERE, "golden", "scaled_img.json")) as fh:
         return json.load(fh)
+
+
+def scaled_cases():
+    return scaled_golden()["cases"]
 
 
 def check_scaled(case, rois, ratios):
@@ -96,13 +100,27 @@ def check_scaled(case, rois, ratios):
 
 def test_oracle_get_scaled_img_matches_the_reference_method():
     """tests/golden/scaled_img.json holds what the reference's own _get_scaled_img / _crop_roi returned (real cv2,
-    IPP off; stand-in slidingwindow module)."""
+    IPP off) on top of the reference's own vendored slidingwindow package (tf_pose/slidingwindow)."""
     for case in scaled_cases():
         scale = tuple(case["scale"]) if isinstance(case["scale"], list) else case["scale"]
         img = golden_image(case["seed"], case["h"], case["w"], 3)
         check_scaled(case, *PO.get_scaled_img(img, tuple(case["target"]), scale))
     assert PO.sliding_windows(500, 184, 216, 184, 0.2) == [(0, 0, 216, 184), (173, 0, 216, 184), (284, 0, 216, 184)]
     assert PO.sliding_windows(100, 100, 216, 184, 0.2) == [(0, 0, 100, 100)]
+
+
+def test_window_enumeration_matches_the_vendored_slidingwindow_package():
+    """Window lists of the reference's vendored ``slidingwindow.generateForSize``
+    (tf_pose/slidingwindow/SlidingWindow.py:100-146; golden made by make_golden.py scaled): the oracle's restatement
+    and the product's ``_sliding_windows`` must enumerate the same (x, y, w, h) in the same order."""
+    from tfpose_b200.estimator import _sliding_windows
+    wins = scaled_golden()["sliding_windows"]
+    assert len(wins) >= 12
+    for c in wins:
+        args = (c["width"], c["height"], c["win_w"], c["win_h"], c["overlap"])
+        want = [tuple(w) for w in c["windows"]]
+        assert PO.sliding_windows(*args) == want, args
+        assert _sliding_windows(*args) == want, args
 
 
 @pytest.fixture(scope="module")

@@ -123,7 +123,10 @@ class DecodeError(RuntimeError):
 
 
 class CapacityError(DecodeError):
-    """A per-frame table overflowed; raise the matching ``max_*`` in the config."""
+    """A per-frame table overflowed; raise the matching ``max_*`` in the config.  ``result`` (when the
+    error comes from ``PoseDecoder.fetch``) is the ``DecodeResult`` of the whole batch: frames whose
+    ``info['flags']`` carry no overflow bit are complete."""
+    result = None
 
 
 def default_config(**overrides):

@@ -14,6 +14,9 @@
 
 using namespace tfpd;
 
+static_assert(sizeof(tfpd_human) == 184, "tfpd_human layout is part of the C-ABI (ctypes HumanRec, numpy HUMAN_DTYPE)");
+static_assert(sizeof(tfpd_frame_info) == 24, "tfpd_frame_info layout is part of the C-ABI");
+
 namespace {
 
 thread_local std::string g_create_error;
@@ -83,6 +86,7 @@ struct tfpd_ctx {
     int early_fetch = 0;                // 0 copy the tables at fetch time, 1 right behind the last kernel, 2 on st_res
     cudaStream_t st_res = nullptr;
     cudaEvent_t ev_res = nullptr;
+    cudaEvent_t ev_done = nullptr;      // behind the last operation of the latest decode/process call on last_stream
     int last_N = 0, last_H = 0, last_W = 0;
     int launches = 0;
     bool decoded = false, fetched = false, d2h_pending = false;
@@ -237,6 +241,19 @@ Workspace ws_view(const Workspace &w, int f0) {
     return v;
 }
 
+// One call in flight per ctx.  A decode/process call that arrives before the previous one was fetched drops that
+// call's results -- the reference overwrites its module globals the same way (pafprocess.cpp:39,128) -- but the
+// previous call's kernels and copies still own the workspace until they finish: the new call's work on every stream
+// it uses (`s`, and `s2` when non-null) is ordered behind them.
+int order_after_previous(tfpd_ctx *ctx, cudaStream_t s, cudaStream_t s2 = nullptr) {
+    if (!ctx->decoded || ctx->fetched) return TFPD_OK;
+    CUDA_TRY(ctx, cudaStreamWaitEvent(s, ctx->ev_done, 0));
+    if (s2) CUDA_TRY(ctx, cudaStreamWaitEvent(s2, ctx->ev_done, 0));
+    if (ctx->result_on_side) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->st_res));     // table copy into h_result
+    if (ctx->d2h_pending) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->st_d2h));        // dense maps leaving dense_buf
+    return TFPD_OK;
+}
+
 void begin_call(tfpd_ctx *ctx, int N, int H, int W, cudaStream_t s) {
     ctx->launches = 0;
     ctx->last_stream = s;
@@ -292,8 +309,10 @@ int tfpd_gauss_kernel(int ksize, float sigma, float *k2d) {
 int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     if (!cfg || !out) return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: null argument");
     *out = nullptr;
-    if (cfg->max_batch < 1 || cfg->max_h < 1 || cfg->max_w < 1 || cfg->max_h > 8191 || cfg->max_w > 16383)
-        return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: bad max_batch/max_h/max_w");
+    // max_batch: frames index gridDim.y / gridDim.x of the per-frame kernels (<= 65535)
+    if (cfg->max_batch < 1 || cfg->max_batch > 65535 || cfg->max_h < 1 || cfg->max_w < 1 || cfg->max_h > 8191 ||
+        cfg->max_w > 16383)
+        return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: bad max_batch (1..65535) / max_h (<=8191) / max_w (<=16383)");
     if (cfg->blur_ksize < 1 || (cfg->blur_ksize & 1) == 0 || cfg->blur_ksize > 127)
         return fail(nullptr, TFPD_ERR_INVALID, "tfpd_create: blur_ksize must be odd and <= 127");
     if (cfg->max_peaks < 1 || cfg->max_peaks > kMaxPeaksHard || cfg->max_cands < 1 || cfg->max_cands > 16384 ||
@@ -407,6 +426,7 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     cudaStreamCreateWithFlags(&ctx->st_d2h, cudaStreamNonBlocking);
     cudaStreamCreateWithFlags(&ctx->st_res, cudaStreamNonBlocking);
     cudaEventCreateWithFlags(&ctx->ev_res, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ctx->ev_done, cudaEventDisableTiming);
     if (const char *e = getenv("TFPD_HOST_CHUNKS")) ctx->host_chunks = atoi(e);
     if (const char *e = getenv("TFPD_K1_L2")) ctx->k1_l2_knobs = atoi(e);
     if (const char *e = getenv("TFPD_K1_ROLES")) ctx->k1_roles = atoi(e);
@@ -417,6 +437,13 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
             cudaMemset(ctx->d_k1_times, 0, 1024 * 4 * 8);
             ctx->ws.dbg_times = ctx->d_k1_times;
         }
+    // the memsets / uploads above ran on the legacy default stream, which the non-blocking streams of this ctx and
+    // of the callers do not wait for: finish them before the first decode can be enqueued
+    e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        tfpd_destroy(ctx);
+        return fail(nullptr, TFPD_ERR_CUDA, "tfpd_create: %s", cudaGetErrorString(e));
+    }
     *out = ctx;
     return TFPD_OK;
 }
@@ -430,6 +457,7 @@ void tfpd_destroy(tfpd_ctx *ctx) {
     for (auto &ev : ctx->ev_chunk) cudaEventDestroy(ev);
     for (auto &g : ctx->graphs) cudaGraphExecDestroy(g.exec);
     if (ctx->ev_res) cudaEventDestroy(ctx->ev_res);
+    if (ctx->ev_done) cudaEventDestroy(ctx->ev_done);
     for (cudaStream_t st : {ctx->st_h2d, ctx->st_work, ctx->st_d2h, ctx->st_res})
         if (st) cudaStreamDestroy(st);
     if (ctx->ws_block) cudaFree(ctx->ws_block);
@@ -619,6 +647,13 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
     } else {
         return fail(ctx, TFPD_ERR_INVALID, "unknown option '%s'", name);
     }
+    // captured graphs bake in grid sizes, kernel choices and the copy placement: any option change drops them
+    if (!ctx->graphs.empty()) {
+        DeviceGuard device_guard__(ctx->cfg.device);
+        if (ctx->decoded) cudaStreamSynchronize(ctx->last_stream);
+        for (auto &g : ctx->graphs) cudaGraphExecDestroy(g.exec);
+        ctx->graphs.clear();
+    }
     return TFPD_OK;
 }
 
@@ -805,8 +840,9 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
         return fail(ctx, TFPD_ERR_INVALID, "decode: dense output pointers must be 16-byte aligned");
     ON_CTX_DEVICE(ctx);
     cudaStream_t s = (cudaStream_t)stream;
-    begin_call(ctx, N, H, W, s);
     int rc;
+    if ((rc = order_after_previous(ctx, s)) != TFPD_OK) return rc;
+    begin_call(ctx, N, H, W, s);
     const bool fast = (H == 4 * h && W == 4 * w && ctx->cfg.blur_ksize == 25);
     if (ctx->use_graph && fast && !ctx->profiling && !ctx->k1_turnstile && !ctx->d_k1_times) {
         // the launch-bound part of a decode (seven stream operations) as one graph launch; captured once per
@@ -844,6 +880,7 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
         }
         ctx->launches = hit->launches;
         CUDA_TRY(ctx, cudaGraphLaunch(hit->exec, s));
+        CUDA_TRY(ctx, cudaEventRecord(ctx->ev_done, s));
         ctx->result_enqueued = true;
         ctx->decoded = true;
         return TFPD_OK;
@@ -851,6 +888,7 @@ int tfpd_decode_device(tfpd_ctx *ctx, const float *net_out, int N, int h, int w,
     rc = enqueue_decode(ctx, ctx->ws, net_out, N, h, w, H, W, s, want_dense ? dense : nullptr, ctx->profiling);
     if (rc != TFPD_OK) return rc;
     if ((rc = enqueue_result_copy(ctx, N, s)) != TFPD_OK) return rc;
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_done, s));
     ctx->decoded = true;
     return TFPD_OK;
 }
@@ -964,6 +1002,7 @@ int tfpd_decode_host_async(tfpd_ctx *ctx, const float *net_out, int N, int h, in
     if (want_dense && !(heat_up && paf_up && peaks))
         return fail(ctx, TFPD_ERR_INVALID, "decode_host: dense outputs must be all set or all null");
     ON_CTX_DEVICE(ctx);
+    if (int rc = order_after_previous(ctx, ctx->st_work, ctx->st_h2d)) return rc;
     const size_t frame_in = (size_t)h * w * kNetC * 4;      // multiple of 4; chunk offsets are kept 16-byte aligned below
     const size_t fpx = (size_t)H * W;
     CUDA_TRY(ctx, ctx->in_buf.reserve((size_t)N * frame_in));
@@ -1024,6 +1063,7 @@ int tfpd_decode_host_async(tfpd_ctx *ctx, const float *net_out, int N, int h, in
         }
     }
     if (int rc = enqueue_result_copy(ctx, N, ctx->st_work)) return rc;
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_done, ctx->st_work));
     ctx->decoded = true;
     ctx->d2h_pending = want_dense;
     return TFPD_OK;
@@ -1047,6 +1087,7 @@ int tfpd_process_paf_device(tfpd_ctx *ctx, int p1, int p2, int p3, const float *
     if (p1 > 8191 || p2 > 16383) return fail(ctx, TFPD_ERR_INVALID, "process_paf: map larger than 8191x16383");
     ON_CTX_DEVICE(ctx);
     cudaStream_t s = (cudaStream_t)stream;
+    if (int rc = order_after_previous(ctx, s)) return rc;
     begin_call(ctx, 1, p1, p2, s);
     CUDA_TRY(ctx, cudaMemsetAsync(ctx->ws.counters, 0, sizeof(FrameCounters), s));
     if (ctx->profiling) cudaEventRecord(ctx->ev[0], s);
@@ -1064,6 +1105,7 @@ int tfpd_process_paf_device(tfpd_ctx *ctx, int p1, int p2, int p3, const float *
     int rc = run_tail(ctx, ctx->ws, 1, src, (size_t)p1 * p2 * kPafC, s, ctx->profiling);
     if (rc != TFPD_OK) return rc;
     if ((rc = enqueue_result_copy(ctx, 1, s)) != TFPD_OK) return rc;
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_done, s));
     ctx->decoded = true;
     return 0;
 }

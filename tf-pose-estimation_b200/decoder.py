@@ -155,8 +155,15 @@ class PoseDecoder(object):
         N, H, W = self._shape
         info = np.empty(N, _lib.INFO_DTYPE)
         table = np.empty((N, self.max_humans), _lib.HUMAN_DTYPE)
-        self._check(self._L.tfpd_fetch_humans(self._ctx, table.ctypes.data, info.ctypes.data))
+        rc = self._L.tfpd_fetch_humans(self._ctx, table.ctypes.data, info.ctypes.data)
         self._keep = None
+        if rc == _lib.ERR_CAPACITY:
+            # one frame overflowing a table must not cost the caller the other frames: the tables are filled,
+            # the exception carries them and ``info['flags']`` names the frames and tables that overflowed
+            err = _lib.CapacityError(rc, self._L.tfpd_last_error(self._ctx).decode())
+            err.result = DecodeResult(info, table, H, W)
+            raise err
+        self._check(rc)
         return DecodeResult(info, table, H, W)
 
     def decode(self, net_out, upsample_size, dense=None, stream=None):

@@ -17,9 +17,9 @@ from .humans import BodyPart, Human
 
 
 def _sliding_windows(width, height, win_w, win_h, overlap):
-    """``slidingwindow.generate(data, DimOrder.HeightWidthChannel, win_w, win_h, overlap)`` (estimator.py:437,461) as
-    [(x, y, w, h)]: windows clipped to the data, step = size - floor(size*overlap), a last window flush with the far
-    edge, x outer / y inner."""
+    """``slidingwindow.generate(data, DimOrder.HeightWidthChannel, win_w, win_h, overlap)`` (estimator.py:439,467;
+    the reference vendors the package: tf_pose/slidingwindow/SlidingWindow.py:87-146) as [(x, y, w, h)]: windows
+    clipped to the data, step = size - floor(size*overlap), a last window flush with the far edge, x outer / y inner."""
     ww, wh = min(win_w, width), min(win_h, height)
     step_x, step_y = ww - int(ww * overlap), wh - int(wh * overlap)
     xs, ys = list(range(0, width - ww + 1, step_x)), list(range(0, height - wh + 1, step_y))
@@ -78,6 +78,10 @@ class TfPosePostProcessor(object):
         self.reuse_map_buffers = reuse_map_buffers
         self._pinned = {}
         H, W = upsample_size_for(target_size[0], target_size[1], max_ratio)
+        # the reference's process_paf has no table limits (std::vector everywhere): same generous capacities as the
+        # pafprocess drop-in so that a crowded frame decodes instead of raising CapacityError
+        for k, v in (("max_peaks", 4096), ("max_cands", 8192), ("max_rows", 1024), ("max_humans", 256)):
+            overrides.setdefault(k, v)
         self._decoder = PoseDecoder(max_batch=1, max_upsample=(H, W), device=device, mode=mode, **overrides)
         self.heatMat = self.pafMat = None
         self.peaks = None
@@ -139,8 +143,8 @@ class TfPosePostProcessor(object):
         GPU: ``None`` (the form ``inference`` uses, :534-535) resizes to ``target_size`` unless the image already has
         it; a float or ``(scale, step)`` resizes by ``base_scale`` and cuts overlapping ``target_size`` windows
         (overlap 0.2 / ``step``); ``(want_x, want_y, scale_ratio)`` resizes and crops one window around a point.
-        Returns ``(rois, ratios)`` like the reference.  The window enumeration restates the third-party
-        ``slidingwindow`` package's ``generate`` (not in this image; parity unpinned for that part alone)."""
+        Returns ``(rois, ratios)`` like the reference.  The window enumeration follows the reference's vendored
+        ``slidingwindow.generate`` (pinned by tests/golden/scaled_img.json)."""
         tw, th = self.target_size
         img_h, img_w = npimg.shape[:2]
         if scale is None:
