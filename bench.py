@@ -1,33 +1,37 @@
 #!/usr/bin/env python
 """bench.py -- decoded frames/s of the heatmap/PAF decode path (BASELINE.json metric).
 
-Workload (BASELINE.json configs[1]): mobilenet_thin 432x368 network outputs, i.e. X[64,46,54,57]
-float32 per GPU, upsample x4 -> 184x216, synthetic skeleton maps (tf-pose-estimation_b200/synth.py),
-full decode to humans.  One "step" = one batch of 64 frames through the hot path:
+One "step" = one batch of frames through the hot path:
   K1 fused upsample+smoother+NMS (dense outputs written: heat_up, paf_up, peaks -- the three
-  tensors the reference's sess.run returns) -> peak sort -> K2 limb scoring -> K3 assembly ->
-  human tables copied to the host.
+  tensors the reference's sess.run returns) -> K2 limb scoring (ranks the peaks itself) ->
+  K3 assembly -> human tables copied to the host.
 
-  value      frames/s with the inputs resident in HBM (dense mode), CUDA-event timed.
-  e2e        frames/s through the host-buffer C-ABI call (tfpd_decode_host): pinned host input,
-             H2D inside the timed region, human tables D2H.  Dense maps stay on the device
-             (inference() returns humans; e2e_dense_maps also ships the three maps back).
+Workloads (BASELINE.json configs; --config picks the one the line's `value` is quoted on):
+  c2  mobilenet_thin 432x368: X[64,46,54,57] per GPU, upsample x4 (default; weak scaling)
+  c3  CMU 656x368: X[128,46,82,57] in total, sharded by image over the GPUs (STRONG scaling:
+      128 / 64 / 32 / 16 frames per GPU at 1 / 2 / 4 / 8 GPUs)
+  c4  crowded scene: ~30 people per frame on the c2 shape, 64 frames per GPU
+  c5  1312x736: X[64,92,164,57] per GPU = 512 frames over 8 GPUs
+The default line is c2 and carries the other three under `per_config`.
+
+  value      frames/s with the inputs resident in HBM (dense mode), CUDA-event timed, max over ranks.
+  e2e        frames/s through the host-buffer C-ABI call (tfpd_decode_host_async + tfpd_fetch_humans):
+             pinned host input, H2D inside the timed region, human tables D2H.  Dense maps stay on
+             the device (inference() returns humans); e2e_dense_maps also ships the three maps back,
+             e2e_objects also builds the list[list[Human]] the reference returns.
   roofline   fused K1 kernel: algorithmic bytes 4*(57hw + 76HW) per frame / its CUDA-event time,
              against MEASURED_PEAKS.json hbm_gbs.
-  cpu_baseline / --impl reference: the same decode on the host cores: the C restatement of the
-             TF ops (TensorFlow itself is not available) + the reference's own pafprocess.cpp
-             (oracle/_ref), one process per core.
+  cpu_baseline / --impl reference: the same decode on the host cores (see cpu_arm below).
 
-Multi-GPU: frames are independent, the batch is sharded by image (each rank decodes its own 64
-frames: weak scaling); no collective on the data path, only the timing reduction and a final
-gather of the human counts.
+Multi-GPU: frames are independent, the batch is sharded by image; no collective on the data path,
+only the timing reduction and a final gather of per-rank figures.
 """
 import argparse
 import gc
 import json
 import os
+import subprocess
 import sys
-import threading
 import time
 
 import numpy as np
@@ -35,111 +39,66 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-H_LOW, W_LOW, FACTOR = 46, 54, 4          # mobilenet_thin @432x368: 368/8 x 432/8
-BATCH = 64
-CONFIG_ID = 2
-N_INPUT_SETS = 4                          # rotate inputs: 4 x 36 MB > L2 together with 773 MB of outputs/step
-WORKLOAD = ("mobilenet_thin 432x368 decode, batch %d per GPU, 46x54x57 -> 184x216 (upsample x4), "
-            "dense maps (heat_up+paf_up+peaks) produced, humans to host")
+FACTOR = 4
+N_INPUT_SETS = 4          # rotating input batches: together with the outputs of a step they exceed the 126 MB L2
+
+# BASELINE.json configs (C2..C5).  `total` = frames of the whole job (strong scaling: split over the
+# ranks), `batch` = frames per GPU (weak scaling).  Capacities only where the defaults would overflow.
+CONFIGS = {
+    "c2": {"id": 2, "h": 46, "w": 54, "people": None, "batch": 64, "caps": {},
+           "name": "mobilenet_thin 432x368 decode, batch %d per GPU, 46x54x57 -> 184x216 (upsample x4), dense maps "
+                   "(heat_up+paf_up+peaks) produced, humans to host"},
+    "c3": {"id": 3, "h": 46, "w": 82, "people": None, "total": 128, "caps": {},
+           "name": "CMU 656x368 decode, 128 frames sharded by image (%d per GPU), 46x82x57 -> 184x328 (upsample x4), "
+                   "dense maps produced, humans to host"},
+    "c4": {"id": 4, "h": 46, "w": 54, "people": 30, "batch": 64,
+           "caps": {"max_peaks": 4096, "max_cands": 8192, "max_humans": 128},
+           "name": "crowded scene (~30 people per frame) on the mobilenet_thin shape, batch %d per GPU, 46x54x57 -> "
+                   "184x216, dense maps produced, humans to host"},
+    "c5": {"id": 5, "h": 92, "w": 164, "people": None, "batch": 64, "caps": {},
+           "name": "high-res 1312x736 decode, batch %d per GPU (512 over 8 GPUs), 92x164x57 -> 368x656 (upsample "
+                   "x4), dense maps produced, humans to host"},
+}
 
 
-def dense_bytes_per_frame(h, w, f):
+def frames_per_rank(cfg, world, override=None):
+    if override:
+        return int(override)
+    if "total" in cfg:
+        return max(1, cfg["total"] // world)
+    return cfg["batch"]
+
+
+def scaling_of(cfg):
+    return "strong" if "total" in cfg else "weak"
+
+
+def dense_bytes_per_frame(h, w, f=FACTOR):
     return 4 * (57 * h * w + 76 * (f * h) * (f * w))
+
+
+# polyphase form of the smoother (what K1 executes): 7-tap vertical pass per output pixel + 7-tap
+# horizontal pass once per four output rows... counted per output pixel of the 19 heat channels as 2*(7 + 7/4) flop
+def polyphase_flops_per_frame(h, w, f=FACTOR):
+    return 2.0 * (7.0 + 7.0 / 4.0) * 19 * (f * h) * (f * w)
 
 
 def measured_peak_gbs():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
-            return float(json.load(fh)["hbm_gbs"]), "measured"
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json, burst copy figure: K1 is timed alone)"
     except Exception:
-        return 6650.0, "fallback"
+        return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-class ClockSampler(threading.Thread):
-    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
-
-    def __init__(self, index):
-        threading.Thread.__init__(self, daemon=True)
-        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
-        try:
-            import pynvml
-            pynvml.nvmlInit()
-            self.nv = pynvml
-            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
-            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
-        except Exception:
-            self.nv = None
-
-    def run(self):
-        if self.nv is None:
-            return
-        nv = self.nv
-        names = {
-            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
-            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
-            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
-            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
-        }
-        while not self.stop_flag:
-            try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
-                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                for bit, name in names.items():
-                    if r & bit:
-                        self.reasons.add(name)
-            except Exception:
-                pass
-            time.sleep(float(os.environ.get("BENCH_SAMPLE_PERIOD", "0.002")))
-
-    def result(self):
-        if not self.samples:
-            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
-        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(self.samples)}
-
-
-# ------------------------------------------------------------------------------------------ CPU arm
-_CPU_X = None
-
-
-def _cpu_decode_one(i):
-    """One frame on one core: restated TF ops (C oracle) + the reference's pafprocess.cpp."""
-    from oracle import oracle as O
-    global _CPU_REF
-    x = _CPU_X[i % len(_CPU_X)]
-    H, W = FACTOR * x.shape[0], FACTOR * x.shape[1]
-    peaks, heat_up, paf_up, _ = O.dense_maps(x, H, W)
-    ref = globals().get("_CPU_REF")
-    if ref is None:
-        try:
-            ref = O.ReferencePafprocess("asbuilt")
-        except Exception:
-            ref = False
-        globals()["_CPU_REF"] = ref
-    if ref:
-        ref.process_paf(peaks, heat_up, paf_up)
-        return len(ref.humans_as_tuples())
-    return len(O.process_paf(peaks, heat_up, paf_up).humans_as_tuples())
-
-
-def cpu_decode_rate(x, frames_per_step, steps, warmup, cores):
-    """frames/s of the CPU decode with `cores` worker processes."""
-    import multiprocessing as mp
-    from oracle import oracle as O
-    O.build()
-    global _CPU_X
-    _CPU_X = x
-    kind = "reference+port" if os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libpafprocess_asbuilt.so")) else "port"
-    ctx = mp.get_context("fork")
-    with ctx.Pool(cores) as pool:
-        for _ in range(warmup):
-            pool.map(_cpu_decode_one, range(frames_per_step), chunksize=1)
-        t0 = time.perf_counter()
-        humans = 0
-        for s in range(steps):
-            humans += sum(pool.map(_cpu_decode_one, range(s * frames_per_step, (s + 1) * frames_per_step), chunksize=1))
-        dt = time.perf_counter() - t0
-    return frames_per_step * steps / dt, dt, humans, kind
+def profile_constant(name, key):
+    """A per-launch figure that only a profiler can give (ncu `--set full`), kept under profiles/ with the
+    capture it came from; None when absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", name)) as fh:
+            return json.load(fh).get(key)
+    except Exception:
+        return None
 
 
 def host_cores():
@@ -149,356 +108,244 @@ def host_cores():
         return max(1, os.cpu_count() or 1)
 
 
-def run_reference(args, rank, world):
-    if rank != 0:
-        return
-    from tfpose_b200 import synth
-    cores = host_cores()
-    x = synth.synth_batch(min(BATCH, 32), H_LOW, W_LOW, config_id=CONFIG_ID)
-    # bounded sample per step: ~0.45 s per frame per core -> keep the whole run within minutes
-    per_step = max(cores, 8)
-    budget_s = 150.0
-    est = 0.5 * per_step * (args.steps + args.warmup) / cores
-    if est > budget_s:
-        per_step = max(1, int(per_step * budget_s / est))
-    rate, dt, humans, kind = cpu_decode_rate(x, per_step, args.steps, args.warmup, cores)
-    sample = "%d synthetic 46x54x57 frames per step (of the 64-frame batch), %d worker processes" % (per_step, cores)
-    line = {
-        "impl": "reference", "metric": "decoded_frames_per_s", "value": rate, "unit": "frames/s", "n_gpus": world,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD % BATCH, "batch_per_gpu": BATCH, "global_batch": BATCH * world,
-                   "sharding": "by image, no collective", "mode": "asbuilt",
-                   "reference_sample_frames_per_step": per_step},
-        "cpu_baseline": {"value": rate, "unit": "frames/s", "cores": cores, "kind": "reference" if kind != "port" else "port",
-                         "sample": sample + "; maps = C restatement of the TF ops (TensorFlow unavailable on this box), "
-                                            "pafprocess = reference's own pafprocess.cpp (oracle/_ref)"},
-        "e2e": {"value": rate, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0, "humans_decoded": humans,
-    }
-    emit(line)
+# ------------------------------------------------------------------------------------------ clocks
+# NVML is polled from a separate PROCESS: a sampler thread inside the timed process has to take the GIL every
+# period, and with eight ranks on one host those wake-ups landed inside the few-millisecond timed regions
+# (driver-run N=8 efficiency 0.845 against 0.98 with identical kernels).
+_SAMPLER_SRC = r'''
+import json, select, sys, time
+idx = [int(a) for a in sys.argv[2:]]
+period = float(sys.argv[1])
+out = {"t": [], "mhz": [], "bits": [], "max_mhz": None, "error": None}
+try:
+    import pynvml as nv
+    nv.nvmlInit()
+    hs = [nv.nvmlDeviceGetHandleByIndex(i) for i in idx]
+    out["max_mhz"] = max(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM) for h in hs)
+    while True:
+        r, _, _ = select.select([sys.stdin], [], [], period)
+        if r:
+            break
+        t = time.time()
+        for h in hs:
+            out["t"].append(t)
+            out["mhz"].append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+            out["bits"].append(int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)))
+except Exception as e:
+    out["error"] = repr(e)
+sys.stdout.write(json.dumps(out))
+'''
+_REASON_BITS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
 
-# ------------------------------------------------------------------------------------------ GPU arm
-def run_ours(args, rank, world, local_rank):
+class ClockSampler(object):
+    """SM clock and throttle reasons of the job's GPUs while the timed regions run (rank 0 starts it)."""
+
+    def __init__(self, indices, period=0.002):
+        self.windows = []
+        try:
+            self.proc = subprocess.Popen([sys.executable, "-c", _SAMPLER_SRC, str(period)] + [str(i) for i in indices],
+                                         stdin=subprocess.PIPE, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def window(self, t0, t1):
+        self.windows.append((t0, t1))
+
+    def result(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        try:
+            raw, _ = self.proc.communicate(b"x", timeout=10)
+            out = json.loads(raw.decode())
+        except Exception:
+            self.proc.kill()
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        if not out["mhz"]:
+            return {"sm_mhz": None, "sm_max_mhz": out["max_mhz"], "reasons": ["unavailable"], "error": out["error"]}
+        t, mhz, bits = np.array(out["t"]), np.array(out["mhz"]), np.array(out["bits"], dtype=np.int64)
+        inside = np.zeros(len(t), bool)
+        for (a, b) in self.windows:
+            inside |= (t >= a) & (t <= b)
+        sel = inside if inside.any() else np.ones(len(t), bool)
+        seen = 0
+        for b_ in bits[sel]:
+            seen |= int(b_)
+        return {"sm_mhz": float(np.median(mhz[sel])), "sm_max_mhz": out["max_mhz"],
+                "reasons": sorted(n for b_, n in _REASON_BITS.items() if seen & b_),
+                "samples": int(sel.sum()), "samples_in_timed_regions": int(inside.sum()), "samples_total": len(t)}
+
+
+# ------------------------------------------------------------------------------------------ CPU arm
+# The reference's CPU decode, stage by stage (SURVEY.md 8d):
+#   A  the TF graph ops of estimator.py:321-337 + smoother.py:62-95.  TensorFlow is unavailable on this box, so the
+#      closest analogue of its CPU kernels stands in: PyTorch's CPU ops on the same op definitions --
+#      interpolate(mode="area") for tf.image.resize_area, conv2d(groups=19, padding=12) (oneDNN) for
+#      DepthwiseConv2dNative, max_pool2d(3,1,1) + where for tf.nn.pool / tf.equal / tf.where.  tests/test_oracle.py
+#      checks these ops against the C restatement (upsample and NMS bit for bit, smoothed map to ~5e-6).
+#      The plain-C restatement (oracle/maps_oracle.c, direct 625-tap loop) is timed beside it; it is several times
+#      slower and is NOT the headline.
+#   B  the reference's OWN pafprocess.cpp, compiled by oracle/Makefile into oracle/_ref (loaded in the parent, so
+#      the driver's library hook sees it; no fallback: a missing library raises).
+#   C  PoseEstimator.estimate_paf's object loop over the getters (estimator.py:276-299).
+# Throughput forms: (i) one worker process per host core, one torch thread each (frames are independent);
+# (ii) one process, torch's intra-op threads over all cores (what a single sess.run does).  The headline CPU figure
+# is the FASTER of the two.
+_W = {}
+
+
+def _cpu_worker_init(x, threads, stage_a):
     import torch
-    import torch.distributed as dist
-    import tfpose_b200 as tp
-    from tfpose_b200 import synth, _lib, shard
+    torch.set_num_threads(int(threads))
+    from oracle import oracle as O
+    k2d = O.gauss_kernel()[0]
+    _W["x"], _W["torch"], _W["O"], _W["stage_a"] = x, torch, O, stage_a
+    _W["ref"] = O.ReferencePafprocess("asbuilt")            # raises when oracle/_ref is absent: no silent port
+    _W["K"] = torch.from_numpy(np.ascontiguousarray(k2d))[None, None].repeat(19, 1, 1, 1)
 
-    torch.cuda.set_device(local_rank)
-    dev = torch.device("cuda", local_rank)
-    # before any host buffer exists: pinned inputs on the GPU's own NUMA node (matters with 8 ranks on two sockets)
-    numa = shard.bind_host_to_gpu_node(local_rank) if not args.no_numa else {"node": -1, "mempolicy": False, "cpus": 0}
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    h, w, f = H_LOW, W_LOW, FACTOR
-    H, W = f * h, f * w
-    B = args.batch
 
-    # synthetic inputs: N_INPUT_SETS different batches per rank (frame seeds never repeat across ranks)
-    sets_host = []
-    for sidx in range(N_INPUT_SETS):
-        base = synth.synth_batch(min(B, 16), h, w, config_id=CONFIG_ID, first_frame=(rank * N_INPUT_SETS + sidx) * 16)
-        reps = (B + len(base) - 1) // len(base)
-        sets_host.append(np.concatenate([base] * reps)[:B].copy())
-    x_dev = [torch.from_numpy(s).to(dev) for s in sets_host]
-    x_pin = [torch.from_numpy(s).pin_memory() for s in sets_host]
-    dense = (torch.empty((B, H, W, 19), device=dev), torch.empty((B, H, W, 38), device=dev),
-             torch.empty((B, H, W, 19), device=dev))
+def _cpu_pool_init(x, threads, stage_a):
+    """Pool initializer: a worker whose set-up raises is respawned by multiprocessing for ever (the bench would hang
+    instead of failing), so the error is kept and re-raised by the first task, which reaches the parent."""
+    try:
+        _cpu_worker_init(x, threads, stage_a)
+    except BaseException as e:      # noqa: B902
+        _W["init_error"] = "%s: %s" % (type(e).__name__, e)
 
-    dec = tp.PoseDecoder(max_batch=B, max_upsample=(H, W), device=local_rank)
-    dec.set_profiling(True)
-    dec.set_option("k1_ctas", args.k1_ctas)
-    stream = torch.cuda.current_stream(dev)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
+def _stage_a_torch(x):
+    """x[h,w,57] -> (peaks, heat_up, paf_up) float32 NHWC arrays, the three tensors of estimator.py:536-539."""
+    torch = _W["torch"]
+    F = torch.nn.functional
+    h, w, _ = x.shape
+    H, W = FACTOR * h, FACTOR * w
+    with torch.no_grad():
+        t = torch.from_numpy(x)[None].permute(0, 3, 1, 2)               # NHWC memory seen as NCHW (channels_last)
+        up = F.interpolate(t, size=(H, W), mode="area")
+        heat_up, paf_up = up[:, :19], up[:, 19:]
+        g = F.conv2d(heat_up, _W["K"], padding=12, groups=19)
+        mx = F.max_pool2d(g, 3, 1, 1)                                   # pads with -inf == clipped border windows
+        peaks = torch.where(g == mx, g, torch.zeros_like(g))
+        to_nhwc = lambda a: np.ascontiguousarray(a[0].permute(1, 2, 0).numpy())
+        return to_nhwc(peaks), to_nhwc(heat_up), to_nhwc(paf_up)
 
-    def max_over_ranks(ms):
-        if world > 1:
-            t = torch.tensor([ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            return float(t.item())
-        return ms
 
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler = ClockSampler(local_rank)      # samples clocks / throttle reasons through every timed region below
-    sampler.start()
-    # the timed regions are a few milliseconds long: keep the collector's pauses out of them
-    gc.collect()
-    gc.disable()
+def _stage_a_c(x):
+    h, w, _ = x.shape
+    peaks, heat_up, paf_up, _g = _W["O"].dense_maps(x, FACTOR * h, FACTOR * w)
+    return peaks, heat_up, paf_up
 
-    # ---- device-resident, one call at a time (decode -> fetch): every kernel runs alone, so this region
-    #      gives the per-kernel times (roofline of K1) and the unpipelined step time ----
-    for i in range(args.warmup):
-        dec.decode(x_dev[i % N_INPUT_SETS], (H, W), dense=dense)
-    k1_ms, stage_acc = [], np.zeros(4)
-    barrier()
-    ev0.record(stream)
-    for i in range(args.steps):
-        dec.decode(x_dev[i % N_INPUT_SETS], (H, W), dense=dense)
-        st = dec.stage_ms()
-        k1_ms.append(st[0])
-        stage_acc += np.array(st)
-    ev1.record(stream)
-    barrier()
-    ms_serial = max_over_ranks(ev0.elapsed_time(ev1))
-    value_serial = world * B * args.steps / (ms_serial * 1e-3)
 
-    # ---- device-resident, pipelined: two contexts ping-pong (decode_async of step i+1 is enqueued before the
-    #      tables of step i are fetched), so host work, launch gaps and the latency-bound assembly of one batch hide
-    #      behind the next batch's K1.  Every step still ends with its human tables on the host.  = value ----
-    n_pipe = max(1, args.pipeline)
-    decs = [dec] + [tp.PoseDecoder(max_batch=B, max_upsample=(H, W), device=local_rank) for _ in range(n_pipe - 1)]
-    denses = [dense] + [tuple(torch.empty_like(t) for t in dense) for _ in range(n_pipe - 1)]
-    for d in decs[1:]:
-        d.set_profiling(True)
-        d.set_option("k1_ctas", args.k1_ctas)
-    if int(os.environ.get("K1_TURNSTILE", "1")):
-        for d in decs:
-            d.set_option("k1_turnstile", 1)
-    if os.environ.get("EARLY_FETCH"):
-        for d in decs:
-            d.set_option("early_fetch", int(os.environ["EARLY_FETCH"]))
-    if args.pipe_streams > 1:
-        streams = [stream] + [torch.cuda.Stream(dev) for _ in range(n_pipe - 1)]
-    else:
-        streams = [stream] * n_pipe
-    humans_total = 0
-    near_ties = 0
-    launches = 0
-    k1_ms_pipe = []
+def _stage_c_objects(ref, H, W):
+    """estimator.py:276-299 statement for statement, over the reference binary's getters."""
+    from tfpose_b200.humans import BodyPart, Human
+    humans = []
+    for human_id in range(ref.get_num_humans()):
+        human = Human([])
+        is_added = False
+        for part_idx in range(18):
+            c_idx = int(ref.get_part_cid(human_id, part_idx))
+            if c_idx < 0:
+                continue
+            is_added = True
+            human.body_parts[part_idx] = BodyPart('%d-%d' % (human_id, part_idx), part_idx,
+                                                  float(ref.get_part_x(c_idx)) / W, float(ref.get_part_y(c_idx)) / H,
+                                                  ref.get_part_score(c_idx))
+        if is_added:
+            human.score = ref.get_score(human_id)
+            humans.append(human)
+    return humans
 
-    def collect(d):
-        nonlocal humans_total, near_ties, launches
-        res = d.fetch()
-        launches += d.launch_count()
-        humans_total += int(res.info["n_humans"].sum())
-        near_ties += int(res.info["near_ties"].sum())
-        k1_ms_pipe.append(d.stage_ms()[0])
 
-    def run_pipelined(steps, count, with_dense=True):
-        inflight = []
-        for i in range(steps):
-            j = i % n_pipe
-            if len(inflight) == n_pipe:
-                d = inflight.pop(0)
-                if count:
-                    collect(d)
-                else:
-                    d.fetch()
-            decs[j].decode_async(x_dev[i % N_INPUT_SETS], (H, W), dense=denses[j] if with_dense else None,
-                                 stream=streams[j])
-            inflight.append(decs[j])
-        for d in inflight:
-            if count:
-                collect(d)
-            else:
-                d.fetch()
-
-    run_pipelined(max(args.warmup, n_pipe), False)
-    barrier()
-    ev0.record(stream)
-    run_pipelined(args.steps, True)
-    for st_ in streams[1:]:
-        stream.wait_stream(st_)
-    ev1.record(stream)
-    barrier()
-    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
-    ms_per_step = ms_total / args.steps
-    value = world * B * args.steps / (ms_total * 1e-3)
-
-    # ---- the same pipeline in minimal mode (no dense tensors written; the fast path of SURVEY.md 8d) ----
-    run_pipelined(max(args.warmup, n_pipe), False, with_dense=False)
-    barrier()
-    ev0.record(stream)
-    run_pipelined(args.steps, False, with_dense=False)
-    for st_ in streams[1:]:
-        stream.wait_stream(st_)
-    ev1.record(stream)
-    barrier()
-    value_min_pipe = world * B * args.steps / (max_over_ranks(ev0.elapsed_time(ev1)) * 1e-3)
-    for d in decs[1:]:
-        d.close()
-    del denses
-
-    # ---- minimal mode, one call at a time, device-resident ----
-    for i in range(args.warmup):
-        dec.decode(x_dev[i % N_INPUT_SETS], (H, W))
-    barrier()
-    ev0.record(stream)
-    for i in range(args.steps):
-        dec.decode(x_dev[i % N_INPUT_SETS], (H, W))
-    ev1.record(stream)
-    barrier()
-    ms_min = max_over_ranks(ev0.elapsed_time(ev1))
-    value_min = world * B * args.steps / (ms_min * 1e-3)
-
-    # ---- end to end through the host-buffer C-ABI call ----
-    h2d = B * h * w * 57 * 4
-    d2h = B * _lib.INFO_DTYPE.itemsize + B * dec.max_humans * _lib.HUMAN_DTYPE.itemsize
-    xs_np = [t.numpy() for t in x_pin]
-    # two contexts: the pinned input of step i+1 crosses PCIe (tfpd_decode_host_async) while step i is decoded and
-    # its tables come back (fetch); every step pays its own H2D and D2H inside the timed region
-    e2e_decs = [dec, tp.PoseDecoder(max_batch=B, max_upsample=(H, W), device=local_rank)]
-
-    def run_e2e(steps):
-        inflight, last = [], None
-        for i in range(steps):
-            d = e2e_decs[i % 2]
-            if len(inflight) == 2:
-                last = inflight.pop(0).fetch()
-            d.decode_host_async(xs_np[i % N_INPUT_SETS], (H, W))
-            inflight.append(d)
-        for d in inflight:
-            last = d.fetch()
-        return last
-
-    run_e2e(max(args.warmup, 2))
-    barrier()
+def _cpu_decode_one(i):
+    """One frame, all three stages; returns (#humans, seconds in A, B, C)."""
+    if "init_error" in _W:
+        raise RuntimeError("CPU-arm worker failed to initialise: " + _W["init_error"])
+    x = _W["x"][i % len(_W["x"])]
     t0 = time.perf_counter()
-    r = run_e2e(args.steps)
-    torch.cuda.synchronize(dev)
-    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
-    barrier()
-    e2e_decs[1].close()
-    e2e_value = world * B * args.steps / (e2e_ms * 1e-3)
-    e2e_humans = int(r.info["n_humans"].sum())
-    sampler.stop_flag = True
-    sampler.join()
-    gc.enable()
+    peaks, heat_up, paf_up = (_stage_a_torch if _W["stage_a"] == "torch" else _stage_a_c)(x)
+    t1 = time.perf_counter()
+    _W["ref"].process_paf(peaks, heat_up, paf_up)
+    t2 = time.perf_counter()
+    humans = _stage_c_objects(_W["ref"], heat_up.shape[0], heat_up.shape[1])
+    t3 = time.perf_counter()
+    return len(humans), t1 - t0, t2 - t1, t3 - t2
 
-    # ---- end to end including the three dense maps back on the host (what sess.run returns) ----
-    e2e_dense_value = None
-    if args.e2e_dense:
-        ksteps = max(2, min(args.steps, 5))
-        out_pin = tuple(torch.empty((B, H, W, c), dtype=torch.float32).pin_memory().numpy() for c in (19, 38, 19))
-        dec.decode_host(xs_np[0], (H, W), out=out_pin)
-        barrier()
+
+def _run_steps(mapper, frames_per_step, steps, warmup):
+    for s in range(warmup):
+        mapper(range(frames_per_step))
+    t0 = time.perf_counter()
+    acc = np.zeros(4)
+    for s in range(steps):
+        for r in mapper(range(s * frames_per_step, (s + 1) * frames_per_step)):
+            acc += np.array(r)
+    dt = time.perf_counter() - t0
+    return frames_per_step * steps / dt, dt, acc
+
+
+def cpu_arm(x, frames_per_step, steps, warmup, stage_a="torch", forms=("procs", "intraop"), detail=True):
+    """The CPU decode of the frames x[n,h,w,57] (cycled), `steps` steps of `frames_per_step` frames per form.
+    Returns the dict that goes under `cpu_baseline` (headline = the fastest form)."""
+    import multiprocessing as mp
+    import torch
+    from oracle import oracle as O
+    O.build()
+    O.ReferencePafprocess("asbuilt")        # in the parent too: fail here, loudly, if oracle/_ref is missing
+    cores = host_cores()
+    out = {"unit": "frames/s", "kind": "port",
+           "parts": {"stage_a_maps": "port: PyTorch CPU ops on the TF op definitions (TensorFlow unavailable on this box)"
+                                     if stage_a == "torch" else "port: C restatement oracle/maps_oracle.c",
+                     "stage_b_pafprocess": "reference: tf_pose/pafprocess/pafprocess.cpp compiled into oracle/_ref",
+                     "stage_c_objects": "reference statements (estimator.py:276-299) over the binary's getters"},
+           "nproc": os.cpu_count(), "torch_num_threads_default": torch.get_num_threads()}
+    best = None
+    if "procs" in forms:
+        ctx = mp.get_context("spawn")       # not fork: the parent may hold CUDA and OpenMP state
+        with ctx.Pool(cores, initializer=_cpu_pool_init, initargs=(x, 1, stage_a)) as pool:
+            rate, dt, acc = _run_steps(lambda rng: pool.map(_cpu_decode_one, rng, chunksize=1), frames_per_step, steps,
+                                       warmup)
+        n = frames_per_step * steps
+        out["form_worker_per_core"] = {"value": rate, "processes": cores, "torch_threads_per_process": 1, "seconds": dt,
+                                       "frames": n, "ms_per_frame_in_worker": {"stage_a": acc[1] / n * 1e3,
+                                                                               "stage_b": acc[2] / n * 1e3,
+                                                                               "stage_c": acc[3] / n * 1e3}}
+        best = ("one worker process per core, one torch thread each", rate, cores, n, dt, int(acc[0]))
+    if "intraop" in forms:
+        _cpu_worker_init(x, cores, stage_a)
+        fps = max(1, min(frames_per_step, 16))
+        rate, dt, acc = _run_steps(lambda rng: [_cpu_decode_one(i) for i in rng], fps, max(1, steps), min(warmup, 1))
+        n = fps * max(1, steps)
+        out["form_one_process_all_cores"] = {"value": rate, "torch_threads": cores, "seconds": dt, "frames": n,
+                                             "ms_per_frame": {"stage_a": acc[1] / n * 1e3, "stage_b": acc[2] / n * 1e3,
+                                                              "stage_c": acc[3] / n * 1e3}}
+        if best is None or rate > best[1]:
+            best = ("one process, torch intra-op threads over all cores", rate, cores, n, dt, int(acc[0]))
+    if detail:
+        # per-stage cost of one frame on ONE thread, each stage-A implementation
+        k = min(len(x), 4)
+        _cpu_worker_init(x, 1, "torch")
+        t_torch1 = min(_timeit(lambda i=i: _stage_a_torch(x[i])) for i in range(k))
+        _cpu_worker_init(x, cores, "torch")
+        t_torch_all = min(_timeit(lambda i=i: _stage_a_torch(x[i])) for i in range(k))
+        t_c = _timeit(lambda: _stage_a_c(x[0]))
+        out["stage_a_torch"] = {"threads_1_ms": t_torch1 * 1e3, "threads_all_ms": t_torch_all * 1e3, "threads_all": cores}
+        out["stage_a_c_oracle_1_thread_ms"] = t_c * 1e3
+        pk, hu, pu = _stage_a_torch(x[0])
+        out["stage_b_pafprocess_ms"] = _timeit(lambda: _W["ref"].process_paf(pk, hu, pu)) * 1e3
+        _W["ref"].process_paf(pk, hu, pu)
+        out["stage_c_objects_ms"] = _timeit(lambda: _stage_c_objects(_W["ref"], hu.shape[0], hu.shape[1])) * 1e3
+    form, rate, used, n, dt, humans = best
+    out.update({"value": rate, "cores": used, "humans_decoded": humans,
+                "sample": "%d frames of the workload's synthetic batch in %.1f s; fastest CPU form: %s" % (n, dt, form)})
+    return out
+
+
+def _timeit(fn, reps=3):
+    fn()
+    best = 1e30
+    for _ in range(reps):
         t0 = time.perf_counter()
-        for i in range(ksteps):
-            dec.decode_host(xs_np[i % N_INPUT_SETS], (H, W), out=out_pin)
-        torch.cuda.synchronize(dev)
-        e2e_dense_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
-        e2e_dense_value = world * B * ksteps / (e2e_dense_ms * 1e-3)
-
-    # final host gather of the per-rank human counts (not timed; KBs)
-    if world > 1:
-        t = torch.tensor([humans_total], device=dev, dtype=torch.int64)
-        gathered = [torch.zeros_like(t) for _ in range(world)] if rank == 0 else None
-        dist.gather(t, gathered, dst=0)
-        if rank == 0:
-            humans_total = int(sum(int(g.item()) for g in gathered))
-
-    cpu_base = None
-    shard.unbind_host(numa)          # the CPU leg below forks one worker per host core
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cores = host_cores()
-        per = max(cores, 8)
-        steps_cpu = max(1, int(round(12.0 * cores / (0.5 * per))))      # ~12 s of wall time
-        steps_cpu = min(steps_cpu, 8)
-        rate, dt, _, kind = cpu_decode_rate(sets_host[0][:32], per, steps_cpu, 1, cores)
-        cpu_base = {"value": rate, "unit": "frames/s", "cores": cores, "kind": "reference" if kind != "port" else "port",
-                    "sample": "%d frames of the same synthetic batch in %.1f s on %d worker processes; maps = C "
-                              "restatement of the TF ops (TensorFlow unavailable), pafprocess = reference's own "
-                              "pafprocess.cpp (oracle/_ref)" % (per * steps_cpu, dt, cores)}
-
-    if rank == 0:
-        peak, peak_src = measured_peak_gbs()
-        k1 = float(np.mean(k1_ms))
-        alg = dense_bytes_per_frame(h, w, f) * B
-        achieved = alg / (k1 * 1e-3) / 1e9
-        traffic = None
-        tpath = os.path.join(ROOT, "profiles", "k1_traffic.json")
-        if os.path.exists(tpath):
-            try:
-                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
-            except Exception:
-                traffic = None
-        line = {
-            "metric": "decoded_frames_per_s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD % B,
-                       "batch_per_gpu": B, "global_batch": B * world, "sharding": "by image, no collective",
-                       "host_numa": {k: numa[k] for k in ("node", "mempolicy", "cpus")},
-                       "l2": "outputs 773 MB/step exceed the 126 MB L2; %d rotating input batches" % N_INPUT_SETS,
-                       "mode": "asbuilt",
-                       "pipeline": "%d contexts round-robin on %d stream(s): later steps are enqueued before step i's "
-                                   "tables are fetched; the HBM-bound map kernel runs on %s of the SMs so that the "
-                                   "latency-bound scoring/assembly kernels of the previous batches overlap it; "
-                                   "roofline/stage_ms from a second K-step region run one call at a time with the same "
-                                   "settings" % (n_pipe, len(set(id(s_) for s_ in streams)),
-                                                 ("%d CTAs" % args.k1_ctas) if args.k1_ctas else "all")},
-            "roofline": {"bound": "hbm", "kernel": "k1_fused_f4 (upsample+smoother+NMS, dense)", "achieved": achieved,
-                         "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "algorithmic_bytes_per_launch": alg, "kernel_ms": k1},
-            "stage_ms": {"k1_maps": stage_acc[0] / args.steps, "peak_sort": stage_acc[1] / args.steps,
-                         "k2_limbs": stage_acc[2] / args.steps, "k3_assemble": stage_acc[3] / args.steps},
-            "value_one_call_at_a_time": value_serial, "k1_ms_in_pipelined_region": float(np.mean(k1_ms_pipe)),
-            "value_minimal_mode": value_min,
-            "value_minimal_mode_pipelined": value_min_pipe,
-            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "call": "PoseDecoder.decode_host_async + fetch (tfpd_decode_host_async / tfpd_fetch_humans): pinned host input -> "
-                            "human tables on host, two contexts alternating, dense maps left on device"},
-            "e2e_dense_maps": e2e_dense_value,
-            "gpu_launches": launches, "clocks": sampler.result(), "humans_decoded": humans_total,
-            "near_tie_pixels": near_ties, "e2e_humans_last_step": e2e_humans,
-        }
-        if cpu_base is not None:
-            line["cpu_baseline"] = cpu_base
-        emit(line)
-    dec.close()
-    if world > 1:
-        dist.destroy_process_group()
-
-
-_REAL_STDOUT = None
-
-
-def quiet_stdout():
-    """stdout carries exactly one JSON line: everything libraries print there (NCCL's version banner comes from C
-    code, on file descriptor 1) is sent to stderr; emit() writes the line to the real stdout."""
-    global _REAL_STDOUT
-    if _REAL_STDOUT is None:
-        sys.stdout.flush()
-        _REAL_STDOUT = os.dup(1)
-        os.dup2(2, 1)
-
-
-def emit(line):
-    sys.stdout.flush()
-    data = (json.dumps(line) + "\n").encode()
-    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
-
-
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=BATCH)
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-numa", action="store_true", help="leave host memory policy and CPU affinity alone")
-    ap.add_argument("--pipeline", type=int, default=3, help="contexts in flight in the device-resident timed region")
-    ap.add_argument("--k1-ctas", type=int, default=128, help="CTAs of the fused map kernel (0 = one per SM)")
-    ap.add_argument("--pipe-streams", type=int, default=2, help="1: all contexts on one stream, 2: one stream each")
-    ap.add_argument("--no-e2e-dense", dest="e2e_dense", action="store_false", default=True)
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    quiet_stdout()
-    if args.impl == "reference":
-        run_reference(args, rank, world)
-    else:
-        run_ours(args, rank, world, local_rank)
-
-
-if __name__ == "__main__":
-    main()
+        fn()
+        best = min(best, time.perf_counter() - t0)
+    return best

@@ -399,3 +399,53 @@ def test_gpu_numa_node_lookup_and_unbind(tmp_path):
     done = shard.bind_host_to_gpu_node(0, sysfs=str(tmp_path))       # no CUDA device here: nothing done, no raise
     assert done["node"] == -1 and not done["mempolicy"]
     shard.unbind_host(done)
+
+
+def test_objbuild_extension_builds_the_same_objects_as_the_python_loop():
+    """csrc/objbuild.c (DecodeResult.all_humans) against decoder.humans_from_table, the Python statement of
+    estimate_paf's object loop (estimator.py:276-299): same humans, same insertion order, same attribute VALUES AND
+    TYPES (Python float / int / str), Human([])'s empty pairs / uidx_list, a human without parts dropped, human ids
+    beyond the cached uidx range."""
+    from tfpose_b200 import _lib
+    from tfpose_b200.decoder import DecodeResult, _objbuild, humans_from_table
+    from tfpose_b200.humans import BodyPart, Human
+    ob = _objbuild()
+    assert ob is not None, "tf-pose-estimation_b200/_objbuild.so is not built (make -C tf-pose-estimation_b200/csrc)"
+    assert ob.HUMAN_RECORD_BYTES == _lib.HUMAN_DTYPE.itemsize == 184
+    rng = np.random.default_rng(3)
+    N, MH = 9, 600
+    table = np.zeros((N, MH), _lib.HUMAN_DTYPE)
+    counts = np.array([0, 1, 3, 6, 2, 600, 1, 4, 5], np.int32)
+    for i in range(N):
+        for j in range(counts[i]):
+            present = rng.random(18) < 0.8
+            table[i, j]["cid"] = np.where(present, rng.integers(0, 4000, 18), -1)
+            table[i, j]["x"] = rng.integers(0, 656, 18)
+            table[i, j]["y"] = rng.integers(0, 368, 18)
+            table[i, j]["part_score"] = rng.random(18).astype(np.float32)
+            table[i, j]["score"] = np.float32(rng.random() * 2)
+    table[3, 1]["cid"] = -1                      # a record without any part: estimate_paf never appends it
+    info = np.zeros(N, _lib.INFO_DTYPE)
+    info["n_humans"] = counts
+    res = DecodeResult(info, table, 368, 656)
+    got = res.all_humans()
+    assert isinstance(got, list) and len(got) == N
+    for i in range(N):
+        want = humans_from_table(table[i], counts[i], 368, 656)
+        assert isinstance(got[i], list) and len(got[i]) == len(want)
+        for a, b in zip(want, got[i]):
+            assert type(b) is Human and b.pairs == [] and b.uidx_list == set() and type(b.body_parts) is dict
+            assert type(b.score) is float and b.score == a.score
+            assert list(b.body_parts) == list(a.body_parts)
+            for k, p in a.body_parts.items():
+                q = b.body_parts[k]
+                assert type(q) is BodyPart
+                assert (q.uidx, q.part_idx, q.x, q.y, q.score) == (p.uidx, p.part_idx, p.x, p.y, p.score)
+                assert (type(q.uidx), type(q.part_idx), type(q.x), type(q.y), type(q.score)) == (str, int, float, float, float)
+                assert str(q) == str(p)
+    assert len(got[3]) == 5 and len(got[5]) == 600 and got[5][599].body_parts
+    assert next(iter(got[5][599].body_parts.values())).uidx.startswith("599-")
+    with pytest.raises(ValueError):
+        ob.build_humans(BodyPart, Human, table[:1].tobytes(), counts.tobytes(), MH, 368, 656)    # table too small
+    with pytest.raises(TypeError):
+        ob.build_humans(int, Human, table.tobytes(), counts.tobytes(), MH, 368, 656)             # no such slots
