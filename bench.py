@@ -284,7 +284,8 @@ def _run_steps(mapper, frames_per_step, steps, warmup):
     return frames_per_step * steps / dt, dt, acc
 
 
-def cpu_arm(x, frames_per_step, steps, warmup, stage_a="torch", forms=("procs", "intraop"), detail=True):
+def cpu_arm(x, frames_per_step, steps, warmup, stage_a="torch", forms=("procs", "intraop"), detail=True,
+            intraop_cap=16):
     """The CPU decode of the frames x[n,h,w,57] (cycled), `steps` steps of `frames_per_step` frames per form.
     Returns the dict that goes under `cpu_baseline` (headline = the fastest form)."""
     import multiprocessing as mp
@@ -313,7 +314,7 @@ def cpu_arm(x, frames_per_step, steps, warmup, stage_a="torch", forms=("procs", 
         best = ("one worker process per core, one torch thread each", rate, cores, n, dt, int(acc[0]))
     if "intraop" in forms:
         _cpu_worker_init(x, cores, stage_a)
-        fps = max(1, min(frames_per_step, 16))
+        fps = max(1, min(frames_per_step, intraop_cap or frames_per_step))
         rate, dt, acc = _run_steps(lambda rng: [_cpu_decode_one(i) for i in rng], fps, max(1, steps), min(warmup, 1))
         n = fps * max(1, steps)
         out["form_one_process_all_cores"] = {"value": rate, "torch_threads": cores, "seconds": dt, "frames": n,
@@ -349,3 +350,435 @@ def _timeit(fn, reps=3):
         fn()
         best = min(best, time.perf_counter() - t0)
     return best
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+class Job(object):
+    """One rank of the job: device, process group, and the reductions the timing needs."""
+
+    def __init__(self, rank, world, local_rank):
+        import torch
+        self.torch, self.rank, self.world, self.local_rank = torch, rank, world, local_rank
+        torch.cuda.set_device(local_rank)
+        self.dev = torch.device("cuda", local_rank)
+        self.dist = None
+        if world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=self.dev)
+            self.dist = dist
+        self.stream = torch.cuda.current_stream(self.dev)
+        self.ev0 = torch.cuda.Event(enable_timing=True)
+        self.ev1 = torch.cuda.Event(enable_timing=True)
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize(self.dev)
+
+    def max_over_ranks(self, v):
+        if self.dist is None:
+            return float(v)
+        t = self.torch.tensor([v], device=self.dev, dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(self, v):
+        if self.dist is None:
+            return float(v)
+        t = self.torch.tensor([v], device=self.dev, dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def all_ranks(self, values):
+        """[world][len(values)] float64 on every rank (a few numbers per rank: never on the data path)."""
+        t = self.torch.tensor([list(values)], device=self.dev, dtype=self.torch.float64)
+        if self.dist is None:
+            return t.cpu().numpy()
+        out = self.torch.zeros((self.world, len(values)), device=self.dev, dtype=self.torch.float64)
+        self.dist.all_gather_into_tensor(out, t)
+        return out.cpu().numpy()
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+
+def make_inputs(cfg, B, rank, base_frames):
+    """N_INPUT_SETS different batches of B frames for this rank: `base_frames` distinct synthetic frames per set
+    (frame seeds never repeat across sets or ranks), tiled up to B."""
+    from tfpose_b200 import synth
+    sets = []
+    for sidx in range(N_INPUT_SETS):
+        nb = min(B, base_frames)
+        kw = {"people": cfg["people"]} if cfg["people"] else {}
+        base = synth.synth_batch(nb, cfg["h"], cfg["w"], config_id=cfg["id"],
+                                 first_frame=(rank * N_INPUT_SETS + sidx) * base_frames, **kw)
+        reps = (B + nb - 1) // nb
+        sets.append(np.concatenate([base] * reps)[:B].copy())
+    return sets
+
+
+def timed_region(job, sampler, fn):
+    """barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks (ms); also this
+    rank's own time."""
+    job.barrier()
+    t0 = time.time()
+    job.ev0.record(job.stream)
+    fn()
+    job.ev1.record(job.stream)
+    job.barrier()
+    if sampler is not None:
+        sampler.window(t0, time.time())
+    mine = job.ev0.elapsed_time(job.ev1)
+    return job.max_over_ranks(mine), mine
+
+
+def measure_device(job, key, args, sampler, steps, base_frames):
+    """Device-resident throughput of one config on this job: pipelined dense (= value), one call at a time (per-kernel
+    times, K1 roofline), and both again in minimal mode."""
+    import tfpose_b200 as tp
+    torch, dev = job.torch, job.dev
+    cfg = CONFIGS[key]
+    B = frames_per_rank(cfg, job.world, args.batch if key == args.config else None)
+    h, w = cfg["h"], cfg["w"]
+    H, W = FACTOR * h, FACTOR * w
+    sets_host = make_inputs(cfg, B, job.rank, base_frames)
+    x_dev = [torch.from_numpy(s).to(dev) for s in sets_host]
+    n_pipe = max(1, args.pipeline)
+    mk_dense = lambda: (torch.empty((B, H, W, 19), device=dev), torch.empty((B, H, W, 38), device=dev),
+                        torch.empty((B, H, W, 19), device=dev))
+    decs = [tp.PoseDecoder(max_batch=B, max_upsample=(H, W), device=job.local_rank, **cfg["caps"]) for _ in range(n_pipe)]
+    denses = [mk_dense() for _ in range(n_pipe)]
+    for d in decs:
+        d.set_profiling(True)
+        d.set_option("k1_ctas", args.k1_ctas)
+    dec, dense = decs[0], denses[0]
+    warm = max(args.warmup, 3)
+
+    # ---- one call at a time (decode -> fetch): every kernel runs alone -> per-kernel times, K1 roofline ----
+    def serial(with_dense, acc):
+        for i in range(steps):
+            dec.decode(x_dev[i % N_INPUT_SETS], (H, W), dense=dense if with_dense else None)
+            if acc is not None:
+                acc.append(dec.stage_ms())
+    for i in range(warm):
+        dec.decode(x_dev[i % N_INPUT_SETS], (H, W), dense=dense)
+    st_dense = []
+    ms_serial, _ = timed_region(job, sampler, lambda: serial(True, st_dense))
+    for i in range(warm):
+        dec.decode(x_dev[i % N_INPUT_SETS], (H, W))
+    st_min = []
+    ms_serial_min, _ = timed_region(job, sampler, lambda: serial(False, st_min))
+    st_dense, st_min = np.array(st_dense), np.array(st_min)
+
+    # ---- pipelined: n_pipe contexts round-robin; later steps are enqueued before step i's tables are fetched ----
+    if int(os.environ.get("K1_TURNSTILE", "1")):
+        for d in decs:
+            d.set_option("k1_turnstile", 1)
+    streams = [job.stream] + [torch.cuda.Stream(dev) for _ in range(n_pipe - 1)] if args.pipe_streams > 1 \
+        else [job.stream] * n_pipe
+    stats = {"humans": 0, "near": 0, "launches": 0, "enqueue_s": 0.0, "fetch_s": 0.0, "peaks": 0}
+
+    def collect(d, count):
+        t0 = time.perf_counter()
+        res = d.fetch(reuse=True)
+        stats["fetch_s"] += time.perf_counter() - t0
+        if count:
+            stats["launches"] += d.launch_count()
+            stats["humans"] += int(res.info["n_humans"].sum())
+            stats["near"] += int(res.info["near_ties"].sum())
+            stats["peaks"] += int(res.info["n_peaks"].sum())
+
+    def pipelined(nsteps, count, with_dense):
+        inflight = []
+        for i in range(nsteps):
+            j = i % n_pipe
+            if len(inflight) == n_pipe:
+                collect(inflight.pop(0), count)
+            t0 = time.perf_counter()
+            decs[j].decode_async(x_dev[i % N_INPUT_SETS], (H, W), dense=denses[j] if with_dense else None,
+                                 stream=streams[j])
+            stats["enqueue_s"] += time.perf_counter() - t0
+            inflight.append(decs[j])
+        for d in inflight:
+            collect(d, count)
+        for st_ in streams[1:]:
+            job.stream.wait_stream(st_)
+
+    pipelined(max(warm, n_pipe), False, True)
+    stats.update(enqueue_s=0.0, fetch_s=0.0)
+    ms_pipe, ms_pipe_mine = timed_region(job, sampler, lambda: pipelined(steps, True, True))
+    host = (stats["enqueue_s"] / steps * 1e3, stats["fetch_s"] / steps * 1e3)
+    pipelined(max(warm, n_pipe), False, False)
+    ms_pipe_min, _ = timed_region(job, sampler, lambda: pipelined(steps, False, False))
+
+    frames_job = job.sum_over_ranks(B)                     # frames of the whole job per step
+    per_rank = job.all_ranks([ms_pipe_mine / steps, float(st_dense[:, 0].mean()), host[0], host[1], B])
+    humans_job = job.sum_over_ranks(stats["humans"])
+    for d in decs:
+        d.close()
+    del denses, dense, x_dev
+    torch.cuda.empty_cache()
+
+    peak, peak_src = measured_peak_gbs()
+    k1 = float(st_dense[:, 0].mean())
+    alg = dense_bytes_per_frame(h, w) * B
+    k1_min = float(st_min[:, 0].mean())
+    flops = polyphase_flops_per_frame(h, w) * B
+    out = {
+        "workload": cfg["name"] % B, "frames_per_gpu": B, "frames_per_step_job": int(frames_job),
+        "scaling": scaling_of(cfg), "steps": steps,
+        "value": frames_job * steps / (ms_pipe * 1e-3), "ms_per_step": ms_pipe / steps,
+        "value_one_call_at_a_time": frames_job * steps / (ms_serial * 1e-3),
+        "value_minimal_mode_pipelined": frames_job * steps / (ms_pipe_min * 1e-3),
+        "value_minimal_mode": frames_job * steps / (ms_serial_min * 1e-3),
+        "stage_ms": {"k1_maps": k1, "peak_sort": float(st_dense[:, 1].mean()), "k2_limbs": float(st_dense[:, 2].mean()),
+                     "k3_assemble": float(st_dense[:, 3].mean())},
+        "stage_ms_minimal": {"k1_maps": k1_min, "k2_limbs": float(st_min[:, 2].mean()),
+                             "k3_assemble": float(st_min[:, 3].mean())},
+        "roofline": {"bound": "hbm", "kernel": "k1_fused_f4 (upsample+smoother+NMS, dense)",
+                     "achieved": alg / (k1 * 1e-3) / 1e9, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                     "frac": alg / (k1 * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_launch": alg, "kernel_ms": k1,
+                     "traffic": profile_constant("k1_traffic.json", "dram_bytes_per_launch") if key == "c2" and B == 64 else None},
+        "roofline_minimal": {"bound": "fp32", "kernel": "k1_fused_f4 (smoother+NMS only, nothing dense written)",
+                             "achieved_tflops": flops / (k1_min * 1e-3) / 1e12, "algorithmic_flops_per_launch": flops,
+                             "kernel_ms": k1_min, "note": "polyphase form: 2*(7 + 7/4) flop per output pixel of 19 channels",
+                             "pipe_fma_pct": profile_constant("k1_minimal.json", "pipe_fma_pct") if key == "c2" else None},
+        "per_rank": [{"rank": r, "ms_per_step": float(v[0]), "k1_ms": float(v[1]), "host_enqueue_ms_per_step": float(v[2]),
+                      "host_fetch_wait_ms_per_step": float(v[3]), "frames": int(v[4])} for r, v in enumerate(per_rank)],
+        "l2": "%d rotating input batches (%.0f MB each) and %.0f MB of dense outputs per step against the 126 MB L2"
+              % (N_INPUT_SETS, B * h * w * 228 / 1e6, B * 76 * H * W * 4 / 1e6),
+        "humans_decoded": int(humans_job), "peaks_per_frame": stats["peaks"] / max(1, steps * B),
+        "near_tie_pixels": stats["near"], "gpu_launches": stats["launches"],
+    }
+    return out, sets_host
+
+
+def measure_e2e(job, key, args, sampler, steps, sets_host):
+    """End to end through the host-buffer C-ABI call: pinned host input -> results on the host, every step paying
+    its own H2D and D2H inside the timed region (wall clock around synchronised regions, max over ranks)."""
+    import tfpose_b200 as tp
+    from tfpose_b200 import _lib
+    torch, dev = job.torch, job.dev
+    cfg = CONFIGS[key]
+    B = len(sets_host[0])
+    h, w = cfg["h"], cfg["w"]
+    H, W = FACTOR * h, FACTOR * w
+    xs = [torch.from_numpy(s).pin_memory().numpy() for s in sets_host]
+    decs = [tp.PoseDecoder(max_batch=B, max_upsample=(H, W), device=job.local_rank, **cfg["caps"]) for _ in range(2)]
+    frames_job = job.sum_over_ranks(B)
+
+    # two contexts: the pinned input of step i+1 crosses PCIe (tfpd_decode_host_async) while step i is decoded and
+    # its tables come back (fetch)
+    def run(nsteps, objects):
+        inflight, last, n_obj = [], None, 0
+        for i in range(nsteps):
+            d = decs[i % 2]
+            if len(inflight) == 2:
+                last = inflight.pop(0).fetch(reuse=True)
+                if objects:
+                    n_obj += sum(len(f) for f in last.all_humans())
+            d.decode_host_async(xs[i % N_INPUT_SETS], (H, W))
+            inflight.append(d)
+        for d in inflight:
+            last = d.fetch(reuse=True)
+            if objects:
+                n_obj += sum(len(f) for f in last.all_humans())
+        return last, n_obj
+
+    def wall(fn):
+        job.barrier()
+        t0 = time.time()
+        r = fn()
+        torch.cuda.synchronize(dev)
+        dt = time.time() - t0
+        if sampler is not None:
+            sampler.window(t0, t0 + dt)
+        ms = job.max_over_ranks(dt * 1e3)
+        job.barrier()
+        return ms, r
+
+    run(max(args.warmup, 3), False)
+    ms, (last, _) = wall(lambda: run(steps, False))
+    out = {"e2e": {"value": frames_job * steps / (ms * 1e-3), "unit": "frames/s",
+                   "h2d_bytes_per_step": B * h * w * 57 * 4,
+                   "d2h_bytes_per_step": B * _lib.INFO_DTYPE.itemsize + B * decs[0].max_humans * _lib.HUMAN_DTYPE.itemsize,
+                   "call": "PoseDecoder.decode_host_async + fetch (tfpd_decode_host_async / tfpd_fetch_humans): pinned "
+                           "host input -> human tables on host, two contexts alternating; heatMat / pafMat stay on the "
+                           "device (inference() also returns them to the host: that variant is e2e_dense_maps)"},
+           "e2e_humans_last_step": int(last.info["n_humans"].sum())}
+    # the same, plus the list[list[Human]] the reference's inference() returns (built by the _objbuild extension)
+    run(max(args.warmup, 3), True)
+    ms, (_, n_obj) = wall(lambda: run(steps, True))
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        hs = last.all_humans()
+    obj_s = (time.perf_counter() - t0) / reps
+    out["e2e_objects"] = {"value": frames_job * steps / (ms * 1e-3), "unit": "frames/s",
+                          "humans_built": int(n_obj), "call": "e2e + DecodeResult.all_humans(): host input -> list[list[Human]]",
+                          "objects_only_frames_per_s_one_core": B / obj_s,
+                          "objects_only_ms_per_step": obj_s * 1e3, "humans_per_step": sum(len(f) for f in hs)}
+    decs[1].close()
+    if args.e2e_dense:
+        ksteps = max(2, min(steps, 5))
+        out_pin = tuple(torch.empty((B, H, W, c), dtype=torch.float32).pin_memory().numpy() for c in (19, 38, 19))
+        decs[0].decode_host(xs[0], (H, W), out=out_pin)
+        ms, _ = wall(lambda: [decs[0].decode_host(xs[i % N_INPUT_SETS], (H, W), out=out_pin) for i in range(ksteps)])
+        out["e2e_dense_maps"] = {"value": frames_job * ksteps / (ms * 1e-3), "unit": "frames/s",
+                                 "d2h_bytes_per_step": B * 76 * H * W * 4,
+                                 "call": "decode_host with the three dense maps copied back into page-locked arrays"}
+    decs[0].close()
+    return out
+
+
+def run_ours(args, rank, world, local_rank):
+    import tfpose_b200  # noqa: F401  (fails loudly when libtfpose_decode.so is not built: no CPU path)
+    from tfpose_b200 import shard
+    # before any host buffer exists: pinned inputs on the GPU's own NUMA node (matters with 8 ranks on two sockets)
+    numa = shard.bind_host_to_gpu_node(local_rank) if not args.no_numa else {"node": -1, "mempolicy": False, "cpus": 0}
+    job = Job(rank, world, local_rank)
+    sampler = ClockSampler(list(range(world)), float(os.environ.get("BENCH_SAMPLE_PERIOD", "0.002"))) if rank == 0 else None
+    # the timed regions are a few milliseconds long: keep the collector's pauses out of them
+    gc.collect()
+    gc.disable()
+    key = args.config
+    main, sets_host = measure_device(job, key, args, sampler, args.steps, 16)
+    e2e = measure_e2e(job, key, args, sampler, args.steps, sets_host) if not args.no_e2e else {}
+    per_config = {}
+    if args.per_config:
+        for other in ("c2", "c3", "c4", "c5"):
+            if other == key:
+                continue
+            res, _ = measure_device(job, other, args, sampler, max(5, min(args.steps, 20)), 8)
+            keep = ("workload", "frames_per_gpu", "frames_per_step_job", "scaling", "steps", "value", "ms_per_step",
+                    "value_one_call_at_a_time", "value_minimal_mode_pipelined", "stage_ms", "per_rank",
+                    "humans_decoded", "peaks_per_frame", "l2")
+            per_config[other] = {k: res[k] for k in keep}
+            per_config[other]["k1_roofline_frac"] = res["roofline"]["frac"]
+            per_config[other]["k1_achieved_gbs"] = res["roofline"]["achieved"]
+    gc.enable()
+    clocks = sampler.result() if sampler is not None else None
+
+    cpu_base = None
+    shard.unbind_host(numa)          # the CPU leg below uses every host core
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_base = cpu_arm(sets_host[0][:32], 32, 2, 1)
+
+    if rank == 0:
+        cfg = CONFIGS[key]
+        line = {
+            "metric": "decoded_frames_per_s", "value": main["value"], "unit": "frames/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": main["ms_per_step"],
+            "higher_is_better": True, "scaling": main["scaling"], "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": main["workload"], "config": key, "batch_per_gpu": main["frames_per_gpu"],
+                       "global_batch": main["frames_per_step_job"], "sharding": "by image, no collective",
+                       "host_numa": {k: numa[k] for k in ("node", "mempolicy", "cpus")}, "l2": main["l2"],
+                       "mode": "asbuilt",
+                       "pipeline": "%d contexts round-robin on %s stream(s): later steps are enqueued before step i's "
+                                   "tables are fetched; the HBM-bound map kernel runs on %s so that the latency-bound "
+                                   "scoring/assembly kernels of the previous batches overlap it; roofline/stage_ms from "
+                                   "a second K-step region run one call at a time with the same settings"
+                                   % (args.pipeline, "%d" % args.pipeline if args.pipe_streams > 1 else "1",
+                                      ("%d CTAs" % args.k1_ctas) if args.k1_ctas else "all SMs")},
+            "roofline": main["roofline"], "roofline_minimal": main["roofline_minimal"],
+            "stage_ms": main["stage_ms"], "stage_ms_minimal": main["stage_ms_minimal"],
+            "value_one_call_at_a_time": main["value_one_call_at_a_time"],
+            "value_minimal_mode": main["value_minimal_mode"],
+            "value_minimal_mode_pipelined": main["value_minimal_mode_pipelined"],
+            "per_rank": main["per_rank"],
+            "gpu_launches": main["gpu_launches"], "clocks": clocks, "humans_decoded": main["humans_decoded"],
+            "near_tie_pixels": main["near_tie_pixels"],
+        }
+        line.update(e2e)
+        if "e2e" not in line:
+            line["e2e"] = None
+        if per_config:
+            line["per_config"] = per_config
+        if cpu_base is not None:
+            line["cpu_baseline"] = cpu_base
+        emit(line)
+    job.close()
+
+
+def run_reference(args, rank, world):
+    """The reference's CPU decode on the box's host cores, same workload and frames per step as the repo arm
+    (rank 0 alone; the other ranks leave at once)."""
+    if rank != 0:
+        return
+    from tfpose_b200 import synth
+    cfg = CONFIGS[args.config]
+    B = frames_per_rank(cfg, 1 if "total" in cfg else world, args.batch)    # one host: the whole job's step
+    kw = {"people": cfg["people"]} if cfg["people"] else {}
+    x = synth.synth_batch(min(B, 64), cfg["h"], cfg["w"], config_id=cfg["id"], **kw)
+    # which CPU form is faster on this host: one short step each, then the timed run with that one
+    probe = cpu_arm(x, B, 1, 1, detail=False, intraop_cap=None)
+    form = "procs" if probe["form_worker_per_core"]["value"] >= probe["form_one_process_all_cores"]["value"] else "intraop"
+    res = cpu_arm(x, B, args.steps, args.warmup, forms=(form,), detail=True, intraop_cap=None)
+    res["probe_frames_per_s"] = {"worker_per_core": probe["form_worker_per_core"]["value"],
+                                 "one_process_all_cores": probe["form_one_process_all_cores"]["value"]}
+    dt = (res.get("form_worker_per_core") or res.get("form_one_process_all_cores"))["seconds"]
+    line = {
+        "impl": "reference", "metric": "decoded_frames_per_s", "value": res["value"], "unit": "frames/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": scaling_of(cfg), "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfg["name"] % frames_per_rank(cfg, world, args.batch), "config": args.config,
+                   "batch_per_gpu": frames_per_rank(cfg, world, args.batch), "frames_per_step": B,
+                   "sharding": "by image, no collective", "mode": "asbuilt"},
+        "cpu_baseline": res,
+        "e2e": {"value": res["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "humans_decoded": res["humans_decoded"],
+    }
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """stdout carries exactly one JSON line: everything libraries print there (NCCL's version banner comes from C
+    code, on file descriptor 1) is sent to stderr; emit() writes the line to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="c2", choices=sorted(CONFIGS), help="BASELINE.json config the line is quoted on")
+    ap.add_argument("--batch", type=int, default=0, help="frames per GPU of --config (0 = the config's own)")
+    ap.add_argument("--no-per-config", dest="per_config", action="store_false", default=True,
+                    help="skip the short runs of the other configs (per_config)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-numa", action="store_true", help="leave host memory policy and CPU affinity alone")
+    ap.add_argument("--pipeline", type=int, default=3, help="contexts in flight in the device-resident timed region")
+    ap.add_argument("--k1-ctas", type=int, default=128, help="CTAs of the fused map kernel (0 = one per SM)")
+    ap.add_argument("--pipe-streams", type=int, default=2, help="1: all contexts on one stream, 2: one stream each")
+    ap.add_argument("--no-e2e-dense", dest="e2e_dense", action="store_false", default=True)
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    quiet_stdout()
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -234,6 +234,11 @@ TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, s
  *   "k1_turnstile" 1: the map kernels of all contexts on this device run one after the other (stream-ordered through
  *                  a per-device event), whatever their streams.  With several contexts in flight this keeps a
  *                  second HBM-bound map kernel from starting on the SMs "k1_ctas" leaves to the tail kernels.
+ *   "k1_early_out" 1 (default): in minimal mode (no dense outputs) the fused map kernel skips a low-res row group of a
+ *                  channel when the largest heat value in the 8 low-res rows that group reads is below
+ *                  thresh_heat * (1 - 2e-4) / (sum of smoother weights)^2: every smoother weight is >= 0, so no
+ *                  blurred value there can come within reach of the heat threshold or of a near-tie test.  Exact:
+ *                  same tables, same near-tie counts; 0 computes every row.  Dense mode always computes every row.
  *   "early_fetch"  when the tables start their way to the host: 0 in tfpd_fetch_humans (default), 1 right behind
  *                  the last kernel on the same stream, 2 behind it on a side stream.
  *   "pow2_path"    kernels for power-of-two upsample factors other than the x4 fast path (2, 8, 16): 1 automatic

@@ -16,6 +16,9 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
+# TFPD_ORACLE_LIBDIR: another build of the same checker libraries (tools/sanitize_cpu.sh points it at the
+# ASan/UBSan builds under oracle/_san); default = the in-tree build
+_LIBDIR = os.environ.get("TFPD_ORACLE_LIBDIR") or _HERE
 _F = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
 _D = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 _I = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
@@ -38,7 +41,7 @@ def maps_lib():
     global _maps
     if _maps is None:
         build()
-        L = C.CDLL(os.path.join(_HERE, "liboracle_maps.so"))
+        L = C.CDLL(os.path.join(_LIBDIR, "liboracle_maps.so"))
         L.oracle_gauss_kernel.argtypes = [C.c_int, C.c_double, _F, _D]
         L.oracle_split.argtypes = [_F, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _F]
         L.oracle_resize_area.argtypes = [_F, C.c_int, C.c_int, C.c_int, _F, C.c_int, C.c_int]
@@ -56,7 +59,7 @@ def paf_lib():
     global _paf
     if _paf is None:
         build()
-        L = C.CDLL(os.path.join(_HERE, "liboracle_paf.so"))
+        L = C.CDLL(os.path.join(_LIBDIR, "liboracle_paf.so"))
         L.paf_oracle_run.argtypes = [_F, _F, _F, C.c_int, C.c_int, C.c_int, C.c_int]
         L.paf_oracle_run.restype = C.c_void_p
         L.paf_oracle_run_cfg.argtypes = [_F, _F, _F, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -229,7 +232,7 @@ class ReferencePafprocess(object):
     get_part_y / get_part_score), bound through the C++ mangled names."""
 
     def __init__(self, variant="asbuilt"):
-        path = os.path.join(_HERE, "_ref", "libpafprocess_%s.so" % variant)
+        path = os.path.join(_LIBDIR, "_ref", "libpafprocess_%s.so" % variant)
         if not os.path.exists(path):
             build()
         if not os.path.exists(path):

@@ -329,3 +329,48 @@ def test_overflowing_frame_does_not_cost_the_batch_its_other_frames(cuda):
     post = tp.TfPosePostProcessor(target_size=(432, 368), keep_maps=False)
     assert len(post.inference_from_output(x[2], upsample_size=4.0)) == int(want.info["n_humans"][2])
     post.close()
+
+
+def test_minimal_mode_early_out_is_exact(cuda):
+    """Minimal mode skips low-res row groups whose heat window cannot reach the threshold ("k1_early_out",
+    include/tfpose_decode.h).  The skip must change nothing: tables, peak lists and frame info -- near-tie counts
+    included -- are identical with the option off, on sparse, crowded and empty frames, on frames whose blobs sit
+    just below / just above the bound (the decisive case: a window maximum within 1e-3 of thresh_heat), and with a
+    raised heat threshold (more of the map is dead)."""
+    import torch
+    from helpers import table_tuples
+
+    def both_ways(x, H, W, **cfg):
+        xd = torch.from_numpy(x).cuda()
+        out = []
+        for early in (1, 0):
+            dec = tp.PoseDecoder(max_batch=len(x), max_upsample=(H, W), **cfg)
+            dec.set_option("k1_early_out", early)
+            res = dec.decode(xd, (H, W))
+            out.append((res, [dec.peaks(i) for i in range(len(x))]))
+            dec.close()
+        (ra, pa), (rb, pb) = out
+        assert np.array_equal(ra.info, rb.info), "frame info (peaks / near-ties / humans) differs with the early-out"
+        for i in range(len(x)):
+            assert table_tuples(ra, i) == table_tuples(rb, i)
+            assert all(np.array_equal(pa[i][k], pb[i][k]) for k in pa[i])
+        return ra
+
+    caps = dict(max_peaks=4096, max_cands=8192, max_humans=128)
+    r = both_ways(synth.synth_batch(16, 46, 54, config_id=2, first_frame=700), 184, 216)
+    assert int(r.info["n_humans"].sum()) > 0
+    both_ways(synth.synth_batch(4, 46, 54, config_id=4, people=30, first_frame=20), 184, 216, **caps)
+    both_ways(synth.synth_batch(3, 46, 82, config_id=3, first_frame=40), 184, 328)
+    both_ways(np.zeros((2, 46, 54, 57), np.float32), 184, 216)
+    # isolated blobs scaled so that the blurred peak / the window maximum straddle the threshold and the bound
+    rng = np.random.default_rng(11)
+    x = np.zeros((12, 20, 30, 57), np.float32)
+    for i, amp in enumerate(np.linspace(0.0495, 0.0515, 12)):
+        x[i, :, :, :19] = rng.normal(0, 1e-4, (20, 30, 19))
+        for c in range(18):
+            cy, cx = rng.integers(2, 18), rng.integers(2, 28)
+            x[i, cy, cx, c] = amp                       # single hot cell: window max == amp, blurred peak far lower
+            x[i, (cy + 9) % 20, (cx + 11) % 30, c] = amp * 21.0   # and one whose BLURRED value is near the threshold
+    both_ways(x, 80, 120, **caps)
+    r = both_ways(synth.synth_batch(8, 46, 54, config_id=2, first_frame=800), 184, 216, thresh_heat=0.3)
+    both_ways(synth.synth_batch(8, 46, 54, config_id=2, first_frame=800), 184, 216, thresh_heat=1e-3, **caps)

@@ -69,6 +69,7 @@ struct tfpd_ctx {
     int k1_pr = 0;                      // TFPD_K1_PR
     int k1_grid = 0;                    // TFPD_K1_GRID: CTAs of the fused map kernel (0 = one per SM)
     int k1_l2_knobs = 2, k1_roles = 3;  // TFPD_K1_L2 / TFPD_K1_ROLES tuning and profiling knobs
+    int k1_early_out = 1;               // minimal mode: skip low-res row groups that cannot reach the heat threshold
     unsigned long long *d_k1_times = nullptr;   // TFPD_K1_TIMES=1: per-CTA timestamps of the last K1 launch
     bool profiling = false, have_timing = false;
     cudaStream_t last_stream = nullptr;
@@ -641,6 +642,8 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
     } else if (!strcmp(name, "resize_path")) {
         if (value < 0 || value > 3) return fail(ctx, TFPD_ERR_INVALID, "resize_path=%d out of range", value);
         ctx->resize_path = value;
+    } else if (!strcmp(name, "k1_early_out")) {
+        ctx->k1_early_out = value != 0;
     } else if (!strcmp(name, "k1_l2")) {
         if (value < 0 || value > 7) return fail(ctx, TFPD_ERR_INVALID, "k1_l2=%d out of range", value);
         ctx->k1_l2_knobs = value;
@@ -727,6 +730,28 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         p.copy_chunk = (w + p.copy_nchunks - 1) / p.copy_nchunks;
         p.thresh = ctx->cfg.thresh_heat;
         memcpy(p.wp, ctx->wp, sizeof(p.wp));
+        for (int q = 0; q < 2; ++q)
+            for (int t = 0; t < 8; ++t) p.wh[q][t] = make_float2(ctx->wp[2 * q][t], ctx->wp[2 * q + 1][t]);
+        // Early-out bound of minimal mode.  Every polyphase weight is >= 0 and each phase's seven weights sum to
+        // sum_w <= 1 + 1e-6, so a blurred value is at most max(0, largest heat value in its 7x7 low-res window) *
+        // sum_w^2, up to the rounding of 14 FMAs (< 2e-6 relative).  Nothing downstream looks at a pixel unless its
+        // blurred value exceeds thresh * (1 - 4e-5) (peak records and both near-tie tests), and the winner-side
+        // near-tie test compares against neighbours within 2e-5 relative: a window below thresh * (1 - 2e-4) is
+        // provably out of reach of all of them.  Disabled (bound = -inf: never dead) for a non-positive threshold.
+        {
+            double sw = 0.0;
+            bool nonneg = true;                 // the bound needs non-negative weights (true for any Gaussian factor)
+            for (int ph = 0; ph < 4; ++ph) {
+                double a = 0.0;
+                for (int t = 0; t < 7; ++t) {
+                    a += (double)ctx->wp[ph][t];
+                    nonneg = nonneg && ctx->wp[ph][t] >= 0.0f;
+                }
+                sw = a > sw ? a : sw;
+            }
+            const double bound = (double)ctx->cfg.thresh_heat * (1.0 - 2e-4) / (sw * sw);
+            p.dead_bound = (ctx->cfg.thresh_heat > 0.0f && ctx->k1_early_out && nonneg) ? (float)bound : -INFINITY;
+        }
         p.l2_knobs = ctx->k1_l2_knobs;
         p.debug_roles = ctx->k1_roles;
         p.dbg_times = ctx->d_k1_times;

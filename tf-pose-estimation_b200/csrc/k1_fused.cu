@@ -280,6 +280,30 @@ __device__ __forceinline__ void emit_peak(const K1Params &p, int n, int c, int Y
     }
 }
 
+// Packed FP32 (Blackwell): one FFMA2 / FMUL2 issue does two IEEE round-to-nearest FMAs.  ptxas broadcasts a scalar
+// register or constant-bank operand to both halves by itself when both components of a float2 are the same value
+// (SASS `R8.F32` / `UR9.F32` next to `.F32x2.HI_LO`), so no operand has to be duplicated in registers.  Every chain
+// below keeps the t = 0..6 order of the scalar code it replaces: the blurred values are bit-identical to it.
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long ra = *reinterpret_cast<unsigned long long *>(&a), rb = *reinterpret_cast<unsigned long long *>(&b),
+                       rc = *reinterpret_cast<unsigned long long *>(&c), rd;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(rb), "l"(rc));
+    return *reinterpret_cast<float2 *>(&rd);
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+    unsigned long long ra = *reinterpret_cast<unsigned long long *>(&a), rb = *reinterpret_cast<unsigned long long *>(&b), rd;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+    return *reinterpret_cast<float2 *>(&rd);
+}
+__device__ __forceinline__ float2 bcast2(float v) { return make_float2(v, v); }
+// acc |= bit iff a == b, as a compare and a PREDICATED or (2 instructions per bit).  Written `acc |= c ? bit : 0`
+// the compiler materialises the flag with a SEL first (3 per bit); sm_100a has no FSET with an integer result
+// (set.eq.u32.f32 also becomes FSETP + SEL).
+__device__ __forceinline__ uint32_t or_bit_if_eq(uint32_t acc, float a, float b, uint32_t bit) {
+    asm("{\n .reg .pred q;\n setp.eq.f32 q, %1, %2;\n @q or.b32 %0, %0, %3;\n}" : "+r"(acc) : "f"(a), "f"(b), "r"(bit));
+    return acc;
+}
+
 template <int PR, bool DENSE>
 __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int pslot_floats, int c, int lane,
                           unsigned &pgroup, uint32_t &wmask0, uint32_t &wmask1) {
@@ -289,33 +313,37 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
     const float NEG = -__int_as_float(0x7f800000);
     const unsigned FULL = 0xffffffffu;
 
-    int cell[CPL];
-    bool cin[CPL];
+    // lane -> its two low-res cells.  Per-lane border state is kept as VALUES, not predicates: nf is the start value
+    // of a cell's horizontal accumulators (+0 inside the image, -inf outside: the 3x3 max then sees clipped border
+    // windows, estimator.py:335), ownmask the pixels this lane decides.
+    const int cell0 = c0 - 4 + lane * CPL;
+    const bool cin0 = (cell0 >= 0) && (cell0 < w), cin1 = (cell0 + 1 >= 0) && (cell0 + 1 < w);
+    const float2 nf0 = bcast2(cin0 ? 0.0f : NEG), nf1 = bcast2(cin1 ? 0.0f : NEG);
     uint32_t ownmask = 0;
-#pragma unroll
-    for (int k = 0; k < CPL; ++k) {
-        cell[k] = c0 - 4 + lane * CPL + k;
-        cin[k] = (cell[k] >= 0) && (cell[k] < w);
-        if ((cell[k] >= c0) && (cell[k] < c0 + tc)) ownmask |= 0xfu << (4 * k);
-    }
+    if ((cell0 >= c0) && (cell0 < c0 + tc)) ownmask |= 0x0fu;
+    if ((cell0 + 1 >= c0) && (cell0 + 1 < c0 + tc)) ownmask |= 0xf0u;
     const int lx0 = 4 * (lane * CPL - 4);        // slot column of this lane's first pixel
-    const float *Xn = p.X + (size_t)n * h * w * kNetC + c;
-    auto hv = [&](int r, int k) -> float {
-        return (cin[k] && r >= 0 && r < h) ? __ldg(Xn + ((size_t)r * w + cell[k]) * kNetC) : 0.0f;
+    // low-res heat values of both cells in row r (zero outside the image: SAME zero padding, smoother.py:91)
+    const float *Xc = p.X + (size_t)n * h * w * kNetC + c + (ptrdiff_t)cell0 * kNetC;
+    auto hv2 = [&](int r) -> float2 {
+        float2 v = make_float2(0.0f, 0.0f);
+        if (r >= 0 && r < h) {
+            const float *row = Xc + (size_t)r * w * kNetC;
+            if (cin0) v.x = __ldg(row);
+            if (cin1) v.y = __ldg(row + kNetC);
+        }
+        return v;
     };
 
-    // 7-row register window of low-res heat values around the current low-res row iy
-    // (nxt / nxt2 = the next two rows, already in flight: global-load latency under a saturated
-    // write stream is microseconds, one row of lead was measured not to cover it)
-    float win[CPL][7], nxt[CPL], nxt2[CPL];
+    // 7-row register window of low-res heat values around the current low-res row iy, both cells packed
+    // (nxt / nxt2 = the next two rows, already in flight: global-load latency under a saturated write stream is
+    // microseconds, one row of lead was measured not to cover it)
+    float2 win[7], nxt, nxt2;
     int iy = it.iy0 - 1;
 #pragma unroll
-    for (int k = 0; k < CPL; ++k) {
-#pragma unroll
-        for (int t = 0; t < 7; ++t) win[k][t] = hv(iy - 3 + t, k);
-        nxt[k] = hv(iy + 4, k);
-        nxt2[k] = hv(iy + 5, k);
-    }
+    for (int t = 0; t < 7; ++t) win[t] = hv2(iy - 3 + t);
+    nxt = hv2(iy + 4);
+    nxt2 = hv2(iy + 5);
     // NMS state: ga/gb ping-pong hold g of the previous / current row, vm = max(g[Y-2], g[Y-1])
     float ga[NPX], gb[NPX], vm[NPX];
 #pragma unroll
@@ -325,41 +353,47 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
     const float thr_lo = p.thresh * (1.0f - 4e-5f);
     const bool is_part = c < kParts;
 
+    auto slide = [&]() {
+        // slide the low-res window down one row; prefetch two rows ahead
+        ++iy;
+#pragma unroll
+        for (int t = 0; t < 6; ++t) win[t] = win[t + 1];
+        win[6] = nxt;
+        nxt = nxt2;
+        nxt2 = hv2(iy + 5);
+    };
+
     // one output row: g(Y) -> cur ; NMS decision for row Y-1 whose g is in prev.  The phase
     // py = Y & 3 is a compile-time constant (rows are unrolled by 4), so every smoother weight is
-    // an immediate constant-bank operand.
+    // a constant-bank operand.
     auto do_row = [&](auto py_tag, const int Y, float (&cur)[NPX], float (&prev)[NPX]) {
         constexpr int py = decltype(py_tag)::value;
         if (Y >= 0 && Y < H) {
-            // vertical polyphase: gv[cell] = sum_t wp[py][t] * X[iy-3+t, cell, c]
-            float gv[CPL];
+            // vertical polyphase, both cells at once: gv = sum_t wp[py][t] * X[iy-3+t, cell, c]
+            float2 gv = fmul2(win[0], bcast2(p.wp[py][0]));
 #pragma unroll
-            for (int k = 0; k < CPL; ++k) {
-                float a = p.wp[py][0] * win[k][0];
-#pragma unroll
-                for (int t = 1; t < 7; ++t) a = fmaf(p.wp[py][t], win[k][t], a);
-                gv[k] = a;
-            }
+            for (int t = 1; t < 7; ++t) gv = ffma2(win[t], bcast2(p.wp[py][t]), gv);
             // window of gv over cells (own first cell - 3 .. own last cell + 3) via shuffles
             float Wn[CPL + 6];
-#pragma unroll
-            for (int j = 0; j < CPL + 6; ++j) {
-                const int d = j - 3;
-                const int dl = floordiv(d, CPL);
-                const int kk = d - dl * CPL;
-                if (dl == 0) Wn[j] = gv[kk];
-                else if (dl < 0) Wn[j] = __shfl_up_sync(FULL, gv[kk], -dl);
-                else Wn[j] = __shfl_down_sync(FULL, gv[kk], dl);
-            }
-            // horizontal polyphase: g[cell,px] = sum_t wp[px][t] * gv[cell-3+t]
+            Wn[3] = gv.x;
+            Wn[4] = gv.y;
+            Wn[0] = __shfl_up_sync(FULL, gv.y, 2);
+            Wn[1] = __shfl_up_sync(FULL, gv.x, 1);
+            Wn[2] = __shfl_up_sync(FULL, gv.y, 1);
+            Wn[5] = __shfl_down_sync(FULL, gv.x, 1);
+            Wn[6] = __shfl_down_sync(FULL, gv.y, 1);
+            Wn[7] = __shfl_down_sync(FULL, gv.x, 2);
+            // horizontal polyphase, two x phases at once: g[cell, 2q..2q+1] = sum_t wh[q][t] * gv[cell-3+t]; the
+            // accumulator starts from nf (+0 / -inf), which is where a cell outside the image is excluded
 #pragma unroll
             for (int k = 0; k < CPL; ++k) {
 #pragma unroll
-                for (int px = 0; px < 4; ++px) {
-                    float a = p.wp[px][0] * Wn[k];
+                for (int q = 0; q < 2; ++q) {
+                    float2 a = ffma2(bcast2(Wn[k]), p.wh[q][0], k == 0 ? nf0 : nf1);
 #pragma unroll
-                    for (int t = 1; t < 7; ++t) a = fmaf(p.wp[px][t], Wn[k + t], a);
-                    cur[k * 4 + px] = cin[k] ? a : NEG;
+                    for (int t = 1; t < 7; ++t) a = ffma2(bcast2(Wn[k + t]), p.wh[q][t], a);
+                    cur[k * 4 + 2 * q] = a.x;
+                    cur[k * 4 + 2 * q + 1] = a.y;
                 }
             }
         } else {
@@ -375,9 +409,9 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
         // g > thr_lo), so its whole NMS step is skipped -- exact, and most rows of most channels are like that.
         bool row_live = true;
         if (!DENSE) {
-            float hp = prev[0];
-#pragma unroll
-            for (int i = 1; i < NPX; ++i) hp = fmaxf(hp, prev[i]);
+            float hp = fmaxf(fmaxf(prev[0], prev[1]), prev[2]);
+            hp = fmaxf(fmaxf(hp, prev[3]), prev[4]);
+            hp = fmaxf(fmaxf(hp, prev[5]), fmaxf(prev[6], prev[7]));
             row_live = __any_sync(FULL, hp > thr_lo);
         }
         if (j >= 0 && j < 4 * it.nrows && row_live) {  // warp-uniform
@@ -391,7 +425,7 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
 #pragma unroll
             for (int i = 0; i < NPX; ++i) {
                 const float m = fmaxf(fmaxf(v[i], v[i + 1]), v[i + 2]);
-                pm |= (prev[i] == m) ? (1u << i) : 0u;
+                pm = or_bit_if_eq(pm, prev[i], m, 1u << i);
                 hot = fmaxf(hot, prev[i]);
             }
             pm &= ownmask;
@@ -434,7 +468,6 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
                 const int i = __ffs(mk) - 1;
                 mk &= mk - 1;
                 float gc = 0.f, nb = 0.f, hc = 0.f;
-                int cx = 0;
 #pragma unroll
                 for (int q = 0; q < NPX; ++q)
                     if (i == q) {
@@ -443,10 +476,10 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
                         nb = fmaxf(fmaxf(v[q], v[q + 2]), cur[q]);
                         // heat score of row Yc: its low-res row is the window centre, or the one above it
                         // when Y just crossed into the next low-res row
-                        hc = (py == 0) ? win[q >> 2][2] : win[q >> 2][3];
-                        cx = cell[q >> 2];
+                        const float2 hw = (py == 0) ? win[2] : win[3];
+                        hc = (q >> 2) ? hw.y : hw.x;
                     }
-                emit_peak(p, n, c, Yc, 4 * cx + (i & 3), gc, hc, nb,
+                emit_peak(p, n, c, Yc, 4 * (cell0 + (i >> 2)) + (i & 3), gc, hc, nb,
                           DENSE ? slot + ((size_t)jr * pitch_px + lx0 + i) * kHeatC + c : nullptr);
             }
             if (DENSE && (jr == PR - 1 || j == 4 * it.nrows - 1)) {
@@ -472,18 +505,7 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
         // vm for the next row = max(g[Y-1], g[Y])
 #pragma unroll
         for (int i = 0; i < NPX; ++i) vm[i] = fmaxf(prev[i], cur[i]);
-        if (py == 3) {
-            // slide the low-res window down one row; prefetch two rows ahead
-            ++iy;
-#pragma unroll
-            for (int k = 0; k < CPL; ++k) {
-#pragma unroll
-                for (int t = 0; t < 6; ++t) win[k][t] = win[k][t + 1];
-                win[k][6] = nxt[k];
-                nxt[k] = nxt2[k];
-                nxt2[k] = hv(iy + 5, k);
-            }
-        }
+        if (py == 3) slide();
     };
 
     // rows Ys .. Ys + 4*nrows + 1; Ys = 4*iy0 - 1 has phase 3, so a group of four rows has the
@@ -496,6 +518,25 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
     int Yr = Ys;
 #pragma unroll 1
     for (int g4 = 0; g4 < it.nrows; ++g4, Yr += 4) {
+        if (!DENSE) {
+            // Early-out (minimal mode only; dense mode must write every row of the peaks tensor).  This group
+            // computes g of rows Yr .. Yr+3 and decides rows Yr-1 .. Yr+2; all of them read low-res rows
+            // iy-3 .. iy+4 = win[0..6] and nxt, cells own-3 .. own+3 -- a subset of the cells this warp holds.
+            // If no lane holds a heat value above dead_bound there, no g of those rows can come within reach of
+            // the heat threshold (bound derived in api.cu): no peak record and no near-tie count can arise, and
+            // for the rows decided later these rows are only ever the losing neighbour.  The group is skipped with
+            // its g taken as -inf; exact.  (Ties with the group before: its last rows were decided against -inf
+            // instead of a value below the bound, which cannot change a decision about a pixel above thr_lo.)
+            float wm_ = fmaxf(fmaxf(win[0].x, win[0].y), fmaxf(nxt.x, nxt.y));
+#pragma unroll
+            for (int t = 1; t < 7; ++t) wm_ = fmaxf(wm_, fmaxf(win[t].x, win[t].y));
+            if (!__any_sync(FULL, wm_ > p.dead_bound)) {
+#pragma unroll
+                for (int i = 0; i < NPX; ++i) ga[i] = gb[i] = vm[i] = NEG;
+                slide();
+                continue;
+            }
+        }
         do_row(P3(), Yr, ga, gb);
         do_row(P0(), Yr + 1, gb, ga);
         do_row(P1(), Yr + 2, ga, gb);

@@ -99,6 +99,10 @@ struct K1Params {
     int copy_chunk, copy_nchunks;                          // copy role: <= 32-cell row chunks (one lane per cell)
     float thresh;
     float wp[4][8];                     // polyphase smoother weights: phase p, low-res tap t (cell offset t-3)
+    float2 wh[2][8];                    // the same weights paired over two adjacent x phases: wh[q][t] = {wp[2q][t], wp[2q+1][t]}
+                                        // (packed operand of the horizontal pass's FFMA2)
+    float dead_bound;                   // minimal mode: a low-res window whose largest heat value is below this cannot
+                                        // produce a blurred value near the heat threshold (k1_fused.cu, early-out)
     int l2_knobs;                       // bit0 up-front L2 prefetch of X, bit1 evict_first stores, bit2 evict_last prefetch
     int debug_roles;                    // bit0 blur role, bit1 copy role (3 = normal; tuning/profiling only)
     int force_pr;
