@@ -449,3 +449,27 @@ def test_objbuild_extension_builds_the_same_objects_as_the_python_loop():
         ob.build_humans(BodyPart, Human, table[:1].tobytes(), counts.tobytes(), MH, 368, 656)    # table too small
     with pytest.raises(TypeError):
         ob.build_humans(int, Human, table.tobytes(), counts.tobytes(), MH, 368, 656)             # no such slots
+
+
+def test_bench_config_table_matches_the_baseline_configs():
+    """bench.py's workload table against BASELINE.json / SURVEY.md 8(d): shapes, frames per GPU at 1/2/4/8 GPUs
+    (C3 is STRONG-scaled: 128 frames in total; C2/C4/C5 keep 64 per GPU, C5 = 512 over 8), and the algorithmic
+    bytes per frame that roofline.achieved is computed from."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    C = bench.CONFIGS
+    assert sorted(C) == ["c2", "c3", "c4", "c5"]
+    assert [(C[k]["h"], C[k]["w"]) for k in ("c2", "c3", "c4", "c5")] == [(46, 54), (46, 82), (46, 54), (92, 164)]
+    assert [bench.frames_per_rank(C["c3"], n) for n in (1, 2, 4, 8)] == [128, 64, 32, 16]
+    assert bench.scaling_of(C["c3"]) == "strong"
+    for k in ("c2", "c4", "c5"):
+        assert [bench.frames_per_rank(C[k], n) for n in (1, 2, 4, 8)] == [64] * 4 and bench.scaling_of(C[k]) == "weak"
+    assert bench.frames_per_rank(C["c5"], 8) * 8 == 512
+    assert bench.frames_per_rank(C["c2"], 4, 16) == 16                      # --batch override
+    assert bench.dense_bytes_per_frame(46, 54) == 12648528                   # SURVEY.md 8(d)
+    assert bench.dense_bytes_per_frame(46, 82) == 19207024
+    assert bench.dense_bytes_per_frame(92, 164) == 76828096
+    assert abs(bench.polyphase_flops_per_frame(46, 54) / 13.2e6 - 1) < 0.01   # "polyphase: ~13.2 MFLOP" per frame
+    assert C["c4"]["people"] == 30 and C["c4"]["caps"]["max_peaks"] == 4096
