@@ -27,7 +27,7 @@ stats = {}
 for name, frames in (("c2", [(46, 54, 2, None, i) for i in range(12)]), ("c4", [(46, 54, 4, 30, i) for i in range(4)]),
                      ("c3", [(46, 82, 3, None, i) for i in range(4)])):
     tot = d1 = d2 = 0
-    worst = 0.0
+    worst = worst1 = 0.0
     for (h, w, cfg, people, fr) in frames:
         x = synth.synth_frame(h, w, synth.frame_seed(cfg, fr), people=people)
         H, W = 4 * h, 4 * w
@@ -52,8 +52,11 @@ for name, frames in (("c2", [(46, 54, 2, None, i) for i in range(12)]), ("c4", [
                 y0, y1 = max(0, 4 * iy - 2), min(H, 4 * iy + 3)
                 gg = g[y0:y1, 4 * c0:4 * c1, :].max(axis=(0, 1))
                 tot += 19; d1 += int(dead1.sum()); d2 += int(dead2.sum())
+                if dead1.any():
+                    worst1 = max(worst1, float((gg[dead1] / thr_lo).max()))
                 if dead2.any():
                     worst = max(worst, float((gg[dead2] / thr_lo).max()))
                     assert (gg[dead2] < thr_lo * np.float32(1 - 2e-5)).all(), (cfg, fr, iy, ch)
-    print("%s: groups %d  dead (window max) %.1f %%  dead (row-weighted) %.1f %%  largest g in a dead group %.3f x thr_lo"
-          % (name, tot, 100.0 * d1 / tot, 100.0 * d2 / tot, worst))
+    print("%s: units %d | ADOPTED rule (window max): skipped %.1f %%, largest blurred value in a skipped unit %.3f x thr_lo | "
+          "row-weighted rule (not adopted): skipped %.1f %%, largest %.3f x thr_lo"
+          % (name, tot, 100.0 * d1 / tot, worst1, 100.0 * d2 / tot, worst))
