@@ -51,8 +51,9 @@ CONFIGS = {
     "c3": {"id": 3, "h": 46, "w": 82, "people": None, "total": 128, "caps": {},
            "name": "CMU 656x368 decode, 128 frames sharded by image (%d per GPU), 46x82x57 -> 184x328 (upsample x4), "
                    "dense maps produced, humans to host"},
-    "c4": {"id": 4, "h": 46, "w": 54, "people": 30, "batch": 64,
-           "caps": {"max_peaks": 4096, "max_cands": 8192, "max_humans": 128},
+    # ~30 people: <= 385 peaks, 1221 candidates, 41 subset rows, 25 humans per frame (oracle, 12 frames): the default
+    # table capacities (2048 / 4096 / 512 / 64) hold them with a 3-5x margin; an overflow would fail the fetch loudly
+    "c4": {"id": 4, "h": 46, "w": 54, "people": 30, "batch": 64, "caps": {},
            "name": "crowded scene (~30 people per frame) on the mobilenet_thin shape, batch %d per GPU, 46x54x57 -> "
                    "184x216, dense maps produced, humans to host"},
     "c5": {"id": 5, "h": 92, "w": 164, "people": None, "batch": 64, "caps": {},

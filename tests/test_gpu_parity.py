@@ -374,3 +374,34 @@ def test_minimal_mode_early_out_is_exact(cuda):
     both_ways(x, 80, 120, **caps)
     r = both_ways(synth.synth_batch(8, 46, 54, config_id=2, first_frame=800), 184, 216, thresh_heat=0.3)
     both_ways(synth.synth_batch(8, 46, 54, config_id=2, first_frame=800), 184, 216, thresh_heat=1e-3, **caps)
+
+
+def test_minimal_mode_work_queue_band_sizes_agree(cuda):
+    """Minimal mode hands out (frame, column chunk, band of low-res rows) items dynamically and never computes the
+    background channel ("k1_min_band", include/tfpose_decode.h).  Whatever the band size -- one row, a size that
+    does not divide the height, the whole frame, more than the frame -- tables, peak lists and frame info must equal
+    those of a dense-mode decode of the same batch (which still runs the static row spans and all 19 channels),
+    on a narrow map, a two-chunk map and a batch larger than the grid's CTA count would need."""
+    import torch
+    from helpers import table_tuples
+    for (n, h, w, cfg) in ((5, 46, 54, 2), (3, 46, 82, 3), (2, 7, 8, 2), (1, 1, 1, 2)):
+        x = synth.synth_batch(n, h, w, config_id=cfg, first_frame=900)
+        if h < 10:
+            rng = np.random.default_rng(h * 31 + w)
+            x = rng.random((n, h, w, 57), dtype=np.float32)
+            x[..., 19:] = x[..., 19:] * 2 - 1
+        H, W = 4 * h, 4 * w
+        xd = torch.from_numpy(x).cuda()
+        caps = dict(max_peaks=4096, max_cands=8192, max_rows=1024, max_humans=512)
+        dec = tp.PoseDecoder(max_batch=n, max_upsample=(H, W), **caps)
+        want = dec.decode(xd, (H, W), dense=_dense(torch, n, H, W))
+        want_pk = [dec.peaks(i) for i in range(n)]
+        for band in (1, 3, 4, 5, 46, 200):
+            dec.set_option("k1_min_band", band)
+            got = dec.decode(xd, (H, W))
+            assert np.array_equal(got.info, want.info), (h, w, band)
+            for i in range(n):
+                assert table_tuples(got, i) == table_tuples(want, i), (h, w, band, i)
+                pk = dec.peaks(i)
+                assert all(np.array_equal(pk[k], want_pk[i][k]) for k in pk), (h, w, band, i)
+        dec.close()

@@ -70,6 +70,7 @@ struct tfpd_ctx {
     int k1_grid = 0;                    // TFPD_K1_GRID: CTAs of the fused map kernel (0 = one per SM)
     int k1_l2_knobs = 2, k1_roles = 3;  // TFPD_K1_L2 / TFPD_K1_ROLES tuning and profiling knobs
     int k1_early_out = 1;               // minimal mode: skip low-res row groups that cannot reach the heat threshold
+    int k1_min_band = 4;                // minimal mode: low-res rows per work item of the map kernel's dynamic queue
     unsigned long long *d_k1_times = nullptr;   // TFPD_K1_TIMES=1: per-CTA timestamps of the last K1 launch
     bool profiling = false, have_timing = false;
     cudaStream_t last_stream = nullptr;
@@ -644,6 +645,9 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
         ctx->resize_path = value;
     } else if (!strcmp(name, "k1_early_out")) {
         ctx->k1_early_out = value != 0;
+    } else if (!strcmp(name, "k1_min_band")) {
+        if (value < 1 || value > 8191) return fail(ctx, TFPD_ERR_INVALID, "k1_min_band=%d out of range", value);
+        ctx->k1_min_band = value;
     } else if (!strcmp(name, "k1_l2")) {
         if (value < 0 || value > 7) return fail(ctx, TFPD_ERR_INVALID, "k1_l2=%d out of range", value);
         ctx->k1_l2_knobs = value;
@@ -729,6 +733,7 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         p.copy_nchunks = (w + copy_cells - 1) / copy_cells;  // <= 32 cells (29 KB staged) per copy item
         p.copy_chunk = (w + p.copy_nchunks - 1) / p.copy_nchunks;
         p.thresh = ctx->cfg.thresh_heat;
+        p.min_band = ctx->k1_min_band;
         memcpy(p.wp, ctx->wp, sizeof(p.wp));
         for (int q = 0; q < 2; ++q)
             for (int t = 0; t < 8; ++t) p.wh[q][t] = make_float2(ctx->wp[2 * q][t], ctx->wp[2 * q + 1][t]);

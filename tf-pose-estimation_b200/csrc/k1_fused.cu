@@ -567,6 +567,84 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
         p.dbg_times[blockIdx.x * 4 + 0] = global_ns();
         p.dbg_times[blockIdx.x * 4 + 3] = smid;
     }
+    if (!DENSE) {
+        // ---- minimal mode: nothing dense is written, the kernel is the blur role alone ----
+        // Every warp is an independent worker (there are no shared slots and no barriers in this mode), and two
+        // things follow from "only peak records and near-tie counts leave the kernel":
+        //  * channel 18 (the background heat map) yields neither (pafprocess.cpp:24 scans parts 0..17): it is not
+        //    computed at all.  Its heat is ~1 everywhere, so its warp could never take the early-out, and a CTA
+        //    finishes with its slowest warp: with a static row span per CTA the skipped row groups of the other 18
+        //    warps saved next to nothing (measured: 68.4 -> 65.6 us).
+        //  * the live / skipped share differs between rows and channels, so the work is handed out dynamically.
+        // Two-level queue: a CTA-level item is one band of `min_band` low-res rows of one (frame, column chunk),
+        // taken from the grid-wide counter; the 19 warps of the CTA take its 18 channels one by one from a
+        // shared-memory word {grid item, next channel} updated by compare-and-swap.  Whoever finds the item used up
+        // marks the word "refilling", fetches the next grid item and stores it; the others retry meanwhile; an
+        // empty grid queue leaves a sticky "done" mark.  Warps of one CTA therefore work on the same cells at about
+        // the same time (the 19 channels of a cell share three 32-byte sectors: L1 locality as in the dense
+        // kernel), without ever synchronising and with nothing that could be overwritten before it is read.
+        if (!(p.debug_roles & 1)) return;
+        constexpr unsigned kRefilling = 255u, kDone = 254u;
+        __shared__ unsigned long long s_state;              // grid item << 8 | next channel (18 = used up)
+        if (tid == 0) s_state = (unsigned long long)kParts; // item 0 "used up": the first warp to come refills
+        __syncthreads();
+        const int band = p.min_band;
+        const int nbands = (p.h + band - 1) / band;
+        const long long total = (long long)p.N * p.nchunks * nbands;
+        int *queue = &p.counters[0].k1_queue;
+        unsigned pgroup = 0;
+        uint32_t wmask0 = 0u, wmask1 = 0u;
+        for (;;) {
+            long long g = -1;
+            int ch = 0;
+            if (lane == 0) {
+                for (;;) {
+                    const unsigned long long old = *reinterpret_cast<volatile unsigned long long *>(&s_state);
+                    const unsigned c = (unsigned)(old & 0xffu);
+                    if (c == kDone) break;                                   // g stays -1: leave
+                    if (c == kRefilling) {
+                        __nanosleep(40);
+                        continue;
+                    }
+                    if (c < (unsigned)kParts) {                              // take channel c of the current item
+                        if (atomicCAS(&s_state, old, old + 1ull) == old) {
+                            g = (long long)(old >> 8);
+                            ch = (int)c;
+                            break;
+                        }
+                        continue;
+                    }
+                    // used up: become the refiller (one at a time)
+                    if (atomicCAS(&s_state, old, (old & ~0xffull) | kRefilling) != old) continue;
+                    const long long gn = atomicAdd(queue, 1);
+                    if (gn >= total) {
+                        *reinterpret_cast<volatile unsigned long long *>(&s_state) = (unsigned long long)kDone;
+                        break;
+                    }
+                    g = gn;
+                    ch = 0;
+                    __threadfence_block();
+                    *reinterpret_cast<volatile unsigned long long *>(&s_state) = ((unsigned long long)gn << 8) | 1ull;
+                    break;
+                }
+            }
+            g = __shfl_sync(0xffffffffu, g, 0);
+            ch = __shfl_sync(0xffffffffu, ch, 0);
+            if (g < 0) break;                   // the grid queue is empty
+            const long long q = g / nbands;     // q = n * nchunks + chunk
+            const int b = (int)(g - q * nbands);
+            Item it;
+            it.iy0 = b * band;
+            it.nrows = min(band, p.h - it.iy0);
+            it.n = (int)(q / p.nchunks);
+            const int chunk = (int)(q - (long long)it.n * p.nchunks);
+            it.c0 = chunk * p.chunk_cells;
+            it.tc = min(p.chunk_cells, p.w - it.c0);
+            blur_role<PR, false>(p, it, nullptr, 0, ch, lane, pgroup, wmask0, wmask1);
+        }
+        if (p.dbg_times && lane == 0 && warp == 0) p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
+        return;
+    }
     if (warp < kBlurWarps) {
         if (!(p.debug_roles & 1)) return;
         if (DENSE) {

@@ -12,6 +12,8 @@
 //   4. the filter (:185-189) and the getter view (:194-214) -> tfpd_human records.
 #include <type_traits>
 
+#include <cstdlib>
+
 #include "tfpd_internal.cuh"
 
 namespace tfpd {
@@ -34,7 +36,12 @@ constexpr int kRegRowsMax = 128;            // subset rows held in registers (4 
 constexpr int kK3Threads = 640;             // 20 warps: 19 greedy walkers + sort helpers
 constexpr int kBitmapWords = kMaxPeaksHard / 32;   // 128
 
-__global__ void __launch_bounds__(kK3Threads) k_assemble(Workspace ws, Thresholds th) {
+// MINB = CTAs per SM the register allocation allows: 1 -> 78 registers, 2 -> 48 registers (no spills either way).
+// The kernel is a latency-bound chain per frame (issue slots ~27 % busy with one CTA per SM), so two co-resident
+// frames halve the SM-time of a batch whenever their shared memory fits -- which matters when the kernel only gets
+// the SMs a reduced map-kernel grid leaves free (bench.py's pipelined region) and on crowded frames.
+template <int MINB>
+__global__ void __launch_bounds__(kK3Threads, MINB) k_assemble(Workspace ws, Thresholds th) {
     extern __shared__ __align__(16) unsigned char sm_raw[];
     unsigned long long *keys = reinterpret_cast<unsigned long long *>(sm_raw);            // [max_cands]
     float *rows = reinterpret_cast<float *>(keys + ws.max_cands);                        // [20][max_rows] SoA
@@ -655,15 +662,21 @@ size_t assemble_smem_bytes(const Workspace &ws) {
 
 int launch_assemble(const Workspace &ws, int N, const Thresholds &th, cudaStream_t s) {
     size_t smem = assemble_smem_bytes(ws);
-    static size_t attr_smem[64] = {};                  // per device: function attributes do not travel between devices
+    static size_t attr_smem[64][2] = {};               // per device and variant: function attributes do not travel between devices
     int dev = 0;
     cudaGetDevice(&dev);
-    if (smem > 48 * 1024 && smem > attr_smem[dev & 63]) {
-        if (cudaFuncSetAttribute(k_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
-            return -1;
-        attr_smem[dev & 63] = smem;
+    // two CTAs per SM when two copies of the shared memory (dynamic + ~2 KB static + 1 KB the hardware reserves per
+    // CTA) fit the SM's 228 KB; TFPD_K3_MINB=1 forces the one-per-SM build (A/B timing)
+    static const int forced = getenv("TFPD_K3_MINB") ? atoi(getenv("TFPD_K3_MINB")) : 0;
+    const bool two = forced ? forced >= 2 : 2 * (smem + 3 * 1024) <= (size_t)228 * 1024;
+    const void *fn = two ? (const void *)k_assemble<2> : (const void *)k_assemble<1>;
+    if (smem > 48 * 1024 && smem > attr_smem[dev & 63][two]) {
+        if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -1;
+        cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        attr_smem[dev & 63][two] = smem;
     }
-    k_assemble<<<N, kK3Threads, smem, s>>>(ws, th);
+    if (two) k_assemble<2><<<N, kK3Threads, smem, s>>>(ws, th);
+    else k_assemble<1><<<N, kK3Threads, smem, s>>>(ws, th);
     return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

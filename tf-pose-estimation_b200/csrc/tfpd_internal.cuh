@@ -101,6 +101,7 @@ struct K1Params {
     float wp[4][8];                     // polyphase smoother weights: phase p, low-res tap t (cell offset t-3)
     float2 wh[2][8];                    // the same weights paired over two adjacent x phases: wh[q][t] = {wp[2q][t], wp[2q+1][t]}
                                         // (packed operand of the horizontal pass's FFMA2)
+    int min_band;                       // minimal mode: low-res rows per work item of the dynamic queue
     float dead_bound;                   // minimal mode: a low-res window whose largest heat value is below this cannot
                                         // produce a blurred value near the heat threshold (k1_fused.cu, early-out)
     int l2_knobs;                       // bit0 up-front L2 prefetch of X, bit1 evict_first stores, bit2 evict_last prefetch

@@ -50,6 +50,18 @@ for name, h, w, cfg, people, caps in (("c2", 46, 54, 2, None, {}), ("c4", 46, 54
             rec["%%s_ctas%%d" %% (mode, ctas or 148)] = {"k1_us": float(np.mean(t)) * 1e3, "k1_us_min": float(np.min(t)) * 1e3, "humans": humans}
             if mode == "minimal_no_early_out":
                 dec.set_option("k1_early_out", 1)
+    dec.set_option("k1_ctas", 0)
+    for band in (2, 4, 8, 16):
+        try:
+            dec.set_option("k1_min_band", band)
+        except Exception:
+            break
+        t = []
+        for i in range(13):
+            dec.decode(xs[i %% 4], (H, W))
+            if i >= 3:
+                t.append(dec.stage_ms()[0])
+        rec["minimal_band%%d_ctas148" %% band] = {"k1_us": float(np.mean(t)) * 1e3, "k1_us_min": float(np.min(t)) * 1e3, "humans": 0}
     rec["dense_gbs_ctas128"] = 4 * (57 * h * w + 76 * H * W) * B / (rec["dense_ctas128"]["k1_us"] * 1e-6) / 1e9
     out[name] = rec
     dec.close()
@@ -72,7 +84,8 @@ def main():
             continue
         results[lib] = json.loads(line[0][7:])
     for cfg in ("c2", "c4", "c3", "c5"):
-        for key in ("dense_ctas128", "dense_ctas148", "minimal_ctas128", "minimal_ctas148", "minimal_no_early_out_ctas148"):
+        for key in ("dense_ctas128", "dense_ctas148", "minimal_ctas128", "minimal_ctas148", "minimal_no_early_out_ctas148",
+                    "minimal_band2_ctas148", "minimal_band4_ctas148", "minimal_band8_ctas148", "minimal_band16_ctas148"):
             row = []
             for lib in libs:
                 r = results.get(lib, {}).get(cfg, {}).get(key)
