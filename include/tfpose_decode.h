@@ -225,6 +225,10 @@ TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, s
  *   "k1_l2"        bit 1: evict-first stores (default 2); bit 0 is reserved (a bulk L2 prefetch of the input at
  *                  kernel start measured slower and was taken out again).
  *   "k2_blocks"    CTAs of the limb-scoring kernel per frame; 0 = automatic (about 6 CTAs per SM over the batch).
+ *   "k2_prefilter" 1 (default): the limb-scoring kernel scores the first 10 - thresh_vector_cnt1 samples of a candidate
+ *                  pair (4 with the reference's constants) in its per-pair set-up and drops the pair when none of them
+ *                  exceeds thresh_vector_score: it could no longer reach "more than thresh_vector_cnt1 of 10"
+ *                  (pafprocess.cpp:80,85).  Exact: same candidates, same scores; 0 scores every pair in full.
  *   "fuse_sort"    1 (default): the limb-scoring kernel ranks the unordered peak records itself (every CTA of a frame
  *                  counts smaller keys in shared memory, CTA 0 writes the table); 0: a sort kernel of its own runs in
  *                  front of it.  Same tables.

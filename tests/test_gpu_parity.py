@@ -405,3 +405,41 @@ def test_minimal_mode_work_queue_band_sizes_agree(cuda):
                 pk = dec.peaks(i)
                 assert all(np.array_equal(pk[k], want_pk[i][k]) for k in pk), (h, w, band, i)
         dec.close()
+
+
+def test_limb_scoring_early_rejection_is_exact(cuda, oracle):
+    """K2 drops a pair after its first 10 - thresh_vector_cnt1 samples when none of them passes ("k2_prefilter").
+    Candidates, connections, humans and frame info (n_cands included) must be identical with the option off -- on
+    sparse and crowded frames, on random maps (every pair has some passing samples), with other vector thresholds
+    (cnt1 = 4: six leading samples; 9: one; 3 and 10: the rejection is off or nothing can qualify) -- and equal to
+    the oracle's with the reference's constants."""
+    import torch
+    from helpers import table_tuples
+    caps = dict(max_peaks=4096, max_cands=16384, max_rows=1024, max_humans=512)
+    rng = np.random.default_rng(77)
+    xr = rng.random((2, 9, 13, 57), dtype=np.float32)
+    xr[..., 19:] = xr[..., 19:] * 2 - 1
+    batches = [(synth.synth_batch(6, 46, 54, config_id=2, first_frame=1000), 4),
+               (synth.synth_batch(2, 46, 54, config_id=4, people=30, first_frame=30), 4), (xr, 4)]
+    for x, f in batches:
+        H, W = f * x.shape[1], f * x.shape[2]
+        xd = torch.from_numpy(x).cuda()
+        for cnt1, vs in ((6, 0.05), (4, 0.05), (9, 0.02), (3, 0.05), (10, 0.05), (6, 0.3)):
+            res = []
+            for pre in (1, 0):
+                dec = tp.PoseDecoder(max_batch=len(x), max_upsample=(H, W), thresh_vector_cnt1=cnt1,
+                                     thresh_vector_score=vs, **caps)
+                dec.set_option("k2_prefilter", pre)
+                r = dec.decode(xd, (H, W))
+                res.append((r, [dec.connections(i) for i in range(len(x))]))
+                dec.close()
+            (ra, ca), (rb, cb) = res
+            assert np.array_equal(ra.info, rb.info), (cnt1, vs)
+            for i in range(len(x)):
+                assert table_tuples(ra, i) == table_tuples(rb, i), (cnt1, vs, i)
+                assert all(np.array_equal(ca[i][k], cb[i][k]) for k in ca[i]), (cnt1, vs, i)
+            if cnt1 == 10:
+                assert int(ra.info["n_cands"].sum()) == 0
+    # and against the oracle with the reference's constants (check_frames runs with the rejection on by default)
+    e, f_ = check_frames(cuda, oracle, batches[1][0], 4, max_peaks=4096, max_cands=8192, max_humans=128)
+    assert e + f_ == 2

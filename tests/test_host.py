@@ -380,7 +380,8 @@ def test_every_option_the_library_accepts_is_documented():
     body = body[:body.index("\n}\n")]
     accepted = set(re.findall(r'strcmp\(name, "([a-z0-9_]+)"\)', body))
     header = open(os.path.join(root, "include", "tfpose_decode.h")).read()
-    doc = header[header.index("tfpd_set_option") - 4000:header.index("tfpd_set_option")]
+    # the comment block in front of the declaration, from its first line (not a fixed distance: it grows with the options)
+    doc = header[header.index("/* Tuning options, by name"):header.index("TFPD_API int tfpd_set_option")]
     documented = set(re.findall(r'\*\s+"([a-z0-9_]+)"\s', doc))
     assert accepted and accepted == documented, (sorted(accepted - documented), sorted(documented - accepted))
     integ = open(os.path.join(root, "INTEGRATION.md")).read()

@@ -359,6 +359,7 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     w.max_humans = cfg->max_humans;
     w.k3_reg_rows = 128;
     w.k2_fused_sort = 1;
+    w.k2_prefilter = 1;
     w.k2_blocks_per_frame = 0;
     if (const char *e = getenv("TFPD_K2_BPF")) w.k2_blocks_per_frame = atoi(e);
     w.k3_warp_sort_max = 1024;
@@ -630,6 +631,8 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
         ctx->ws.k2_blocks_per_frame = value;
     } else if (!strcmp(name, "fuse_sort")) {
         ctx->ws.k2_fused_sort = value != 0;
+    } else if (!strcmp(name, "k2_prefilter")) {
+        ctx->ws.k2_prefilter = value != 0;
     } else if (!strcmp(name, "graph")) {
         ctx->use_graph = value != 0;
     } else if (!strcmp(name, "k1_turnstile")) {

@@ -175,6 +175,10 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
     // that spreading them over all warps shortens the serial chain of sub-steps
     int per = (total + warps_total - 1) / warps_total;
     per = min(kPairsPerPass, max(kPairsPerWarp, (per + kPairsPerWarp - 1) / kPairsPerWarp * kPairsPerWarp));
+    // leading samples the setup phase scores to reject a pair early: the fewest after which "no hit so far" proves that
+    // the count cannot exceed vector_cnt1 (4 for the reference's cnt1 = 6); off for settings where that would be more
+    // than 6 samples or none
+    const int prefilter = (ws.k2_prefilter && th.vector_cnt1 >= 4 && th.vector_cnt1 < kStepPaf) ? kStepPaf - th.vector_cnt1 : 0;
     int limb_hint = 0;                          // pairs are visited in increasing order: resume the limb search
     for (int base = (blockIdx.x * (kK2Threads / 32) + warp) * per; base < total; base += warps_total * per) {
         // ---- setup (lane = pair) ----
@@ -204,20 +208,47 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
             }
             xy1 = (x1 & 0xffff) | (y1 << 16);
             lab = (limb << 24) | (a << 12) | b;
-            meta = c_limb_chan[limb][0] | (ok ? 0x100 : 0);
+            bool keep = ok;
+            if (ok && prefilter > 0) {
+                // Early rejection, exact.  A pair becomes a candidate only if MORE than vector_cnt1 of its
+                // STEP_PAF = 10 samples score above vector_score (pafprocess.cpp:80,85).  Samples 0 .. prefilter-1
+                // are scored here by the pair's own lane with the statements of the scoring phase below (same
+                // rounding, same loads, hence the same pass/fail per sample); when even a pass on every remaining
+                // sample could not lift the count above vector_cnt1 the pair is dropped -- it could only have been
+                // rejected later.  With the reference's constants (cnt1 = 6) that is: none of the first four samples
+                // passes, which holds for the great majority of pairs that are not limbs.  Survivors go through the
+                // unchanged 10-sample scoring, so accepted candidates and their scores are untouched.
+                const int chan0 = c_limb_chan[limb][0];
+                int hits0 = 0;
+                for (int k = 0; k < prefilter; ++k) {
+                    const float fx = __fadd_rn((float)x1, __fmul_rn((float)k, stepx));
+                    const float fy = __fadd_rn((float)y1, __fmul_rn((float)k, stepy));
+                    const int lx = (int)((double)fx + 0.5);
+                    const int ly = (int)((double)fy + 0.5);
+                    const float *pp = paf + ((size_t)(ly >> src.shift) * src.cols + (lx >> src.shift)) * src.chan +
+                                      src.chan_off + chan0;
+                    const float sk = __fadd_rn(__fmul_rn(vx, __ldg(pp)), __fmul_rn(vy, __ldg(pp + 1)));
+                    hits0 += (sk > th.vector_score) ? 1 : 0;
+                }
+                keep = hits0 + (kStepPaf - prefilter) > th.vector_cnt1;
+            }
+            meta = c_limb_chan[limb][0] | (keep ? 0x100 : 0);
         }
-        const int npass = min(per, total - base);                                         // warp-uniform
+        // the scoring phase walks the SURVIVORS only: sub-step t, slot s takes the (3t+s)-th lane whose pair is kept
+        const unsigned alive = __ballot_sync(FULL, pvalid && (meta & 0x100));
+        const int npass = __popc(alive);                                                  // warp-uniform
         const int nsub = (npass + kPairsPerWarp - 1) / kPairsPerWarp;
 
         // ---- scoring (10 lanes per pair) ----
         auto fetch = [&](int t, float &o_vx, float &o_vy, float &o_pvx, float &o_pvy, bool &o_ok) {
-            const int owner = min(kPairsPerWarp * t + slot, 31);
+            const int rank = kPairsPerWarp * t + slot;
+            const int owner = (slot < kPairsPerWarp && rank < npass) ? (int)__fns(alive, 0, rank + 1) : 0;
             const int g_xy = __shfl_sync(FULL, xy1, owner);
             const int g_meta = __shfl_sync(FULL, meta, owner);
             const float g_sx = __shfl_sync(FULL, stepx, owner), g_sy = __shfl_sync(FULL, stepy, owner);
             o_vx = __shfl_sync(FULL, vx, owner);
             o_vy = __shfl_sync(FULL, vy, owner);
-            o_ok = (slot < kPairsPerWarp) && (kPairsPerWarp * t + slot < npass) && (g_meta & 0x100);
+            o_ok = (slot < kPairsPerWarp) && (rank < npass) && (g_meta & 0x100);
             o_pvx = o_pvy = 0.f;
             if (o_ok) {
                 const int x1 = (int)(int16_t)(g_xy & 0xffff), y1 = g_xy >> 16;
@@ -245,7 +276,8 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
 #pragma unroll
             for (int k = 0; k < kStepPaf; ++k) total_s = __fadd_rn(total_s, __shfl_sync(FULL, s, (group_base + k) & 31));
             const int hits = __popc(__ballot_sync(FULL, s > th.vector_score) & group_mask);
-            const int owner = min(kPairsPerWarp * t + slot, 31);
+            const int rank = kPairsPerWarp * t + slot;
+            const int owner = (slot < kPairsPerWarp && rank < npass) ? (int)__fns(alive, 0, rank + 1) : 0;
             const float g_norm = __shfl_sync(FULL, norm, owner);
             const int g_lab = __shfl_sync(FULL, lab, owner);
             if (c_ok && i == 0 && hits > th.vector_cnt1) {                        // first half of :85

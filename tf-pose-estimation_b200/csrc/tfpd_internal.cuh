@@ -60,6 +60,7 @@ struct Workspace {
     int k3_warp_sort_max;       // longest limb segment sorted by one warp (1024; TFPD_K3_WARPSORT lowers it for tests)
     int k3_parallel_limbs;      // 1: whole-limb assembly steps where provably order-free (TFPD_K3_PARALLEL=0 turns them off)
     int k3_reg_rows;
+    int k2_prefilter;        // 1: limb scoring rejects a pair after its first samples when it can no longer qualify (exact)
     int k2_blocks_per_frame; // > 0: CTAs of the scoring kernel per frame (default: ~6 CTAs per SM over the batch)
     int k2_fused_sort;      // the scoring kernel ranks the peak records itself (no k_sort_peaks launch)            // subset rows K3 keeps in registers before spilling to smem (128; TFPD_K3_REGROWS lowers it for tests)
     unsigned long long *dbg_times;  // null, or the ctx's timestamp buffer: K3 writes clock64 per phase at [2048 + frame*8 + phase], frame < 64
