@@ -243,9 +243,10 @@ TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, s
  *                  thresh_heat * (1 - 2e-4) / (sum of smoother weights)^2: every smoother weight is >= 0, so no
  *                  blurred value there can come within reach of the heat threshold or of a near-tie test.  Exact:
  *                  same tables, same near-tie counts; 0 computes every row.  Dense mode always computes every row.
- *   "k1_min_band"  minimal mode: low-res rows per work item of the fused map kernel's dynamic queue (default 4).  An
- *                  item is one band of rows of one frame; the 18 part channels of an item are taken by the warps of
- *                  one CTA.  Smaller bands balance better, larger ones re-read fewer window rows.  Same results.
+ *   "k1_min_band"  minimal mode: low-res rows per CTA of the fused map kernel (default 4).  In minimal mode the kernel
+ *                  runs one small CTA (6 warps, four per SM) per band of rows of a frame; its warps take the 18 part
+ *                  channels one by one.  Smaller bands balance better, larger ones re-read fewer window rows.  Same
+ *                  results.  ("k1_ctas" applies to dense mode only.)
  *   "early_fetch"  when the tables start their way to the host: 0 in tfpd_fetch_humans (default), 1 right behind
  *                  the last kernel on the same stream, 2 behind it on a side stream.
  *   "pow2_path"    kernels for power-of-two upsample factors other than the x4 fast path (2, 8, 16): 1 automatic

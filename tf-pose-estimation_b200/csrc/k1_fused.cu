@@ -39,6 +39,10 @@ constexpr int kHelperWarps = 2;              // blur warps that turn into copy w
 constexpr int kBlurThreads = kBlurWarps * 32;
 constexpr int kCopyThreads = kCopyWarps * 32;
 constexpr int kThreads = kBlurThreads + kCopyThreads;   // 640 -> 96 registers per thread
+// minimal mode (blur role alone): small CTAs, several per SM -- 6 warps x 4 CTAs = 24 warps per SM at <= 85 registers
+constexpr int kMinWarps = 6;
+constexpr int kMinThreads = kMinWarps * 32;
+constexpr int kMinCtasPerSm = 4;
 // a warp pass owns at most 32*CPL-8 = 56 cells (see launch_k1_fused_f4: chunk_cells <= 56)
 constexpr int NPX = 4 * CPL;                // output pixels per lane per row
 
@@ -516,6 +520,7 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
     using P2 = std::integral_constant<int, 2>;
     using P3 = std::integral_constant<int, 3>;
     int Yr = Ys;
+    bool last_dead = false;
 #pragma unroll 1
     for (int g4 = 0; g4 < it.nrows; ++g4, Yr += 4) {
         if (!DENSE) {
@@ -534,21 +539,35 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
 #pragma unroll
                 for (int i = 0; i < NPX; ++i) ga[i] = gb[i] = vm[i] = NEG;
                 slide();
+                last_dead = true;
                 continue;
             }
+            last_dead = false;
         }
         do_row(P3(), Yr, ga, gb);
         do_row(P0(), Yr + 1, gb, ga);
         do_row(P1(), Yr + 2, ga, gb);
         do_row(P2(), Yr + 3, gb, ga);
     }
-    do_row(P3(), Yr, ga, gb);
-    do_row(P0(), Yr + 1, gb, ga);
+    // The two tail rows compute g of rows Yr, Yr+1 (low-res rows iy-3 .. iy+4 again) and decide rows Yr-1, Yr.  When the
+    // band's last group was skipped (g of Yr-2, Yr-1 out of reach) and this window is dead as well, there is nothing to
+    // decide: same argument as above.
+    bool skip_tail = false;
+    if (!DENSE && last_dead) {
+        float wm_ = fmaxf(fmaxf(win[0].x, win[0].y), fmaxf(nxt.x, nxt.y));
+#pragma unroll
+        for (int t = 1; t < 7; ++t) wm_ = fmaxf(wm_, fmaxf(win[t].x, win[t].y));
+        skip_tail = !__any_sync(FULL, wm_ > p.dead_bound);
+    }
+    if (!skip_tail) {
+        do_row(P3(), Yr, ga, gb);
+        do_row(P0(), Yr + 1, gb, ga);
+    }
     if (DENSE) pgroup += (unsigned)((4 * it.nrows + PR - 1) / PR);
 }
 
 template <int PR, bool DENSE>
-__global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
+__global__ void __launch_bounds__(DENSE ? kThreads : kMinThreads, DENSE ? 1 : kMinCtasPerSm) k1_fused_f4(const K1Params p) {
     extern __shared__ __align__(128) float smem[];
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -561,7 +580,7 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
     unsigned char *cbase = reinterpret_cast<unsigned char *>(smem + 2 * (size_t)pslot_floats);
     uint64_t *bars_all = reinterpret_cast<uint64_t *>(cbase + kCopyWarps * cw_bytes);
 
-    if (p.dbg_times && tid == 0) {
+    if (p.dbg_times && tid == 0 && blockIdx.x < 1024) {
         unsigned smid;
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
         p.dbg_times[blockIdx.x * 4 + 0] = global_ns();
@@ -569,80 +588,44 @@ __global__ void __launch_bounds__(kThreads, 1) k1_fused_f4(const K1Params p) {
     }
     if (!DENSE) {
         // ---- minimal mode: nothing dense is written, the kernel is the blur role alone ----
-        // Every warp is an independent worker (there are no shared slots and no barriers in this mode), and two
-        // things follow from "only peak records and near-tie counts leave the kernel":
-        //  * channel 18 (the background heat map) yields neither (pafprocess.cpp:24 scans parts 0..17): it is not
-        //    computed at all.  Its heat is ~1 everywhere, so its warp could never take the early-out, and a CTA
-        //    finishes with its slowest warp: with a static row span per CTA the skipped row groups of the other 18
-        //    warps saved next to nothing (measured: 68.4 -> 65.6 us).
-        //  * the live / skipped share differs between rows and channels, so the work is handed out dynamically.
-        // Two-level queue: a CTA-level item is one band of `min_band` low-res rows of one (frame, column chunk),
-        // taken from the grid-wide counter; the 19 warps of the CTA take its 18 channels one by one from a
-        // shared-memory word {grid item, next channel} updated by compare-and-swap.  Whoever finds the item used up
-        // marks the word "refilling", fetches the next grid item and stores it; the others retry meanwhile; an
-        // empty grid queue leaves a sticky "done" mark.  Warps of one CTA therefore work on the same cells at about
-        // the same time (the 19 channels of a cell share three 32-byte sectors: L1 locality as in the dense
-        // kernel), without ever synchronising and with nothing that could be overwritten before it is read.
+        // Only peak records and near-tie counts leave the kernel, so
+        //  * channel 18 (the background heat map) is not computed: it yields neither (pafprocess.cpp:24 scans parts
+        //    0..17), and its heat is ~1 everywhere, so it could never take the early-out;
+        //  * warps need nothing from each other (no slots, no barriers).
+        // Grid = one SMALL, non-persistent CTA per item (a band of `min_band` low-res rows of one frame and column
+        // chunk): 6 warps, four CTAs per SM (24 warps per SM; the 19-warp persistent CTA of the dense kernel ran
+        // issue-bound at 65 % of the issue slots, ncu r02e).  The warps of a CTA take the item's 18 channels one by
+        // one from a shared-memory ticket, so they work on the same cells at about the same time (the channels of a
+        // cell share three 32-byte sectors: L1 locality).  Which rows and channels are skipped differs from item to
+        // item; the hardware's CTA scheduler does the balancing, and -- unlike persistent CTAs pulling from a
+        // software queue (tried: r02d) -- CTAs that retire every few microseconds let the scoring / assembly kernels
+        // of the batch before take SM slots in between when several contexts are in flight.
         if (!(p.debug_roles & 1)) return;
-        constexpr unsigned kRefilling = 255u, kDone = 254u;
-        __shared__ unsigned long long s_state;              // grid item << 8 | next channel (18 = used up)
-        if (tid == 0) s_state = (unsigned long long)kParts; // item 0 "used up": the first warp to come refills
+        __shared__ int s_next;
+        if (tid == 0) s_next = 0;
         __syncthreads();
         const int band = p.min_band;
         const int nbands = (p.h + band - 1) / band;
-        const long long total = (long long)p.N * p.nchunks * nbands;
-        int *queue = &p.counters[0].k1_queue;
+        const long long g = blockIdx.x;
+        const long long q = g / nbands;         // q = n * nchunks + chunk
+        const int b = (int)(g - q * nbands);
+        Item it;
+        it.iy0 = b * band;
+        it.nrows = min(band, p.h - it.iy0);
+        it.n = (int)(q / p.nchunks);
+        const int chunk = (int)(q - (long long)it.n * p.nchunks);
+        it.c0 = chunk * p.chunk_cells;
+        it.tc = min(p.chunk_cells, p.w - it.c0);
         unsigned pgroup = 0;
         uint32_t wmask0 = 0u, wmask1 = 0u;
         for (;;) {
-            long long g = -1;
             int ch = 0;
-            if (lane == 0) {
-                for (;;) {
-                    const unsigned long long old = *reinterpret_cast<volatile unsigned long long *>(&s_state);
-                    const unsigned c = (unsigned)(old & 0xffu);
-                    if (c == kDone) break;                                   // g stays -1: leave
-                    if (c == kRefilling) {
-                        __nanosleep(40);
-                        continue;
-                    }
-                    if (c < (unsigned)kParts) {                              // take channel c of the current item
-                        if (atomicCAS(&s_state, old, old + 1ull) == old) {
-                            g = (long long)(old >> 8);
-                            ch = (int)c;
-                            break;
-                        }
-                        continue;
-                    }
-                    // used up: become the refiller (one at a time)
-                    if (atomicCAS(&s_state, old, (old & ~0xffull) | kRefilling) != old) continue;
-                    const long long gn = atomicAdd(queue, 1);
-                    if (gn >= total) {
-                        *reinterpret_cast<volatile unsigned long long *>(&s_state) = (unsigned long long)kDone;
-                        break;
-                    }
-                    g = gn;
-                    ch = 0;
-                    __threadfence_block();
-                    *reinterpret_cast<volatile unsigned long long *>(&s_state) = ((unsigned long long)gn << 8) | 1ull;
-                    break;
-                }
-            }
-            g = __shfl_sync(0xffffffffu, g, 0);
+            if (lane == 0) ch = atomicAdd(&s_next, 1);
             ch = __shfl_sync(0xffffffffu, ch, 0);
-            if (g < 0) break;                   // the grid queue is empty
-            const long long q = g / nbands;     // q = n * nchunks + chunk
-            const int b = (int)(g - q * nbands);
-            Item it;
-            it.iy0 = b * band;
-            it.nrows = min(band, p.h - it.iy0);
-            it.n = (int)(q / p.nchunks);
-            const int chunk = (int)(q - (long long)it.n * p.nchunks);
-            it.c0 = chunk * p.chunk_cells;
-            it.tc = min(p.chunk_cells, p.w - it.c0);
+            if (ch >= kParts) break;
             blur_role<PR, false>(p, it, nullptr, 0, ch, lane, pgroup, wmask0, wmask1);
         }
-        if (p.dbg_times && lane == 0 && warp == 0) p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
+        if (p.dbg_times && lane == 0 && warp == 0 && blockIdx.x < 1024) p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
         return;
     }
     if (warp < kBlurWarps) {
@@ -719,14 +702,18 @@ int polyphase_weights(const double *s1d, int ksize, float wp[4][8]) {
 }
 
 int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t s) {
+    if (!dense) {
+        // minimal mode: one small CTA per (frame, column chunk, band of rows); the grid size does not depend on sm_count
+        const long long items = (long long)p.N * p.nchunks * ((p.h + p.min_band - 1) / p.min_band);
+        if (items <= 0) return 0;
+        if (items > 0x7fffffffLL) return -1;
+        k1_fused_f4<4, false><<<(unsigned)items, kMinThreads, 0, s>>>(p);
+        return cudaGetLastError() == cudaSuccess ? 1 : -1;
+    }
     // one CTA per SM; fewer only when there are fewer low-res rows than SMs
     const long long units = (long long)p.N * p.nchunks * p.h;
     const int grid = (int)min(units, (long long)sm_count);
     if (grid <= 0) return 0;
-    if (!dense) {
-        k1_fused_f4<4, false><<<grid, kBlurThreads, 0, s>>>(p);
-        return cudaGetLastError() == cudaSuccess ? 1 : -1;
-    }
     const size_t cslot = (size_t)p.copy_chunk * 4 * kNetC * 4;
     const size_t raw = (size_t)k1_raw_bytes(p.copy_chunk);
     const size_t prow = (size_t)p.chunk_cells * 4 * kHeatC * 4;     // one peaks row of a blur chunk
