@@ -247,6 +247,10 @@ TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, s
  *                  runs one small CTA (6 warps, four per SM) per band of rows of a frame; its warps take the 18 part
  *                  channels one by one.  Smaller bands balance better, larger ones re-read fewer window rows.  Same
  *                  results.  ("k1_ctas" applies to dense mode only.)
+ *   "tail_priority" 1: limb scoring and assembly run on a high-priority stream owned by the ctx, forked from and joined
+ *                  back into the caller's stream by events (the caller's stream order is unchanged).  With several
+ *                  contexts in flight their CTAs are then placed ahead of the pending CTAs of another context's map
+ *                  kernel.  0 (default): everything on the caller's stream.  Same results.
  *   "early_fetch"  when the tables start their way to the host: 0 in tfpd_fetch_humans (default), 1 right behind
  *                  the last kernel on the same stream, 2 behind it on a side stream.
  *   "pow2_path"    kernels for power-of-two upsample factors other than the x4 fast path (2, 8, 16): 1 automatic

@@ -88,6 +88,12 @@ struct tfpd_ctx {
     int early_fetch = 0;                // 0 copy the tables at fetch time, 1 right behind the last kernel, 2 on st_res
     cudaStream_t st_res = nullptr;
     cudaEvent_t ev_res = nullptr;
+    // "tail_priority": limb scoring and assembly run on a high-priority stream of the ctx, forked from and joined
+    // back into the caller's stream by events, so that their CTAs are placed ahead of pending map-kernel CTAs of
+    // other contexts
+    int tail_priority = 0;
+    cudaStream_t st_tail = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t ev_done = nullptr;      // behind the last operation of the latest decode/process call on last_stream
     int last_N = 0, last_H = 0, last_W = 0;
     int launches = 0;
@@ -198,8 +204,23 @@ Thresholds thresholds_of(const tfpd_config &c) {
 }
 
 // zero the per-frame counters, then stages 2..4 shared by both seams
+int run_tail_on(tfpd_ctx *ctx, const Workspace &ws, int N, const PafSource &src, size_t frame_stride, cudaStream_t s,
+                bool timed);
+
 int run_tail(tfpd_ctx *ctx, const Workspace &ws, int N, const PafSource &src, size_t frame_stride, cudaStream_t s,
              bool timed) {
+    if (!ctx->tail_priority || !ctx->st_tail) return run_tail_on(ctx, ws, N, src, frame_stride, s, timed);
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_fork, s));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->st_tail, ctx->ev_fork, 0));
+    const int rc = run_tail_on(ctx, ws, N, src, frame_stride, ctx->st_tail, timed);
+    // join even after a launch error: the caller's stream must not be left forked (also ends a stream capture cleanly)
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_join, ctx->st_tail));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(s, ctx->ev_join, 0));
+    return rc;
+}
+
+int run_tail_on(tfpd_ctx *ctx, const Workspace &ws, int N, const PafSource &src, size_t frame_stride, cudaStream_t s,
+                bool timed) {
     int r;
     if (timed) cudaEventRecord(ctx->ev[1], s);
     if (!ws.k2_fused_sort) {
@@ -430,6 +451,13 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     cudaStreamCreateWithFlags(&ctx->st_res, cudaStreamNonBlocking);
     cudaEventCreateWithFlags(&ctx->ev_res, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ctx->ev_done, cudaEventDisableTiming);
+    {
+        int lo = 0, hi = 0;                              // "greatest" priority is the numerically lowest value
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        cudaStreamCreateWithPriority(&ctx->st_tail, cudaStreamNonBlocking, hi);
+        cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming);
+    }
     if (const char *e = getenv("TFPD_HOST_CHUNKS")) ctx->host_chunks = atoi(e);
     if (const char *e = getenv("TFPD_K1_L2")) ctx->k1_l2_knobs = atoi(e);
     if (const char *e = getenv("TFPD_K1_ROLES")) ctx->k1_roles = atoi(e);
@@ -461,6 +489,9 @@ void tfpd_destroy(tfpd_ctx *ctx) {
     for (auto &g : ctx->graphs) cudaGraphExecDestroy(g.exec);
     if (ctx->ev_res) cudaEventDestroy(ctx->ev_res);
     if (ctx->ev_done) cudaEventDestroy(ctx->ev_done);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    if (ctx->st_tail) cudaStreamDestroy(ctx->st_tail);
     for (cudaStream_t st : {ctx->st_h2d, ctx->st_work, ctx->st_d2h, ctx->st_res})
         if (st) cudaStreamDestroy(st);
     if (ctx->ws_block) cudaFree(ctx->ws_block);
@@ -646,6 +677,8 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
     } else if (!strcmp(name, "resize_path")) {
         if (value < 0 || value > 3) return fail(ctx, TFPD_ERR_INVALID, "resize_path=%d out of range", value);
         ctx->resize_path = value;
+    } else if (!strcmp(name, "tail_priority")) {
+        ctx->tail_priority = value != 0;
     } else if (!strcmp(name, "k1_early_out")) {
         ctx->k1_early_out = value != 0;
     } else if (!strcmp(name, "k1_min_band")) {

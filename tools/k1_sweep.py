@@ -42,13 +42,15 @@ def k1_alone(xs):
     dec.close()
 
 
-def pipelined(xs, n_pipe, ctas, steps=60, dense_mode=True):
+def pipelined(xs, n_pipe, ctas, steps=60, dense_mode=True, tail_priority=0, band=4):
     decs = [tp.PoseDecoder(max_batch=B, max_upsample=(H, W)) for _ in range(n_pipe)]
     denses = [tuple(torch.empty((B, H, W, c), device="cuda") for c in (19, 38, 19)) for _ in range(n_pipe)] if dense_mode else None
     streams = [torch.cuda.Stream() for _ in range(n_pipe)]
     for d in decs:
         d.set_option("k1_ctas", ctas)
         d.set_option("k1_turnstile", 1)
+        d.set_option("tail_priority", tail_priority)
+        d.set_option("k1_min_band", band)
 
     def run(n):
         inflight = []
@@ -81,5 +83,9 @@ if __name__ == "__main__":
         for ctas in (112, 120, 128, 148):
             print("%s pipelined dense, %3d CTAs: " % (name, ctas) + "  ".join(
                 "%d ctx %.1f us" % (n, pipelined(xs, n, ctas)) for n in (2, 3, 4, 6)))
-        print("%s pipelined minimal, 148 CTAs: " % name + "  ".join(
-            "%d ctx %.1f us" % (n, pipelined(xs, n, 0, dense_mode=False)) for n in (2, 3, 4, 6)))
+        for tp_ in (0, 1):
+            for band in (4, 8):
+                print("%s pipelined minimal, tail_priority %d, band %d: " % (name, tp_, band) + "  ".join(
+                    "%d ctx %.1f us" % (n, pipelined(xs, n, 0, dense_mode=False, tail_priority=tp_, band=band)) for n in (2, 3, 4, 6)))
+        print("%s pipelined dense, 128 CTAs, tail_priority 1: " % name + "  ".join(
+            "%d ctx %.1f us" % (n, pipelined(xs, n, 128, tail_priority=1)) for n in (2, 3, 4)))

@@ -1,5 +1,7 @@
 """Limb-scoring kernel (K2) with and without the early rejection ("k2_prefilter"), sparse (c2) and crowded (c4)
-frames, 64 frames per call, minimal mode, K2 timed alone with CUDA events.  usage: python tools/k2_prefilter_times.py"""
+frames, 64 frames per call, minimal mode, K2 timed alone with CUDA events -- and against the peak-table capacity:
+K2's shared memory is 10 B per peak slot, which sets how many of its CTAs share an SM.
+usage: python tools/k2_prefilter_times.py"""
 import os
 import sys
 
@@ -14,16 +16,17 @@ B, h, w = 64, 46, 54
 for name, cfg, people in (("c2 sparse", 2, None), ("c4 crowded", 4, 30)):
     base = synth.synth_batch(16, h, w, config_id=cfg, **({"people": people} if people else {}))
     x = torch.from_numpy(np.concatenate([base] * 4)).cuda()
-    dec = tp.PoseDecoder(max_batch=B, max_upsample=(184, 216))
-    dec.set_profiling(True)
-    for pre in (0, 1, 0, 1):
-        dec.set_option("k2_prefilter", pre)
-        t = []
-        for i in range(12):
-            res = dec.decode(x, (184, 216))
-            if i >= 2:
-                t.append(dec.stage_ms())
-        st = np.mean(t, 0) * 1e3
-        print("%-10s k2_prefilter %d: K2 %.1f us (K1 %.1f, K3 %.1f) | candidates/frame %.0f humans %d"
-              % (name, pre, st[2], st[0], st[3], res.info["n_cands"].mean(), int(res.info["n_humans"].sum())))
-    dec.close()
+    for max_peaks in (1024, 2048, 4096):
+        dec = tp.PoseDecoder(max_batch=B, max_upsample=(184, 216), max_peaks=max_peaks)
+        dec.set_profiling(True)
+        for pre in (0, 1, 0, 1):
+            dec.set_option("k2_prefilter", pre)
+            t = []
+            for i in range(12):
+                res = dec.decode(x, (184, 216))
+                if i >= 2:
+                    t.append(dec.stage_ms())
+            st = np.mean(t, 0) * 1e3
+            print("%-10s max_peaks %4d k2_prefilter %d: K2 %.1f us (K1 %.1f, K3 %.1f) | candidates/frame %.0f humans %d"
+                  % (name, max_peaks, pre, st[2], st[0], st[3], res.info["n_cands"].mean(), int(res.info["n_humans"].sum())))
+        dec.close()
