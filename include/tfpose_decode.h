@@ -244,9 +244,9 @@ TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, s
  *                  blurred value there can come within reach of the heat threshold or of a near-tie test.  Exact:
  *                  same tables, same near-tie counts; 0 computes every row.  Dense mode always computes every row.
  *   "k1_min_band"  minimal mode: low-res rows per CTA of the fused map kernel (default 4).  In minimal mode the kernel
- *                  runs one small CTA (6 warps, four per SM) per band of rows of a frame; its warps take the 18 part
- *                  channels one by one.  Smaller bands balance better, larger ones re-read fewer window rows.  Same
- *                  results.  ("k1_ctas" applies to dense mode only.)
+ *                  runs three small CTAs (6 warps = 6 part channels each, four CTAs per SM) per band of rows of a
+ *                  frame.  Smaller bands balance better, larger ones re-read fewer window rows.  Same results.
+ *                  ("k1_ctas" applies to dense mode only.)
  *   "tail_priority" 1: limb scoring and assembly run on a high-priority stream owned by the ctx, forked from and joined
  *                  back into the caller's stream by events (the caller's stream order is unchanged).  With several
  *                  contexts in flight their CTAs are then placed ahead of the pending CTAs of another context's map

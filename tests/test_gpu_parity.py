@@ -443,3 +443,37 @@ def test_limb_scoring_early_rejection_is_exact(cuda, oracle):
     # and against the oracle with the reference's constants (check_frames runs with the rejection on by default)
     e, f_ = check_frames(cuda, oracle, batches[1][0], 4, max_peaks=4096, max_cands=8192, max_humans=128)
     assert e + f_ == 2
+
+
+def test_repeated_decodes_are_bit_identical(cuda):
+    """Determinism stress (stands in for compute-sanitizer racecheck, which the GPU pool does not allow): a data race
+    between the map kernel's roles (TMA staging slots, mbarrier phases, lazily cleared peak slots), in the fused peak
+    ranking or in the assembly kernel's in-place packing would show as run-to-run differences.  The same batch is
+    decoded 60 times per mode on alternating streams and contexts; dense tensors (whole buffers, pre-filled with a
+    sentinel), tables and frame info must be bit-identical every time."""
+    import torch
+    from helpers import table_tuples
+    x = synth.synth_batch(8, 46, 54, config_id=2, first_frame=1200)
+    x[5] = synth.synth_frame(46, 54, synth.frame_seed(4, 1200), people=30)          # one crowded frame in the batch
+    xd = torch.from_numpy(x).cuda()
+    decs = [tp.PoseDecoder(max_batch=8, max_upsample=(184, 216), max_peaks=4096, max_cands=8192, max_humans=128)
+            for _ in range(2)]
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    first = {}
+    for rep in range(60):
+        for dense_mode in (True, False):
+            d, st = decs[rep & 1], streams[(rep >> 1) & 1]
+            dense = _dense(torch, 8, 184, 216, fill=float(rep + 3)) if dense_mode else None
+            res = d.decode(xd, (184, 216), dense=dense, stream=st)
+            st.synchronize()
+            got = ([table_tuples(res, i) for i in range(8)], res.info.tobytes(),
+                   [t.cpu().numpy().tobytes() for t in dense] if dense_mode else None)
+            if dense_mode not in first:
+                first[dense_mode] = got
+            else:
+                assert got[0] == first[dense_mode][0] and got[1] == first[dense_mode][1], (rep, dense_mode)
+                if dense_mode:
+                    assert got[2] == first[True][2], "dense tensors differ between repeats (rep %d)" % rep
+    assert first[True][0] == first[False][0]
+    for d in decs:
+        d.close()

@@ -91,6 +91,10 @@ struct tfpd_ctx {
     // "tail_priority": limb scoring and assembly run on a high-priority stream of the ctx, forked from and joined
     // back into the caller's stream by events, so that their CTAs are placed ahead of pending map-kernel CTAs of
     // other contexts
+    // TFPD_CHECKED=1 in the environment at tfpd_create: a 256-byte guard band filled with 0xA5 follows every workspace
+    // array; tfpd_fetch_humans verifies them (an out-of-bounds write of any kernel into the neighbouring array's
+    // territory fails the call).  Stands in for compute-sanitizer memcheck, which this GPU pool does not allow.
+    std::vector<size_t> guard_offsets;
     int tail_priority = 0;
     cudaStream_t st_tail = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
@@ -381,6 +385,9 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     w.k3_reg_rows = 128;
     w.k2_fused_sort = 1;
     w.k2_prefilter = 1;
+#ifdef TFPD_CHECKED
+    w.dbg_trip = getenv("TFPD_CHECKED_TRIP") ? atoi(getenv("TFPD_CHECKED_TRIP")) : 0;
+#endif
     w.k2_blocks_per_frame = 0;
     if (const char *e = getenv("TFPD_K2_BPF")) w.k2_blocks_per_frame = atoi(e);
     w.k3_warp_sort_max = 1024;
@@ -390,9 +397,14 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     if (const char *e = getenv("TFPD_K3_REGROWS")) w.k3_reg_rows = atoi(e) < 0 ? 0 : atoi(e);
     const size_t N = (size_t)cfg->max_batch, MP = (size_t)w.max_peaks, MC = (size_t)w.max_cands;
     size_t off = 0;
+    const bool checked = getenv("TFPD_CHECKED") && atoi(getenv("TFPD_CHECKED"));
     auto take = [&](size_t bytes) {
         size_t o = off;
         off = align_up(off + bytes, 256);
+        if (checked && bytes) {
+            ctx->guard_offsets.push_back(off);
+            off += 256;
+        }
         return o;
     };
     const size_t o_cnt = take(N * sizeof(FrameCounters));
@@ -412,6 +424,7 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     }
     cudaMemset(ctx->ws_block, 0, off);
     unsigned char *b = (unsigned char *)ctx->ws_block;
+    for (size_t g : ctx->guard_offsets) cudaMemset(b + g, 0xA5, 256);
     w.counters = (FrameCounters *)(b + o_cnt);
     w.rec_key = (uint32_t *)(b + o_rk);
     w.rec_val = (float *)(b + o_rv);
@@ -702,6 +715,15 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
 
 int tfpd_last_launch_count(const tfpd_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
+#ifdef TFPD_CHECKED
+// checked build only (negative control of tools/checked_run.sh): overwrite one byte of workspace guard band `which`
+extern "C" TFPD_API int tfpd_debug_poke_guard(tfpd_ctx *ctx, int which) {
+    if (!ctx || which < 0 || (size_t)which >= ctx->guard_offsets.size()) return TFPD_ERR_INVALID;
+    DeviceGuard device_guard__(ctx->cfg.device);
+    return cudaMemset((unsigned char *)ctx->ws_block + ctx->guard_offsets[which] + 17, 0, 1) == cudaSuccess ? TFPD_OK : TFPD_ERR_CUDA;
+}
+#endif
+
 int tfpd_debug_k1_times(tfpd_ctx *ctx, uint64_t *out, int max_ctas) {
     if (!ctx || !out || max_ctas < 1) return TFPD_ERR_INVALID;
     if (!ctx->d_k1_times) return fail(ctx, TFPD_ERR_STATE, "per-CTA timestamps are off (create the ctx with TFPD_K1_TIMES=1)");
@@ -977,6 +999,16 @@ int tfpd_fetch_humans(tfpd_ctx *ctx, tfpd_human *humans, tfpd_frame_info *info) 
             ctx->d2h_pending = false;
         }
         ctx->fetched = true;
+        if (!ctx->guard_offsets.empty()) {
+            unsigned char probe[256];
+            for (size_t gi = 0; gi < ctx->guard_offsets.size(); ++gi) {
+                CUDA_TRY(ctx, cudaMemcpy(probe, (unsigned char *)ctx->ws_block + ctx->guard_offsets[gi], 256, cudaMemcpyDeviceToHost));
+                for (int k = 0; k < 256; ++k)
+                    if (probe[k] != 0xA5)
+                        return fail(ctx, TFPD_ERR_CUDA, "TFPD_CHECKED: guard band %zu of the workspace was overwritten at byte %d "
+                                                        "(an out-of-bounds write behind workspace array %zu)", gi, k, gi);
+            }
+        }
     }
     const tfpd_frame_info *hi = (const tfpd_frame_info *)ctx->h_result;
     if (info) memcpy(info, hi, (size_t)N * sizeof(tfpd_frame_info));

@@ -460,6 +460,7 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
                         const int b = __ffs(mk) - 1;
                         mk &= mk - 1;
                         const int rr = b / NPX, i = b - rr * NPX;
+                        TFPD_CHK(lx0 + i >= 0 && ((size_t)rr * pitch_px + lx0 + i) * kHeatC + c < (size_t)pslot_floats);
                         slot[((size_t)rr * pitch_px + lx0 + i) * kHeatC + c] = 0.0f;
                     }
                     wm = 0;
@@ -483,6 +484,8 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
                         const float2 hw = (py == 0) ? win[2] : win[3];
                         hc = (q >> 2) ? hw.y : hw.x;
                     }
+                if (DENSE) TFPD_CHK(lx0 + i >= 0 && ((size_t)jr * pitch_px + lx0 + i) * kHeatC + c < (size_t)pslot_floats);
+                TFPD_CHK(Yc >= 0 && Yc < H && 4 * (cell0 + (i >> 2)) + (i & 3) >= 0 && 4 * (cell0 + (i >> 2)) + (i & 3) < W);
                 emit_peak(p, n, c, Yc, 4 * (cell0 + (i >> 2)) + (i & 3), gc, hc, nb,
                           DENSE ? slot + ((size_t)jr * pitch_px + lx0 + i) * kHeatC + c : nullptr);
             }
@@ -577,8 +580,18 @@ __global__ void __launch_bounds__(DENSE ? kThreads : kMinThreads, DENSE ? 1 : kM
     float *pslots = smem;                                 // 2 peak-row slots (blur role)
     // per copy warp: 2 replication slots + 2 raw chunks; then 2 mbarriers per copy warp
     const size_t cw_bytes = 2 * (size_t)cslot_floats * 4 + 2 * (size_t)raw_bytes;
-    unsigned char *cbase = reinterpret_cast<unsigned char *>(smem + 2 * (size_t)pslot_floats);
-    uint64_t *bars_all = reinterpret_cast<uint64_t *>(cbase + kCopyWarps * cw_bytes);
+    // (TFPD_GUARD_BYTES is 0 in the product build; the checked build guards the two boundaries between the roles' areas)
+    unsigned char *g_slots = reinterpret_cast<unsigned char *>(smem + 2 * (size_t)pslot_floats);
+    unsigned char *cbase = g_slots + TFPD_GUARD_BYTES;
+    unsigned char *g_copy = cbase + kCopyWarps * cw_bytes;
+    uint64_t *bars_all = reinterpret_cast<uint64_t *>(g_copy + TFPD_GUARD_BYTES);
+#ifdef TFPD_CHECKED
+    if (DENSE) {
+        guard_fill(g_slots, tid, (int)blockDim.x);
+        guard_fill(g_copy, tid, (int)blockDim.x);
+        __syncthreads();
+    }
+#endif
 
     if (p.dbg_times && tid == 0 && blockIdx.x < 1024) {
         unsigned smid;
@@ -592,18 +605,18 @@ __global__ void __launch_bounds__(DENSE ? kThreads : kMinThreads, DENSE ? 1 : kM
         //  * channel 18 (the background heat map) is not computed: it yields neither (pafprocess.cpp:24 scans parts
         //    0..17), and its heat is ~1 everywhere, so it could never take the early-out;
         //  * warps need nothing from each other (no slots, no barriers).
-        // Grid = one SMALL, non-persistent CTA per item (a band of `min_band` low-res rows of one frame and column
-        // chunk): 6 warps, four CTAs per SM (24 warps per SM; the 19-warp persistent CTA of the dense kernel ran
-        // issue-bound at 65 % of the issue slots, ncu r02e).  The warps of a CTA take the item's 18 channels one by
-        // one from a shared-memory ticket, so they work on the same cells at about the same time (the channels of a
-        // cell share three 32-byte sectors: L1 locality).  Which rows and channels are skipped differs from item to
-        // item; the hardware's CTA scheduler does the balancing, and -- unlike persistent CTAs pulling from a
-        // software queue (tried: r02d) -- CTAs that retire every few microseconds let the scoring / assembly kernels
-        // of the batch before take SM slots in between when several contexts are in flight.
+        // Grid = SMALL, non-persistent CTAs: blockIdx.x = item (a band of `min_band` low-res rows of one frame and
+        // column chunk), blockIdx.y = one of three groups of six part channels, warp = channel.  6 warps per CTA, four
+        // CTAs per SM (24 warps per SM; the 19-warp persistent CTA of the dense kernel ran issue-bound at 65 % of the
+        // issue slots, ncu r02e).  The six channels of a CTA share the 32-byte sectors of a cell (L1 locality), the
+        // other two groups of the same band are the neighbouring CTAs.  Which rows and channels are skipped differs
+        // from CTA to CTA; the hardware's CTA scheduler does the balancing, and with thousands of CTAs of a few
+        // microseconds each the last wave is short (with one CTA per band: 768 CTAs on 592 slots, the SMs were
+        // active 66 % of the kernel, ncu r02f).  Unlike persistent CTAs pulling from a software queue (tried: r02d),
+        // CTAs that retire every few microseconds also let the scoring / assembly kernels of the batch before take SM
+        // slots in between when several contexts are in flight.
         if (!(p.debug_roles & 1)) return;
-        __shared__ int s_next;
-        if (tid == 0) s_next = 0;
-        __syncthreads();
+        static_assert(kParts % kMinWarps == 0, "channel groups");
         const int band = p.min_band;
         const int nbands = (p.h + band - 1) / band;
         const long long g = blockIdx.x;
@@ -618,14 +631,9 @@ __global__ void __launch_bounds__(DENSE ? kThreads : kMinThreads, DENSE ? 1 : kM
         it.tc = min(p.chunk_cells, p.w - it.c0);
         unsigned pgroup = 0;
         uint32_t wmask0 = 0u, wmask1 = 0u;
-        for (;;) {
-            int ch = 0;
-            if (lane == 0) ch = atomicAdd(&s_next, 1);
-            ch = __shfl_sync(0xffffffffu, ch, 0);
-            if (ch >= kParts) break;
-            blur_role<PR, false>(p, it, nullptr, 0, ch, lane, pgroup, wmask0, wmask1);
-        }
-        if (p.dbg_times && lane == 0 && warp == 0 && blockIdx.x < 1024) p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
+        blur_role<PR, false>(p, it, nullptr, 0, (int)blockIdx.y * kMinWarps + warp, lane, pgroup, wmask0, wmask1);
+        if (p.dbg_times && lane == 0 && warp == 0 && blockIdx.y == 0 && blockIdx.x < 1024)
+            p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
         return;
     }
     if (warp < kBlurWarps) {
@@ -654,6 +662,9 @@ __global__ void __launch_bounds__(DENSE ? kThreads : kMinThreads, DENSE ? 1 : kM
             u += it.nrows;
         }
         if (DENSE && tid == 0) bulk_wait_all();
+#ifdef TFPD_CHECKED
+        if (DENSE && lane == 0) TFPD_CHK(guard_ok(g_slots) && guard_ok(g_copy));
+#endif
         if (p.dbg_times && tid == 0) p.dbg_times[blockIdx.x * 4 + 1] = global_ns();
         if (DENSE && (p.debug_roles & 2) && kHelperWarps > 0) {
             // The blur role of this CTA is done (measured: at ~65 % of the kernel) and its peak-row slots are
@@ -676,6 +687,9 @@ __global__ void __launch_bounds__(DENSE ? kThreads : kMinThreads, DENSE ? 1 : kM
             unsigned char *raws = reinterpret_cast<unsigned char *>(cslots + 2 * (size_t)cslot_floats);
             copy_role(p, cslots, cslot_floats, raws, raw_bytes, bars_all + 2 * cw, lane);
             if (lane == 0) bulk_wait_all();
+#ifdef TFPD_CHECKED
+            if (lane == 0) TFPD_CHK(guard_ok(g_slots) && guard_ok(g_copy));
+#endif
         }
         if (p.dbg_times && lane == 0 && cw == 0) p.dbg_times[blockIdx.x * 4 + 2] = global_ns();
     }
@@ -707,7 +721,7 @@ int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t
         const long long items = (long long)p.N * p.nchunks * ((p.h + p.min_band - 1) / p.min_band);
         if (items <= 0) return 0;
         if (items > 0x7fffffffLL) return -1;
-        k1_fused_f4<4, false><<<(unsigned)items, kMinThreads, 0, s>>>(p);
+        k1_fused_f4<4, false><<<dim3((unsigned)items, kParts / kMinWarps), kMinThreads, 0, s>>>(p);
         return cudaGetLastError() == cudaSuccess ? 1 : -1;
     }
     // one CTA per SM; fewer only when there are fewer low-res rows than SMs
@@ -717,7 +731,7 @@ int launch_k1_fused_f4(const K1Params &p, bool dense, int sm_count, cudaStream_t
     const size_t cslot = (size_t)p.copy_chunk * 4 * kNetC * 4;
     const size_t raw = (size_t)k1_raw_bytes(p.copy_chunk);
     const size_t prow = (size_t)p.chunk_cells * 4 * kHeatC * 4;     // one peaks row of a blur chunk
-    const size_t fixed = kCopyWarps * (2 * cslot + 2 * raw) + 16 * (kCopyWarps + kHelperWarps);
+    const size_t fixed = kCopyWarps * (2 * cslot + 2 * raw) + 16 * (kCopyWarps + kHelperWarps) + 2 * TFPD_GUARD_BYTES;
     const size_t limit = 227 * 1024 - 1024;
     // function attributes are per device: one flag per device a ctx of this process may live on
     static bool attr_set[64] = {};

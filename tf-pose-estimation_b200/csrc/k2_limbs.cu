@@ -88,6 +88,7 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
                 const int lo = s_first[key_part(k)], hi = s_first[key_part(k) + 1];
                 int r = lo;
                 for (int t = lo; t < hi; ++t) r += (int)(s_key[t] < k);
+                TFPD_CHK(r >= 0 && r < ws.max_peaks && s_idx[j] < cnt);
                 s_px[r] = (int16_t)key_x(k);
                 s_py[r] = (int16_t)key_y(k);
                 if (blockIdx.x == 0) {
@@ -196,6 +197,7 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
             const int a = r / nb;
             const int b = r - a * nb;
             const int ia = s_first[pa] + a, ib = s_first[pb] + b;
+            TFPD_CHK(ia >= 0 && ia < ws.max_peaks && ib >= 0 && ib < ws.max_peaks && limb < kLimbs);
             const int x1 = s_px[ia], y1 = s_py[ia], x2 = s_px[ib], y2 = s_py[ib];
             const float dx = (float)(x2 - x1), dy = (float)(y2 - y1);                     // :63-64
             norm = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));           // :65
@@ -225,6 +227,7 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
                     const float fy = __fadd_rn((float)y1, __fmul_rn((float)k, stepy));
                     const int lx = (int)((double)fx + 0.5);
                     const int ly = (int)((double)fy + 0.5);
+                    TFPD_CHK(lx >= 0 && ly >= 0 && (ly >> src.shift) < src.rows && (lx >> src.shift) < src.cols);
                     const float *pp = paf + ((size_t)(ly >> src.shift) * src.cols + (lx >> src.shift)) * src.chan +
                                       src.chan_off + chan0;
                     const float sk = __fadd_rn(__fmul_rn(vx, __ldg(pp)), __fmul_rn(vy, __ldg(pp + 1)));
@@ -257,6 +260,7 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
                 const float fy = __fadd_rn((float)y1, __fmul_rn((float)i, g_sy));
                 const int lx = (int)((double)fx + 0.5);
                 const int ly = (int)((double)fy + 0.5);
+                TFPD_CHK(lx >= 0 && ly >= 0 && (ly >> src.shift) < src.rows && (lx >> src.shift) < src.cols);
                 const float *pp = paf + ((size_t)(ly >> src.shift) * src.cols + (lx >> src.shift)) * src.chan +
                                   src.chan_off + (g_meta & 0xff);
                 o_pvx = __ldg(pp);              // the two PAF channels of a limb are adjacent (pafprocess.h:20-24)

@@ -43,14 +43,20 @@ constexpr int kBitmapWords = kMaxPeaksHard / 32;   // 128
 template <int MINB>
 __global__ void __launch_bounds__(kK3Threads, MINB) k_assemble(Workspace ws, Thresholds th) {
     extern __shared__ __align__(16) unsigned char sm_raw[];
+    // (TFPD_GUARD_BYTES is 0 in the product build; the checked build puts a guard band behind every sub-array)
     unsigned long long *keys = reinterpret_cast<unsigned long long *>(sm_raw);            // [max_cands]
-    float *rows = reinterpret_cast<float *>(keys + ws.max_cands);                        // [20][max_rows] SoA
-    uint32_t *used = reinterpret_cast<uint32_t *>(rows + 20 * (size_t)ws.max_rows);      // [19][2][128]
+    unsigned char *g_keys = reinterpret_cast<unsigned char *>(keys + ws.max_cands);
+    float *rows = reinterpret_cast<float *>(g_keys + TFPD_GUARD_BYTES);                  // [20][max_rows] SoA
+    unsigned char *g_rows = reinterpret_cast<unsigned char *>(rows + 20 * (size_t)ws.max_rows);
+    uint32_t *used = reinterpret_cast<uint32_t *>(g_rows + TFPD_GUARD_BYTES);            // [19][2][128]
+    unsigned char *g_used = reinterpret_cast<unsigned char *>(used + kLimbs * 2 * kBitmapWords);
     // the frame's peak table, staged once: assembly and the getter view index it by cid (a dependent global
     // load per connection was the latency chain of this kernel)
-    float *s_pscore = reinterpret_cast<float *>(used + kLimbs * 2 * kBitmapWords);       // [max_peaks]
+    float *s_pscore = reinterpret_cast<float *>(g_used + TFPD_GUARD_BYTES);              // [max_peaks]
     int16_t *s_pkx = reinterpret_cast<int16_t *>(s_pscore + ws.max_peaks);               // [max_peaks]
     int16_t *s_pky = s_pkx + ws.max_peaks;                                               // [max_peaks]
+    unsigned char *g_end = reinterpret_cast<unsigned char *>(s_pky + ws.max_peaks);
+    (void)g_end;
     __shared__ int s_lstart[kLimbs + 1];
     __shared__ int s_ccount[kLimbs];
     __shared__ int s_first[kHeatC + 1];
@@ -61,6 +67,12 @@ __global__ void __launch_bounds__(kK3Threads, MINB) k_assemble(Workspace ws, Thr
     __shared__ float s_stage[3][kRegRowsMax];   // new subset rows on their way from connection lanes to row lanes
 
     const int n = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef TFPD_CHECKED
+    guard_fill(g_keys, tid, kK3Threads);
+    guard_fill(g_rows, tid, kK3Threads);
+    guard_fill(g_used, tid, kK3Threads);
+    guard_fill(g_end, tid, kK3Threads);
+#endif
     if (ws.dbg_times && tid == 0 && n < 64) ws.dbg_times[2048 + n * 8 + 0] = clock64();
     const int MR = ws.max_rows;
     const int raw = ws.counters[n].n_cand;
@@ -225,6 +237,11 @@ __global__ void __launch_bounds__(kK3Threads, MINB) k_assemble(Workspace ws, Thr
         ws.conn_start[n * 20 + tid] = s_lstart[tid];
         ws.conn_count[n * 20 + tid] = s_ccount[tid];
     }
+#ifdef TFPD_CHECKED
+    if (ws.dbg_trip && tid == 0) keys[ws.max_cands] = 1ull;      // negative control: one element past the key array
+    __syncthreads();
+    if (lane == 0) TFPD_CHK(guard_ok(g_keys) && guard_ok(g_rows) && guard_ok(g_used) && guard_ok(g_end));
+#endif
     if (warp != 0) return;
 
     // ---- 3. subset assembly (warp 0) ----
@@ -650,6 +667,10 @@ __global__ void __launch_bounds__(kK3Threads, MINB) k_assemble(Workspace ws, Thr
             for (int l = 0; l < kLimbs; ++l) tc += s_ccount[l];
             ws.dbg_times[2048 + n * 8 + 7] = ((unsigned long long)tc << 32) | (unsigned)s_maxseg;   // connections | longest segment
         }
+#ifdef TFPD_CHECKED
+        TFPD_CHK(guard_ok(g_keys) && guard_ok(g_rows) && guard_ok(g_used) && guard_ok(g_end));
+        TFPD_CHK(nrows >= 0 && nh >= 0 && cnt <= ws.max_cands);
+#endif
     }
 }
 
@@ -657,7 +678,7 @@ __global__ void __launch_bounds__(kK3Threads, MINB) k_assemble(Workspace ws, Thr
 
 size_t assemble_smem_bytes(const Workspace &ws) {
     return (size_t)ws.max_cands * 8 + (size_t)20 * ws.max_rows * 4 + (size_t)kLimbs * 2 * kBitmapWords * 4 +
-           (size_t)ws.max_peaks * 8;
+           (size_t)ws.max_peaks * 8 + 4 * TFPD_GUARD_BYTES;
 }
 
 int launch_assemble(const Workspace &ws, int N, const Thresholds &th, cudaStream_t s) {

@@ -13,7 +13,38 @@
 #include <stdint.h>
 #include "tfpose_decode.h"
 
+// Checked build (make -C tf-pose-estimation_b200/csrc checked -> tools/ab/libtfpose_decode_checked.so, -DTFPD_CHECKED):
+// TFPD_CHK(cond) traps with a message when cond is false; guard words sit between the shared-memory sub-arrays of the
+// kernels and are verified when a role finishes.  Compiled out of the product build.  Stands in for compute-sanitizer,
+// which this GPU pool does not allow (profiles/r02_sanitizers/README.md).
+#ifdef TFPD_CHECKED
+#include <cstdio>
+#define TFPD_CHK(cond)                                                                                          \
+    do {                                                                                                        \
+        if (!(cond)) {                                                                                          \
+            printf("TFPD_CHK failed: %s  at %s:%d  (block %d,%d thread %d)\n", #cond, __FILE__, __LINE__,          \
+                   (int)blockIdx.x, (int)blockIdx.y, (int)threadIdx.x);                                         \
+            __trap();                                                                                           \
+        }                                                                                                       \
+    } while (0)
+#define TFPD_GUARD_BYTES 128
+#else
+#define TFPD_CHK(cond) ((void)0)
+#define TFPD_GUARD_BYTES 0
+#endif
+
 namespace tfpd {
+
+#ifdef TFPD_CHECKED
+__device__ inline void guard_fill(void *g, int tid, int nthreads) {
+    for (int i = tid; i < TFPD_GUARD_BYTES / 4; i += nthreads) reinterpret_cast<volatile uint32_t *>(g)[i] = 0xA5A5A5A5u;
+}
+__device__ inline bool guard_ok(const void *g) {
+    bool ok = true;
+    for (int i = 0; i < TFPD_GUARD_BYTES / 4; ++i) ok = ok && reinterpret_cast<const volatile uint32_t *>(g)[i] == 0xA5A5A5A5u;
+    return ok;
+}
+#endif
 
 constexpr int kParts = TFPD_NUM_PARTS;
 constexpr int kLimbs = TFPD_NUM_LIMBS;
@@ -60,6 +91,9 @@ struct Workspace {
     int k3_warp_sort_max;       // longest limb segment sorted by one warp (1024; TFPD_K3_WARPSORT lowers it for tests)
     int k3_parallel_limbs;      // 1: whole-limb assembly steps where provably order-free (TFPD_K3_PARALLEL=0 turns them off)
     int k3_reg_rows;
+#ifdef TFPD_CHECKED
+    int dbg_trip;            // checked build only, TFPD_CHECKED_TRIP=1: the assembly kernel writes one element past its key array (negative control)
+#endif
     int k2_prefilter;        // 1: limb scoring rejects a pair after its first samples when it can no longer qualify (exact)
     int k2_blocks_per_frame; // > 0: CTAs of the scoring kernel per frame (default: ~6 CTAs per SM over the batch)
     int k2_fused_sort;      // the scoring kernel ranks the peak records itself (no k_sort_peaks launch)            // subset rows K3 keeps in registers before spilling to smem (128; TFPD_K3_REGROWS lowers it for tests)
