@@ -70,7 +70,7 @@ struct tfpd_ctx {
     int k1_grid = 0;                    // TFPD_K1_GRID: CTAs of the fused map kernel (0 = one per SM)
     int k1_l2_knobs = 2, k1_roles = 3;  // TFPD_K1_L2 / TFPD_K1_ROLES tuning and profiling knobs
     int k1_early_out = 1;               // minimal mode: skip low-res row groups that cannot reach the heat threshold
-    int k1_min_band = 4;                // minimal mode: low-res rows per work item of the map kernel's dynamic queue
+    int k1_min_band = 0;                // minimal mode: low-res rows per CTA of the map kernel (0 = automatic)
     unsigned long long *d_k1_times = nullptr;   // TFPD_K1_TIMES=1: per-CTA timestamps of the last K1 launch
     bool profiling = false, have_timing = false;
     cudaStream_t last_stream = nullptr;
@@ -695,7 +695,7 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
     } else if (!strcmp(name, "k1_early_out")) {
         ctx->k1_early_out = value != 0;
     } else if (!strcmp(name, "k1_min_band")) {
-        if (value < 1 || value > 8191) return fail(ctx, TFPD_ERR_INVALID, "k1_min_band=%d out of range", value);
+        if (value < 0 || value > 8191) return fail(ctx, TFPD_ERR_INVALID, "k1_min_band=%d out of range", value);
         ctx->k1_min_band = value;
     } else if (!strcmp(name, "k1_l2")) {
         if (value < 0 || value > 7) return fail(ctx, TFPD_ERR_INVALID, "k1_l2=%d out of range", value);
@@ -792,6 +792,19 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         p.copy_chunk = (w + p.copy_nchunks - 1) / p.copy_nchunks;
         p.thresh = ctx->cfg.thresh_heat;
         p.min_band = ctx->k1_min_band;
+        if (p.min_band <= 0) {
+            // automatic: the largest band of 16 / 8 / 4 low-res rows that still gives ~6 waves of CTAs (three CTAs per
+            // band, four resident per SM).  Measured (profiles/r02g_k1_ab.log, 64 frames): 46x54 maps 4 rows (52.5 us
+            // against 53.8 / 59.2 at 8 / 16), 92x164 maps 16 rows (129.5 us against 154.0 at 4): larger bands re-read
+            // fewer window rows, smaller ones fill the last wave.
+            const long long enough = 6LL * 4 * ctx->sm_count;
+            p.min_band = 4;
+            for (int cand = 16; cand >= 8; cand /= 2)
+                if ((long long)N * p.nchunks * ((h + cand - 1) / cand) * (kParts / 6) >= enough) {
+                    p.min_band = cand;
+                    break;
+                }
+        }
         memcpy(p.wp, ctx->wp, sizeof(p.wp));
         for (int q = 0; q < 2; ++q)
             for (int t = 0; t < 8; ++t) p.wh[q][t] = make_float2(ctx->wp[2 * q][t], ctx->wp[2 * q + 1][t]);
