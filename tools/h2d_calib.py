@@ -23,6 +23,10 @@ REPS = 40
 
 
 def main():
+    # stdout carries exactly one JSON line: NCCL prints its version banner on file descriptor 1 from C code
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -83,7 +87,7 @@ def main():
                 "concurrent_over_alone": float(v[:, 1].sum() / max(v[:, 0].sum(), 1e-9)),
                 "frames_per_s_bound_concurrent": float(v[:, 1].sum() * 1e9 / (BYTES / 64)),
                 "nproc": os.cpu_count()}
-        sys.stdout.write(json.dumps(line) + "\n")
+        os.write(real_stdout, (json.dumps(line) + "\n").encode())
     if dist is not None:
         dist.destroy_process_group()
 
