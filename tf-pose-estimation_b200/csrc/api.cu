@@ -541,8 +541,8 @@ int tfpd_draw_humans(tfpd_ctx *ctx, uint8_t *images, int on_device, int N, int i
                      const int32_t *centers, const int32_t *counts, int max_h, void *stream) {
     if (!ctx) return TFPD_ERR_INVALID;
     if (!images || !centers || !counts) return fail(ctx, TFPD_ERR_INVALID, "draw_humans: null argument");
-    if (N < 1 || img_h < 1 || img_w < 1 || max_h < 1 || img_h > 32767 || img_w > 32767)
-        return fail(ctx, TFPD_ERR_INVALID, "draw_humans: bad dimensions");
+    if (N < 1 || N > 65535 || img_h < 1 || img_w < 1 || max_h < 1 || img_h > 32767 || img_w > 32767)     // N is gridDim.y of the draw kernels
+        return fail(ctx, TFPD_ERR_INVALID, "draw_humans: bad dimensions (N 1..65535, image sides 1..32767)");
     for (int i = 0; i < N; ++i)
         if (counts[i] < 0 || counts[i] > max_h) return fail(ctx, TFPD_ERR_INVALID, "draw_humans: counts[%d]=%d outside 0..%d", i, counts[i], max_h);
     ON_CTX_DEVICE(ctx);
