@@ -238,9 +238,6 @@ TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, s
  *   "k1_turnstile" 1: the map kernels of all contexts on this device run one after the other (stream-ordered through
  *                  a per-device event), whatever their streams.  With several contexts in flight this keeps a
  *                  second HBM-bound map kernel from starting on the SMs "k1_ctas" leaves to the tail kernels.
- *   "k1_helpers"   dense mode: when a CTA's blur role is done its first blur warps become copy warps on the same item
- *                  queue, with staging buffers carved out of the idle peak-row slots.  0 (default): two helpers with two
- *                  replication slots each; 1: as many single-slot helpers as fit (up to four).  Same outputs.
  *   "k1_early_out" 1 (default): in minimal mode (no dense outputs) the fused map kernel skips a low-res row group of a
  *                  channel when the largest heat value in the 8 low-res rows that group reads is below
  *                  thresh_heat * (1 - 2e-4) / (sum of smoother weights)^2: every smoother weight is >= 0, so no

@@ -374,8 +374,7 @@ def test_tuning_options_do_not_change_results(cuda):
     for name, val in (("k1_ctas", 0), ("k1_ctas", 128), ("k1_ctas", 7), ("k1_l2", 0), ("k1_l2", 3),
                       ("early_fetch", 1), ("early_fetch", 2), ("fuse_sort", 0), ("fuse_sort", 1), ("graph", 1),
                       ("k1_turnstile", 1), ("tail_priority", 1), ("graph", 0), ("tail_priority", 1), ("k2_prefilter", 0),
-                      ("tail_priority", 0), ("k1_turnstile", 0), ("graph", 1), ("tail_priority", 1), ("k1_helpers", 1),
-                      ("k1_ctas", 128), ("k1_helpers", 0)):   # capture with the forked tail stream
+                      ("tail_priority", 0), ("k1_turnstile", 0), ("graph", 1), ("tail_priority", 1)):   # capture with the forked tail stream
         dec.set_option(name, val)
         dense = tuple(torch.full((6, 184, 216, c), 3.0, device="cuda") for c in (19, 38, 19))
         res = dec.decode(xd, (184, 216), dense=dense)

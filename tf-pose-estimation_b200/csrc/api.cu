@@ -70,7 +70,6 @@ struct tfpd_ctx {
     int k1_grid = 0;                    // TFPD_K1_GRID: CTAs of the fused map kernel (0 = one per SM)
     int k1_l2_knobs = 2, k1_roles = 3;  // TFPD_K1_L2 / TFPD_K1_ROLES tuning and profiling knobs
     int k1_early_out = 1;               // minimal mode: skip low-res row groups that cannot reach the heat threshold
-    int k1_helpers = 0;                 // "k1_helpers": 0 two double-slot copy helpers per CTA, 1 up to four single-slot ones
     int k1_min_band = 0;                // minimal mode: low-res rows per CTA of the map kernel (0 = automatic)
     unsigned long long *d_k1_times = nullptr;   // TFPD_K1_TIMES=1: per-CTA timestamps of the last K1 launch
     bool profiling = false, have_timing = false;
@@ -477,7 +476,6 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     if (const char *e = getenv("TFPD_K1_ROLES")) ctx->k1_roles = atoi(e);
     if (const char *e = getenv("TFPD_K1_PR")) ctx->k1_pr = atoi(e);
     if (const char *e = getenv("TFPD_K1_GRID")) ctx->k1_grid = atoi(e);
-    if (const char *e = getenv("TFPD_K1_HELPERS")) ctx->k1_helpers = atoi(e) != 0;
     if (const char *e = getenv("TFPD_K1_TIMES"))
         if (atoi(e) && cudaMalloc((void **)&ctx->d_k1_times, 1024 * 4 * 8) == cudaSuccess) {
             cudaMemset(ctx->d_k1_times, 0, 1024 * 4 * 8);
@@ -694,9 +692,6 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
         ctx->resize_path = value;
     } else if (!strcmp(name, "tail_priority")) {
         ctx->tail_priority = value != 0;
-    } else if (!strcmp(name, "k1_helpers")) {
-        if (value < 0 || value > 1) return fail(ctx, TFPD_ERR_INVALID, "k1_helpers=%d out of range", value);
-        ctx->k1_helpers = value;
     } else if (!strcmp(name, "k1_early_out")) {
         ctx->k1_early_out = value != 0;
     } else if (!strcmp(name, "k1_min_band")) {
@@ -796,7 +791,6 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         p.copy_nchunks = (w + copy_cells - 1) / copy_cells;  // <= 32 cells (29 KB staged) per copy item
         p.copy_chunk = (w + p.copy_nchunks - 1) / p.copy_nchunks;
         p.thresh = ctx->cfg.thresh_heat;
-        p.helper_mode = ctx->k1_helpers;
         p.min_band = ctx->k1_min_band;
         if (p.min_band <= 0) {
             // automatic: the largest band of 16 / 8 / 4 low-res rows that still gives ~6 waves of CTAs (three CTAs per

@@ -35,7 +35,7 @@ namespace {
 constexpr int CPL = 2;                      // low-res cells per lane
 constexpr int kBlurWarps = kHeatC;          // 19
 constexpr int kCopyWarps = 1;                // dedicated copy warps (20 warps = 5 per SM sub-partition -> 96 registers)
-constexpr int kHelperWarps = 4;              // at most this many blur warps turn into copy warps once the blur role is done
+constexpr int kHelperWarps = 2;              // blur warps that turn into copy warps once the blur role is done
 constexpr int kBlurThreads = kBlurWarps * 32;
 constexpr int kCopyThreads = kCopyWarps * 32;
 constexpr int kThreads = kBlurThreads + kCopyThreads;   // 640 -> 96 registers per thread
@@ -164,11 +164,8 @@ __device__ __forceinline__ void copy_prefetch(const K1Params &p, long long R, un
 // per-CTA finish times of a static split spread by +-20 % (measured, tools/k1_cta_times.py) because the
 // warp's pace is set by how fast ITS stores drain, so the split has to follow the pace.  The warp always
 // holds two grabbed items: the one it expands and the one whose bulk load is in flight.
-// nslots = replication slots of this warp: 2 (the dedicated warp: the stores of item k drain while item k+1 is expanded)
-// or 1 (helper warps in "k1_helpers" mode 1: a slot is 25 KB, so three single-slot helpers fit where two double-slot
-// ones did; the raw chunks stay double-buffered either way).
 __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, unsigned char *raws, int raw_bytes,
-                          uint64_t *bars, int lane, int nslots) {
+                          uint64_t *bars, int lane) {
     const int H = 4 * p.h, W = 4 * p.w;
     const size_t total_bytes = (size_t)p.N * p.h * p.w * (kNetC * 4);
     const long long Rend = (long long)p.N * p.h * p.copy_nchunks;
@@ -197,12 +194,9 @@ __device__ void copy_role(const K1Params &p, float *cslots, int slot_floats, uns
             Rnn = atomicAdd(queue, 1);                     // consumed at the end of this iteration
         }
         const CopyItem ci = copy_item(p, R);
-        float *sh = cslots + (size_t)(nslots == 2 ? b : 0u) * slot_floats;      // heat part: tc*76 floats
+        float *sh = cslots + (size_t)b * slot_floats;      // heat part: tc*76 floats
         float *sp = sh + ci.tc * 4 * kHeatC;               // paf part:  tc*152 floats
-        if (lane == 0) {                                   // the stores that last used THIS slot have drained
-            if (nslots == 2) bulk_wait_read1();
-            else bulk_wait_read0();
-        }
+        if (lane == 0) bulk_wait_read1();                  // the stores that last used THIS slot have drained
         mbar_wait(&bars[b], (k >> 1) & 1u);                // the chunk has landed in raw[b]
         __syncwarp();
         const unsigned char *rawb = raws + (size_t)b * raw_bytes;
@@ -677,15 +671,12 @@ __global__ void __launch_bounds__(DENSE ? kThreads : kMinThreads, DENSE ? 1 : kM
             // idle: the first kHelperWarps blur warps carve them into staging buffers and pull copy items from
             // the same queue as the copy warp until it is empty.
             named_bar(1, kBlurThreads);                   // every blur warp is past its last slot access; stores drained
-            // helper_mode 0: two helpers with two replication slots each; 1: as many single-slot helpers as fit (<= 4)
-            const int hslots_n = p.helper_mode ? 1 : 2;
-            const size_t cw_bytes_h = (size_t)hslots_n * cslot_floats * 4 + 2 * (size_t)raw_bytes;
+            const size_t cw_bytes_h = 2 * (size_t)cslot_floats * 4 + 2 * (size_t)raw_bytes;
             const int fit = (int)((2 * (size_t)pslot_floats * 4) / cw_bytes_h);
-            const int nhelp = p.helper_mode ? min(kHelperWarps, fit) : min(2, fit);
-            if (warp < nhelp) {
+            if (warp < kHelperWarps && warp < fit) {
                 float *hslots = reinterpret_cast<float *>(reinterpret_cast<unsigned char *>(pslots) + warp * cw_bytes_h);
-                unsigned char *hraws = reinterpret_cast<unsigned char *>(hslots + (size_t)hslots_n * cslot_floats);
-                copy_role(p, hslots, cslot_floats, hraws, raw_bytes, bars_all + 2 * (kCopyWarps + warp), lane, hslots_n);
+                unsigned char *hraws = reinterpret_cast<unsigned char *>(hslots + 2 * (size_t)cslot_floats);
+                copy_role(p, hslots, cslot_floats, hraws, raw_bytes, bars_all + 2 * (kCopyWarps + warp), lane);
                 if (lane == 0) bulk_wait_all();
             }
         }
@@ -694,7 +685,7 @@ __global__ void __launch_bounds__(DENSE ? kThreads : kMinThreads, DENSE ? 1 : kM
         if (DENSE && (p.debug_roles & 2)) {
             float *cslots = reinterpret_cast<float *>(cbase + cw * cw_bytes);
             unsigned char *raws = reinterpret_cast<unsigned char *>(cslots + 2 * (size_t)cslot_floats);
-            copy_role(p, cslots, cslot_floats, raws, raw_bytes, bars_all + 2 * cw, lane, 2);
+            copy_role(p, cslots, cslot_floats, raws, raw_bytes, bars_all + 2 * cw, lane);
             if (lane == 0) bulk_wait_all();
 #ifdef TFPD_CHECKED
             if (lane == 0) TFPD_CHK(guard_ok(g_slots) && guard_ok(g_copy));

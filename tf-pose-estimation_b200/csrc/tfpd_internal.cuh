@@ -136,7 +136,6 @@ struct K1Params {
     float wp[4][8];                     // polyphase smoother weights: phase p, low-res tap t (cell offset t-3)
     float2 wh[2][8];                    // the same weights paired over two adjacent x phases: wh[q][t] = {wp[2q][t], wp[2q+1][t]}
                                         // (packed operand of the horizontal pass's FFMA2)
-    int helper_mode;                    // dense mode, blur warps turned copy helpers: 0 two double-slot helpers, 1 up to four single-slot ones
     int min_band;                       // minimal mode: low-res rows per work item of the dynamic queue
     float dead_bound;                   // minimal mode: a low-res window whose largest heat value is below this cannot
                                         // produce a blurred value near the heat threshold (k1_fused.cu, early-out)
