@@ -40,9 +40,12 @@ constexpr int kBlurThreads = kBlurWarps * 32;
 constexpr int kCopyThreads = kCopyWarps * 32;
 constexpr int kThreads = kBlurThreads + kCopyThreads;   // 640 -> 96 registers per thread
 // minimal mode (blur role alone): small CTAs, several per SM -- 6 warps x 4 CTAs = 24 warps per SM at <= 85 registers
-constexpr int kMinWarps = 6;
+#ifndef TFPD_MIN_WARPS
+#define TFPD_MIN_WARPS 6                    // (a build with 3 warps x 8 CTAs per SM was measured against this one: profiles/README.md)
+#endif
+constexpr int kMinWarps = TFPD_MIN_WARPS;
 constexpr int kMinThreads = kMinWarps * 32;
-constexpr int kMinCtasPerSm = 4;
+constexpr int kMinCtasPerSm = 24 / kMinWarps;
 // a warp pass owns at most 32*CPL-8 = 56 cells (see launch_k1_fused_f4: chunk_cells <= 56)
 constexpr int NPX = 4 * CPL;                // output pixels per lane per row
 
