@@ -20,16 +20,6 @@ namespace tfpd {
 
 namespace {
 
-// COCOPAIRS (pafprocess.h:16-19) as compile-time functions: the register-resident assembly below needs the
-// part columns of a limb as constants so that the row registers are indexed statically.
-__host__ __device__ constexpr int limb_pa(int l) {
-    constexpr int t[kLimbs] = {1, 1, 2, 3, 5, 6, 1, 8, 9, 1, 11, 12, 1, 0, 14, 0, 15, 2, 5};
-    return t[l];
-}
-__host__ __device__ constexpr int limb_pb(int l) {
-    constexpr int t[kLimbs] = {2, 5, 3, 4, 6, 7, 8, 9, 10, 11, 12, 13, 0, 14, 16, 15, 17, 16, 17};
-    return t[l];
-}
 constexpr int kWarpSortMax = 1024;           // longest limb segment a single warp sorts
 constexpr int kRegRowsMax = 128;            // subset rows held in registers (4 per lane) before spilling to smem
 
