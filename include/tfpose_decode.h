@@ -232,9 +232,9 @@ TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, s
  *   "fuse_sort"    1 (default): the limb-scoring kernel ranks the unordered peak records itself (every CTA of a frame
  *                  counts smaller keys in shared memory, CTA 0 writes the table); 0: a sort kernel of its own runs in
  *                  front of it.  Same tables.
- *   "graph"        1: tfpd_decode_device replays a CUDA graph of the whole decode (counter reset, the four kernels,
+ *   "graph"        1: tfpd_decode_device replays a CUDA graph of the whole decode (counter reset, the three kernels,
  *                  the table copy) captured once per distinct argument set (x4 path, profiling off, up to 16
- *                  cached): one launch instead of seven stream operations.  Same results.
+ *                  cached): one launch instead of six stream operations.  Same results.
  *   "k1_turnstile" 1: the map kernels of all contexts on this device run one after the other (stream-ordered through
  *                  a per-device event), whatever their streams.  With several contexts in flight this keeps a
  *                  second HBM-bound map kernel from starting on the SMs "k1_ctas" leaves to the tail kernels.
