@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
     int16_t *s_py = s_px + ws.max_peaks;
     __shared__ int s_first[kHeatC + 1];
     __shared__ int s_tstart[kLimbs + 1];
+    __shared__ unsigned char s_owner[kK2Threads / 32][32];      // per warp: lane owning the k-th surviving pair of the pass
     const int n = blockIdx.y;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (ws.k2_fused_sort) {
@@ -237,15 +238,21 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
             }
             meta = c_limb_chan[limb][0] | (keep ? 0x100 : 0);
         }
-        // the scoring phase walks the SURVIVORS only: sub-step t, slot s takes the (3t+s)-th lane whose pair is kept
+        // the scoring phase walks the SURVIVORS only: sub-step t, slot s takes the (3t+s)-th lane whose pair is kept.
+        // Every surviving lane publishes its lane id at its rank in a per-warp table (one store; __fns -- a software
+        // loop -- looked the owner up twice per sub-step before and was 27 % of the kernel's instructions, ncu r02m).
+        __syncwarp();                                                                     // last pass's readers are done
         const unsigned alive = __ballot_sync(FULL, pvalid && (meta & 0x100));
+        if (pvalid && (meta & 0x100)) s_owner[warp][__popc(alive & ((1u << lane) - 1u))] = (unsigned char)lane;
+        __syncwarp();
         const int npass = __popc(alive);                                                  // warp-uniform
         const int nsub = (npass + kPairsPerWarp - 1) / kPairsPerWarp;
 
         // ---- scoring (10 lanes per pair) ----
-        auto fetch = [&](int t, float &o_vx, float &o_vy, float &o_pvx, float &o_pvy, bool &o_ok) {
+        auto fetch = [&](int t, float &o_vx, float &o_vy, float &o_pvx, float &o_pvy, bool &o_ok, int &o_owner) {
             const int rank = kPairsPerWarp * t + slot;
-            const int owner = (slot < kPairsPerWarp && rank < npass) ? (int)__fns(alive, 0, rank + 1) : 0;
+            const int owner = (slot < kPairsPerWarp && rank < npass) ? (int)s_owner[warp][rank] : 0;
+            o_owner = owner;
             const int g_xy = __shfl_sync(FULL, xy1, owner);
             const int g_meta = __shfl_sync(FULL, meta, owner);
             const float g_sx = __shfl_sync(FULL, stepx, owner), g_sy = __shfl_sync(FULL, stepy, owner);
@@ -269,28 +276,41 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
         };
         float c_vx, c_vy, c_pvx, c_pvy;
         bool c_ok;
-        fetch(0, c_vx, c_vy, c_pvx, c_pvy, c_ok);
+        int c_owner;
+        fetch(0, c_vx, c_vy, c_pvx, c_pvy, c_ok, c_owner);
         for (int t = 0; t < nsub; ++t) {
             float n_vx = 0.f, n_vy = 0.f, n_pvx = 0.f, n_pvy = 0.f;
             bool n_ok = false;
-            if (t + 1 < nsub) fetch(t + 1, n_vx, n_vy, n_pvx, n_pvy, n_ok);
+            int n_owner = 0;
+            if (t + 1 < nsub) fetch(t + 1, n_vx, n_vy, n_pvx, n_pvy, n_ok, n_owner);
             const float s = c_ok ? __fadd_rn(__fmul_rn(c_vx, c_pvx), __fmul_rn(c_vy, c_pvy)) : 0.f;   // :77
             // scores += score, i = 0..9, in order (:78); criterion1 counts score > THRESH_VECTOR_SCORE (:80)
             float total_s = 0.0f;
 #pragma unroll
             for (int k = 0; k < kStepPaf; ++k) total_s = __fadd_rn(total_s, __shfl_sync(FULL, s, (group_base + k) & 31));
             const int hits = __popc(__ballot_sync(FULL, s > th.vector_score) & group_mask);
-            const int rank = kPairsPerWarp * t + slot;
-            const int owner = (slot < kPairsPerWarp && rank < npass) ? (int)__fns(alive, 0, rank + 1) : 0;
+            const int owner = c_owner;
             const float g_norm = __shfl_sync(FULL, norm, owner);
             const int g_lab = __shfl_sync(FULL, lab, owner);
+            bool accept = false;
+            float crit2 = 0.0f;
             if (c_ok && i == 0 && hits > th.vector_cnt1) {                        // first half of :85
                 // float criterion2 = scores / STEP_PAF + min(0.0, 0.5 * h1 / norm - 1.0);   (:83)
                 const double pen = 0.5 * (double)src.H / (double)g_norm - 1.0;
                 const double d = (double)__fdiv_rn(total_s, (float)kStepPaf) + (pen < 0.0 ? pen : 0.0);
-                const float crit2 = (float)d;
-                if (crit2 > 0.0f) {                                                // second half of :85
-                    int idx = atomicAdd(&ws.counters[n].n_cand, 1);
+                crit2 = (float)d;
+                accept = crit2 > 0.0f;                                             // second half of :85
+            }
+            // one atomic per sub-step for all (up to three) accepted pairs of the warp: the list is unordered (the
+            // assembly kernel sorts it by key), each accepted lane takes its offset by rank
+            const unsigned am = __ballot_sync(FULL, accept);
+            if (am) {
+                const int leader = __ffs(am) - 1;
+                int base = 0;
+                if (lane == leader) base = atomicAdd(&ws.counters[n].n_cand, __popc(am));
+                base = __shfl_sync(FULL, base, leader);
+                if (accept) {
+                    const int idx = base + __popc(am & ((1u << lane) - 1u));
                     if (idx < ws.max_cands) {
                         // ascending key order == (limb asc, score desc, idx1 asc, idx2 asc)
                         unsigned long long key = ((unsigned long long)(g_lab >> 24) << 56) |
@@ -305,6 +325,7 @@ __global__ void __launch_bounds__(kK2Threads) k_limb_score(Workspace ws, PafSour
             c_pvx = n_pvx;
             c_pvy = n_pvy;
             c_ok = n_ok;
+            c_owner = n_owner;
         }
     }
 }
