@@ -60,9 +60,11 @@ enum {
 
 /* per-frame flag bits (tfpd_frame_info.flags) */
 enum {
-    TFPD_FLAG_SCORE_TIE = 1,       /* two candidates of one limb have bit-equal scores: the reference's
-                                      order is then decided by libstdc++ introsort internals
-                                      (pafprocess.cpp:97); this library orders (score desc, idx1, idx2) */
+    TFPD_FLAG_SCORE_TIE = 1,       /* two candidates of one limb have bit-equal scores: the reference's order is then
+                                      what libstdc++'s std::sort makes of the order the candidates were generated in
+                                      (pafprocess.cpp:57-60,97).  Informational: the library reproduces that order
+                                      (option "std_sort_ties", on by default); with the option off it orders
+                                      (score desc, idx1, idx2) */
     TFPD_FLAG_FOUND_GT2 = 2,       /* a connection matched >2 subset rows and was dropped (pafprocess.cpp:136-141) */
     TFPD_FLAG_PEAK_OVERFLOW = 4,
     TFPD_FLAG_CAND_OVERFLOW = 8,
@@ -225,6 +227,11 @@ TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, s
  *   "k1_l2"        bit 1: evict-first stores (default 2); bit 0 is reserved (a bulk L2 prefetch of the input at
  *                  kernel start measured slower and was taken out again).
  *   "k2_blocks"    CTAs of the limb-scoring kernel per frame; 0 = automatic (about 6 CTAs per SM over the batch).
+ *   "std_sort_ties" 1 (default): a limb whose candidates include bit-equal scores is ordered by a literal restatement of
+ *                  libstdc++'s std::sort (introsort: median-of-3, unguarded partition, 16-element insertion-sort
+ *                  threshold, heap-sort fallback) applied to the candidates in the reference's generation order -- the
+ *                  order pafprocess.cpp:97 produces, so the greedy step accepts what the reference accepts.  0: the
+ *                  total order (score desc, idx1 asc, idx2 asc).  Frames without such ties are unaffected.
  *   "k2_prefilter" 1 (default): the limb-scoring kernel scores the first 10 - thresh_vector_cnt1 samples of a candidate
  *                  pair (4 with the reference's constants) in its per-pair set-up and drops the pair when none of them
  *                  exceeds thresh_vector_score: it could no longer reach "more than thresh_vector_cnt1 of 10"

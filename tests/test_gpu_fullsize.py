@@ -89,7 +89,7 @@ def _run_properties(torch, oracle, N, h, w, cfg, people, n_unique, spot, **caps)
 
     # oracle spot check
     for i in range(spot):
-        R, (_, _, _, g) = oracle.decode_frame(x[i], H, W, sort="total")
+        R, (_, _, _, g) = oracle.decode_frame(x[i], H, W, sort="std")
         if int(oracle.fragile_pixels(g).sum()) or int(res.info["near_ties"][i]):
             continue
         ok, why = humans_equal(res.humans(i), R.humans_as_tuples(), H, W)

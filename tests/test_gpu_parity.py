@@ -52,9 +52,9 @@ def check_frames(torch, oracle, x, factor, mode="asbuilt", dense_mode=True, fram
                GPU's own peak set: in dense mode the oracle's process_paf is fed the GPU's three dense
                tensors; in minimal mode (no dense tensors exist) it is fed the oracle's heat_up / paf_up
                (bit-exact replicas either way) and a peaks tensor rebuilt from the GPU's peak table.
-    Every frame whose limb scores have no bit-equal tie (TFPD_FLAG_SCORE_TIE clear: libstdc++'s order then
-    cannot matter) is ALSO decoded by the reference's own compiled pafprocess.cpp (oracle/_ref) from the
-    same three maps, and the GPU's humans must equal its getters' answers one for one.
+    Every frame is ALSO decoded by the reference's own compiled pafprocess.cpp (oracle/_ref) from the same three
+    maps, and the GPU's humans must equal its getters' answers one for one -- bit-equal score ties included: the
+    library orders them with a literal std::sort ("std_sort_ties"), and the oracle runs in its std::sort mode.
     Returns (#exact, #decomposed); ``check_frames.ref_compared`` counts the frames the reference binary saw."""
     N, h, w, _ = x.shape
     H, W = factor * h, factor * w
@@ -64,7 +64,7 @@ def check_frames(torch, oracle, x, factor, mode="asbuilt", dense_mode=True, fram
     res = dec.decode(xd, (H, W), dense=dense)
     exact = decomposed = 0
     for i in (range(N) if frames is None else frames):
-        R, (peaks, heat_up, paf_up, g) = oracle.decode_frame(x[i], H, W, mode=mode, sort="total")
+        R, (peaks, heat_up, paf_up, g) = oracle.decode_frame(x[i], H, W, mode=mode, sort="std")
         frag_map = oracle.fragile_pixels(g)
         fragile = int(frag_map.sum())
         if dense_mode:
@@ -83,7 +83,7 @@ def check_frames(torch, oracle, x, factor, mode="asbuilt", dense_mode=True, fram
                 ref_maps = (gp, hu_g, pu_g)                                          # the GPU's own maps
             else:
                 ref_maps = (peaks_tensor_from_table(pk, H, W), heat_up, paf_up)      # the GPU's own peak set
-            R = oracle.process_paf(*ref_maps, mode=mode, sort="total")
+            R = oracle.process_paf(*ref_maps, mode=mode, sort="std")
         else:
             ref_maps = (peaks, heat_up, paf_up)
         assert int(res.info["n_peaks"][i]) == len(R.peaks["x"])
@@ -93,12 +93,13 @@ def check_frames(torch, oracle, x, factor, mode="asbuilt", dense_mode=True, fram
         assert ok, "frame %d: %s" % (i, why)
         assert bool(res.info["flags"][i] & 1) == bool(R.flags & 1), "score-tie flag differs"
         assert int(res.info["n_rows"][i]) == R.rows_unfiltered
-        if not (int(res.info["flags"][i]) & 1):
-            ref = reference_binary(oracle, mode)
-            ref.process_paf(*ref_maps)
-            ok, why = humans_equal(res.humans(i), ref.humans_as_tuples(), H, W)
-            assert ok, "frame %d vs the reference binary (%s): %s" % (i, mode, why)
-            check_frames.ref_compared += 1
+        # the reference's own compiled pafprocess.cpp, on every frame: bit-equal score ties are ordered the way its
+        # std::sort orders them ("std_sort_ties", on by default)
+        ref = reference_binary(oracle, mode)
+        ref.process_paf(*ref_maps)
+        ok, why = humans_equal(res.humans(i), ref.humans_as_tuples(), H, W)
+        assert ok, "frame %d vs the reference binary (%s): %s" % (i, mode, why)
+        check_frames.ref_compared += 1
         if fragile:
             decomposed += 1
         else:

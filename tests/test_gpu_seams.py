@@ -67,9 +67,7 @@ def test_pafprocess_module_vs_reference_binary_on_dense_maps(cuda, oracle, mode)
             assert want == R.humans_as_tuples()
         else:
             want = R.humans_as_tuples()
-        if R.flags & 1:
-            want = oracle.process_paf(pk, hu, pu, mode=mode, sort="total").humans_as_tuples()
-        got = _module_humans()
+        got = _module_humans()      # bit-equal score ties included: the library orders them like std::sort does
         assert [(np.float32(s), p) for s, p in got] == \
                [(np.float32(s), {k: (x_, y_, float(np.float32(v))) for k, (x_, y_, v) in p.items()}) for s, p in want]
     pafprocess.configure(mode="asbuilt")
@@ -77,12 +75,14 @@ def test_pafprocess_module_vs_reference_binary_on_dense_maps(cuda, oracle, mode)
 
 @pytest.mark.parametrize("mode", ["asbuilt", "upstream"])
 def test_pafprocess_random_dense_with_exact_ties(cuda, oracle, mode):
-    """Quantised random dense maps: exact score ties, > 16 candidates per limb, found == 2 and
-    found > 2.  With ties the reference's order is libstdc++-internal; the library documents
-    (score desc, idx1, idx2) and must raise TFPD_FLAG_SCORE_TIE -- compare with the oracle run in
-    that total order, and with the std::sort order whenever no tie is flagged."""
+    """Quantised random dense maps: exact score ties, > 16 candidates per limb, found == 2 and found > 2.  With ties
+    the reference's order is what libstdc++'s std::sort makes of the generation order (pafprocess.cpp:97).  By default
+    ("std_sort_ties" = 1) the library reproduces it: humans equal the oracle's run with the real std::sort AND the
+    reference's own compiled pafprocess.cpp on EVERY seed, tied or not, and TFPD_FLAG_SCORE_TIE is still raised.  With
+    the option off the documented total order (score desc, idx1, idx2) applies: equal to the oracle run in that order."""
     pafprocess.configure(mode=mode)
-    seen_tie = seen_gt2 = 0
+    ref = oracle.ReferencePafprocess(mode)
+    seen_tie = seen_gt2 = differ = 0
     for seed in range(12):
         rng = np.random.default_rng(100 + seed)
         H, W = 40, 48
@@ -92,22 +92,28 @@ def test_pafprocess_random_dense_with_exact_ties(cuda, oracle, mode):
         peaks[ys, xs, cs] = (rng.integers(1, 5, n) / 4.0).astype(np.float32)
         heat = peaks + np.float32(0.125)
         paf = (rng.integers(-2, 3, (H, W, 38)) / 2.0).astype(np.float32)
-        pafprocess.process_paf(peaks, heat, paf)
-        d = pafprocess._ctx()
-        info = d.fetch().info[0]
+        norm = lambda hs: [(np.float32(s), {k: (a, b, float(np.float32(v))) for k, (a, b, v) in p.items()}) for s, p in hs]
         Rt = oracle.process_paf(peaks, heat, paf, mode=mode, sort="total")
-        assert bool(info["flags"] & 1) == bool(Rt.flags & 1)
-        assert bool(info["flags"] & 2) == bool(Rt.flags & 2)
+        Rs = oracle.process_paf(peaks, heat, paf, mode=mode, sort="std")
+        ref.process_paf(peaks, heat, paf)
+        assert norm(ref.humans_as_tuples()) == norm(Rs.humans_as_tuples())          # the oracle's std mode IS the reference
+        d = pafprocess._ctx()
+        for std_ties, want in ((1, Rs), (0, Rt)):
+            d.set_option("std_sort_ties", std_ties)
+            pafprocess.process_paf(peaks, heat, paf)
+            info = d.fetch().info[0]
+            assert bool(info["flags"] & 1) == bool(Rt.flags & 1)
+            assert bool(info["flags"] & 2) == bool(want.flags & 2)
+            got = [(np.float32(s), p) for s, p in _module_humans()]
+            assert got == norm(want.humans_as_tuples()), (mode, seed, std_ties)
+        d.set_option("std_sort_ties", 1)
         seen_tie += int(info["flags"] & 1)
         seen_gt2 += int(bool(info["flags"] & 2))
-        got = [(np.float32(s), p) for s, p in _module_humans()]
-        want = [(np.float32(s), {k: (a, b, float(np.float32(v))) for k, (a, b, v) in p.items()})
-                for s, p in Rt.humans_as_tuples()]
-        assert got == want, (mode, seed)
+        differ += int(norm(Rs.humans_as_tuples()) != norm(Rt.humans_as_tuples()))
         if not (Rt.flags & 1):
-            Rs = oracle.process_paf(peaks, heat, paf, mode=mode, sort="std")
             assert Rs.humans_as_tuples() == Rt.humans_as_tuples()
     assert seen_tie > 0
+    print("exact-tie seeds: %d of 12 flagged, %d where the reference's order and the total order give different humans" % (seen_tie, differ))
     pafprocess.configure(mode="asbuilt")
 
 
@@ -132,7 +138,7 @@ def test_post_processor_numpy_and_cuda_inputs(cuda, oracle):
     humans + heatMat / pafMat side effects (estimator.py:544-551), NumPy (host) and CUDA inputs."""
     import torch
     x = synth.synth_batch(1, 46, 54, config_id=2, first_frame=2)
-    R, (peaks, heat_up, paf_up, g) = oracle.decode_frame(x[0], 184, 216, sort="total")
+    R, (peaks, heat_up, paf_up, g) = oracle.decode_frame(x[0], 184, 216, sort="std")
     assert int(oracle.fragile_pixels(g).sum()) == 0
     pp = tp.TfPosePostProcessor(target_size=(432, 368))
     humans = pp.inference_from_output(x, upsample_size=4.0)
@@ -164,7 +170,7 @@ def test_general_resize_area_ratios(cuda, oracle, ratio):
     res_min = dec.decode(torch.from_numpy(x).cuda(), (H, W))
     assert np.array_equal(res.info, res_min.info)
     for i in range(2):
-        R, (peaks, heat_up, paf_up, g) = oracle.decode_frame(x[i], H, W, sort="total")
+        R, (peaks, heat_up, paf_up, g) = oracle.decode_frame(x[i], H, W, sort="std")
         assert rel_err(dense[0][i].cpu().numpy(), heat_up, heat_up) <= 1e-5
         assert rel_err(dense[1][i].cpu().numpy(), paf_up, paf_up) <= 1e-5
         gp = dense[2][i].cpu().numpy()
@@ -173,7 +179,7 @@ def test_general_resize_area_ratios(cuda, oracle, ratio):
         # the discrete stages must be bit-exact GIVEN the maps: the oracle's process_paf fed with the
         # GPU's own dense tensors reproduces the GPU's humans (covers inexact ratios and near-ties)
         hu_g, pu_g = dense[0][i].cpu().numpy(), dense[1][i].cpu().numpy()
-        R2 = oracle.process_paf(gp, hu_g, pu_g, sort="total")
+        R2 = oracle.process_paf(gp, hu_g, pu_g, sort="std")
         ok, why = humans_equal(res.humans(i), R2.humans_as_tuples(), H, W)
         assert ok, (ratio, i, why)
         if fragile == 0 and np.array_equal(hu_g, heat_up) and np.array_equal(pu_g, paf_up):

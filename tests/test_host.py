@@ -474,3 +474,56 @@ def test_bench_config_table_matches_the_baseline_configs():
     assert bench.dense_bytes_per_frame(92, 164) == 76828096
     assert abs(bench.polyphase_flops_per_frame(46, 54) / 13.2e6 - 1) < 0.01   # "polyphase: ~13.2 MFLOP" per frame
     assert C["c4"]["people"] == 30
+
+
+def test_literal_std_sort_matches_libstdcxx(tmp_path):
+    """csrc/std_sort_literal.h (the assembly kernel's order for limb candidates with bit-equal scores) against the REAL
+    std::sort with the reference's comparator (pafprocess.cpp:97,239-241), compiled together into a small harness
+    (tests/native/std_sort_harness.cpp): identical element order on tie-heavy arrays in generation order, on sorted /
+    reversed / organ-pipe / all-equal inputs around the 16-element insertion-sort threshold, and on Musser's
+    median-of-3 killer sequences, which must reach the depth-limit heap-sort fallback."""
+    import ctypes as C
+    import subprocess
+    so = str(tmp_path / "std_sort_harness.so")
+    subprocess.run(["g++", "-O2", "-std=c++14", "-fPIC", "-shared", "-o", so,
+                    os.path.join(ROOT, "tests", "native", "std_sort_harness.cpp")], check=True)
+    L = C.CDLL(so)
+    P = np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")
+    L.harness_literal_sort.argtypes = [P, C.c_int]
+    L.harness_std_sort.argtypes = [P, C.c_int]
+    rng = np.random.default_rng(1)
+
+    def keys_of(scores, limb=7):
+        n = len(scores)
+        bits = np.asarray(scores, np.float32).view(np.uint32).astype(np.uint64)
+        nb = int(np.ceil(np.sqrt(max(n, 1)))) + 1
+        idx = np.arange(n, dtype=np.uint64)
+        return (np.uint64(limb) << np.uint64(56)) | ((np.uint64(0xffffffff) - bits) << np.uint64(24)) | \
+               ((idx // np.uint64(nb)) << np.uint64(12)) | (idx % np.uint64(nb))
+
+    def same(k):
+        a, b = k.copy(), k.copy()
+        L.harness_literal_sort(a, len(k))
+        L.harness_std_sort(b, len(k))
+        return np.array_equal(a, b)
+
+    checked = 0
+    for n in list(range(0, 40)) + [63, 64, 65, 129, 500, 1024, 4096]:
+        for levels in (1, 2, 5, 1000):
+            r = rng.integers(1, levels + 1, n)
+            half = np.arange(n // 2)
+            organ = (np.concatenate([half, half[::-1], np.zeros(n - 2 * (n // 2), int)])[:n] + 1) if n else r
+            for sc in (r, np.sort(r), np.sort(r)[::-1], organ):
+                assert same(keys_of(np.asarray(sc, np.float32) / np.float32(max(levels, n, 1)))), (n, levels)
+                checked += 1
+    before = L.harness_heap_sort_calls()
+    for n in (256, 1024, 4096):
+        k = n // 2
+        v = np.zeros(n)
+        for i in range(1, k + 1):                       # Musser 1997
+            v[i - 1] = i if i % 2 == 1 else k + i - 1
+            v[k + i - 1] = 2 * i
+        for seq in (v, v.max() + 1 - v):
+            assert same(keys_of((seq / (n + 2.0)).astype(np.float32), limb=3)), n
+    assert L.harness_heap_sort_calls() - before >= 6, "the killer sequences did not reach the heap-sort fallback"
+    assert checked > 500

@@ -392,6 +392,7 @@ int tfpd_create(const tfpd_config *cfg, tfpd_ctx **out) {
     if (const char *e = getenv("TFPD_K2_BPF")) w.k2_blocks_per_frame = atoi(e);
     w.k3_warp_sort_max = 1024;
     w.k3_parallel_limbs = 1;
+    w.k3_std_ties = 1;
     if (const char *e = getenv("TFPD_K3_PARALLEL")) w.k3_parallel_limbs = atoi(e) != 0;
     if (const char *e = getenv("TFPD_K3_WARPSORT")) w.k3_warp_sort_max = atoi(e);
     if (const char *e = getenv("TFPD_K3_REGROWS")) w.k3_reg_rows = atoi(e) < 0 ? 0 : atoi(e);
@@ -675,6 +676,8 @@ int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value) {
         ctx->ws.k2_blocks_per_frame = value;
     } else if (!strcmp(name, "fuse_sort")) {
         ctx->ws.k2_fused_sort = value != 0;
+    } else if (!strcmp(name, "std_sort_ties")) {
+        ctx->ws.k3_std_ties = value != 0;
     } else if (!strcmp(name, "k2_prefilter")) {
         ctx->ws.k2_prefilter = value != 0;
     } else if (!strcmp(name, "graph")) {

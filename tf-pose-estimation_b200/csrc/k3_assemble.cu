@@ -15,6 +15,7 @@
 #include <cstdlib>
 
 #include "tfpd_internal.cuh"
+#include "std_sort_literal.h"
 
 namespace tfpd {
 
@@ -25,6 +26,29 @@ constexpr int kRegRowsMax = 128;            // subset rows held in registers (4 
 
 constexpr int kK3Threads = 640;             // 20 warps: 19 greedy walkers + sort helpers
 constexpr int kBitmapWords = kMaxPeaksHard / 32;   // 128
+
+// bitonic network with a mirrored first stage per block, one warp, ascending: every comparator puts the smaller key at
+// the lower index, so the (virtual) +inf padding beyond the segment never moves and is simply skipped
+__device__ void warp_bitonic(unsigned long long *seg, int len, int lane) {
+    int np2 = 1;
+    while (np2 < len) np2 <<= 1;
+    for (int k = 2; k <= np2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const int mask = (j == (k >> 1)) ? (k - 1) : j;
+            for (int i = lane; i < len; i += 32) {
+                const int l = i ^ mask;
+                if (l > i && l < len) {
+                    const unsigned long long a = seg[i], b = seg[l];
+                    if (a > b) {
+                        seg[i] = b;
+                        seg[l] = a;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+    }
+}
 
 // MINB = CTAs per SM the register allocation allows: 1 -> 78 registers, 2 -> 48 registers (no spills either way).
 // The kernel is a latency-bound chain per frame (issue slots ~27 % busy with one CTA per SM), so two co-resident
@@ -110,30 +134,7 @@ __global__ void __launch_bounds__(kK3Threads, MINB) k_assemble(Workspace ws, Thr
     __syncthreads();
     if (ws.dbg_times && tid == 0 && n < 64) ws.dbg_times[2048 + n * 8 + 2] = clock64();
     if (s_maxseg <= min(kWarpSortMax, ws.k3_warp_sort_max)) {
-        // bitonic network with a mirrored first stage per block: every comparator puts the smaller key at the
-        // lower index, so the (virtual) +inf padding beyond the segment never moves and is simply skipped
-        if (warp < kLimbs) {
-            unsigned long long *seg = keys + s_lstart[warp];
-            const int len = s_lcount[warp];
-            int np2 = 1;
-            while (np2 < len) np2 <<= 1;
-            for (int k = 2; k <= np2; k <<= 1) {
-                for (int j = k >> 1; j > 0; j >>= 1) {
-                    const int mask = (j == (k >> 1)) ? (k - 1) : j;
-                    for (int i = lane; i < len; i += 32) {
-                        const int l = i ^ mask;
-                        if (l > i && l < len) {
-                            const unsigned long long a = seg[i], b = seg[l];
-                            if (a > b) {
-                                seg[i] = b;
-                                seg[l] = a;
-                            }
-                        }
-                    }
-                    __syncwarp();
-                }
-            }
-        }
+        if (warp < kLimbs) warp_bitonic(keys + s_lstart[warp], s_lcount[warp], lane);
     } else {
         // a very long segment (one limb with > kWarpSortMax candidates): frame-wide bitonic sort by all threads;
         // the key order (limb first) keeps the segments where they are
@@ -164,6 +165,27 @@ __global__ void __launch_bounds__(kK3Threads, MINB) k_assemble(Workspace ws, Thr
     for (int i = tid + 1; i < cnt; i += kK3Threads)
         if ((keys[i] >> 24) == (keys[i - 1] >> 24)) atomicOr(&s_flags, TFPD_FLAG_SCORE_TIE);
     __syncthreads();
+    if (ws.k3_std_ties && (s_flags & TFPD_FLAG_SCORE_TIE)) {
+        // Rare path.  A limb segment with bit-equal scores is put back into the order the reference pushed its
+        // candidates in (idx1, idx2 ascending = the key's low 24 bits, unique within a limb: the same warp network on
+        // the key rotated by 24 bits) and then sorted by the literal std::sort above: the reference's own order.
+        if (warp < kLimbs) {
+            unsigned long long *seg = keys + s_lstart[warp];
+            const int len = s_lcount[warp];
+            bool tie = false;
+            for (int i = lane + 1; i < len; i += 32) tie |= (seg[i] >> 24) == (seg[i - 1] >> 24);
+            if (__any_sync(0xffffffffu, tie)) {
+                for (int i = lane; i < len; i += 32) seg[i] = (seg[i] << 40) | (seg[i] >> 24);
+                __syncwarp();
+                warp_bitonic(seg, len, lane);
+                for (int i = lane; i < len; i += 32) seg[i] = (seg[i] >> 40) | (seg[i] << 24);
+                __syncwarp();
+                if (lane == 0) std_sort_literal(seg, len);
+                __syncwarp();
+            }
+        }
+        __syncthreads();
+    }
 
     // ---- 2. greedy matching (:98-124), one warp per limb ----
     // The walk over the sorted candidates is serial only in the ACCEPTED ones: a window of 32 candidates is

@@ -91,6 +91,7 @@ struct Workspace {
     int k3_warp_sort_max;       // longest limb segment sorted by one warp (1024; TFPD_K3_WARPSORT lowers it for tests)
     int k3_parallel_limbs;      // 1: whole-limb assembly steps where provably order-free (TFPD_K3_PARALLEL=0 turns them off)
     int k3_reg_rows;
+    int k3_std_ties;            // 1: limb segments with bit-equal scores are ordered by a literal std::sort (the reference's order)
 #ifdef TFPD_CHECKED
     int dbg_trip;            // checked build only, TFPD_CHECKED_TRIP=1: the assembly kernel writes one element past its key array (negative control)
 #endif

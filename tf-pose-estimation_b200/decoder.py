@@ -414,7 +414,7 @@ class PoseDecoder(object):
         return {"limb": limb[:k].copy(), "cid1": c1[:k].copy(), "cid2": c2[:k].copy(), "score": score[:k].copy()}
 
     def set_option(self, name, value):
-        """Tuning options of include/tfpose_decode.h (``k1_ctas``, ``k1_turnstile``, ``k1_early_out``, ``k1_min_band``, ``tail_priority``, ``graph``, ``fuse_sort``, ``k2_prefilter``, ``early_fetch``,
+        """Tuning options of include/tfpose_decode.h (``k1_ctas``, ``k1_turnstile``, ``k1_early_out``, ``k1_min_band``, ``tail_priority``, ``graph``, ``fuse_sort``, ``k2_prefilter``, ``std_sort_ties``, ``early_fetch``,
         ``host_chunks``, ``k1_l2``, ``pow2_path``)."""
         self._check(self._L.tfpd_set_option(self._ctx, name.encode(), int(value)))
 

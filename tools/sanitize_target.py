@@ -47,7 +47,7 @@ def decode_and_check(x, factor, mode="asbuilt", dense_mode=True, options=(), **c
     torch.cuda.synchronize()
     checked = 0
     for i in range(n):
-        R, (peaks, hu, pu, g) = O.decode_frame(x[i], H, W, mode=mode, sort="total")
+        R, (peaks, hu, pu, g) = O.decode_frame(x[i], H, W, mode=mode, sort="std")
         if dense_mode:
             assert np.array_equal(dense[0][i].cpu().numpy(), hu) and np.array_equal(dense[1][i].cpu().numpy(), pu)
         if int(O.fragile_pixels(g).sum()) == 0 and not (R.flags & 1):
@@ -83,7 +83,7 @@ def main():
     from tfpose_b200 import pafprocess as pp
     pk, hu, pu, g = O.dense_maps(x2[0], 184, 216)
     humans = tp.PoseEstimator.estimate_paf(pk, hu, pu)
-    R = O.process_paf(pk, hu, pu, sort="total")
+    R = O.process_paf(pk, hu, pu, sort="std")
     assert len(humans) == len(R.humans_as_tuples())
     pp.configure()
     print("seam 2: %d humans" % len(humans))
