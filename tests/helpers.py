@@ -69,3 +69,34 @@ def check_peaks_tensor(oracle, gp, peaks, g, fragile, what):
         if fragile == 0:
             assert not (mism[..., :18] & (g[..., :18] > 0.05 * (1 - 4e-5))).any(), \
                 "%s: support differs above the heat threshold" % what
+
+
+_TIE_CHAINS = [(1, 2, 3, 4), (1, 5, 6, 7), (1, 8, 9, 10), (1, 11, 12, 13)]   # neck -> shoulder -> elbow -> wrist, neck -> hip -> knee -> ankle
+
+
+def chained_tie_case(seed, H=160, W=120):
+    """Dense (peaks, heat, paf) on which the reference's result DEPENDS on std::sort's order between bit-equal scores
+    (pafprocess.cpp:97): two 4-part chains of the skeleton, each laid out on one horizontal line with every part's peaks
+    in its own x range and a constant PAF (1, 0) on the three limbs' channel pairs along that line.  Every candidate of
+    a limb then has direction (1, 0) and -- the map is tall, so the length penalty of :83 vanishes -- the same score:
+    25..49 bit-equal candidates that compete for the same peaks, more than std::sort's 16-element insertion-sort
+    (stable) range.  Humans have 4 parts, so they pass the reference's compiled-in part-count filter."""
+    from tfpose_b200.common import CocoPairs, CocoPairsNetwork
+    rng = np.random.default_rng(seed)
+    peaks = np.zeros((H, W, 19), np.float32)
+    heat = np.zeros((H, W, 19), np.float32)
+    paf = np.zeros((H, W, 38), np.float32)
+    y = 8
+    for chain in [_TIE_CHAINS[i] for i in rng.permutation(4)[:2]]:
+        for k, part in enumerate(chain):
+            n = int(rng.integers(5, 8))
+            xs = np.sort(rng.choice(np.arange(2 + 30 * k, 28 + 30 * k), n, replace=False))
+            for x in xs:
+                v = np.float32(rng.integers(2, 5) / 4.0)
+                peaks[y, x, part] = v
+                heat[y, x, part] = v
+        for a, b in zip(chain[:-1], chain[1:]):
+            limb = [i for i, p in enumerate(CocoPairs) if tuple(p) == (a, b)][0]
+            paf[y, :, CocoPairsNetwork[limb][0]] = 1.0
+        y += 40
+    return peaks, heat, paf

@@ -117,6 +117,42 @@ def test_pafprocess_random_dense_with_exact_ties(cuda, oracle, mode):
     pafprocess.configure(mode="asbuilt")
 
 
+@pytest.mark.parametrize("mode", ["asbuilt", "upstream"])
+def test_bit_equal_scores_follow_the_reference_std_sort_order(cuda, oracle, mode):
+    """helpers.chained_tie_case: 25..49 bit-equal candidates per limb that compete for the same peaks, where the
+    reference's humans depend on what libstdc++'s introsort makes of the generation order (tests/test_oracle.py pins
+    that premise on the CPU).  By default the library must return the reference binary's humans getter for getter and
+    the connections of the oracle's std::sort run; with "std_sort_ties" = 0 those of the total order -- and the two
+    must differ, or the test would prove nothing."""
+    from helpers import chained_tie_case
+    pafprocess.configure(mode=mode)
+    ref = oracle.ReferencePafprocess(mode)
+    norm = lambda hs: [(np.float32(s), {k: (a, b, float(np.float32(v))) for k, (a, b, v) in p.items()}) for s, p in hs]
+    conns = lambda R: [(l, int(a), int(b), np.float32(sc)) for l in range(19) for a, b, sc in zip(*R.conns[l])]
+    differ = 0
+    for seed in range(10):
+        pk, hu, pu = chained_tie_case(seed)
+        Rs = oracle.process_paf(pk, hu, pu, mode=mode, sort="std")
+        Rt = oracle.process_paf(pk, hu, pu, mode=mode, sort="total")
+        ref.process_paf(pk, hu, pu)
+        d = pafprocess._ctx()
+        for std_ties, want in ((1, Rs), (0, Rt)):
+            d.set_option("std_sort_ties", std_ties)
+            pafprocess.process_paf(pk, hu, pu)
+            info = d.fetch().info[0]
+            assert info["flags"] & 1
+            got = [(np.float32(s), p) for s, p in _module_humans()]
+            assert got == norm(want.humans_as_tuples()), (mode, seed, std_ties)
+            c = d.connections(0)
+            assert list(zip(c["limb"].tolist(), c["cid1"].tolist(), c["cid2"].tolist(), [np.float32(v) for v in c["score"]])) == conns(want)
+            if std_ties:
+                assert got == norm(ref.humans_as_tuples()), "differs from the reference binary (%s, seed %d)" % (mode, seed)
+        d.set_option("std_sort_ties", 1)
+        differ += int(norm(Rs.humans_as_tuples()) != norm(Rt.humans_as_tuples()))
+    assert differ >= 8
+    pafprocess.configure(mode="asbuilt")
+
+
 def test_pafprocess_argument_errors(cuda):
     """swig raises ValueError for ndim != 3 (pafprocess_wrap.cpp:4937); channel-count and shape
     mismatches (unchecked UB in the reference) are rejected with an error here."""

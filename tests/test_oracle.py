@@ -179,3 +179,23 @@ def test_oracle_matches_golden_toy(oracle):
         R = oracle.process_paf(d["peaks"], d["heat"], d["paf"], mode=mode)
         assert tuples_from_result(R.humans_as_tuples(), H, W) == tuples_from_json(gold[mode])
         assert len(gold[mode]) == 2
+
+
+@pytest.mark.parametrize("mode", ["asbuilt", "upstream"])
+def test_tie_order_matters_and_the_std_mode_is_the_reference(oracle, mode):
+    """Premise of the GPU test of "std_sort_ties": on helpers.chained_tie_case inputs (dozens of bit-equal candidates
+    per limb competing for the same peaks) the reference's own compiled pafprocess.cpp returns what the restatement
+    returns with the real std::sort, and NOT what the total order (score desc, idx1, idx2) returns."""
+    from helpers import chained_tie_case
+    ref = oracle.ReferencePafprocess(mode)
+    differ = 0
+    for seed in range(10):
+        pk, hu, pu = chained_tie_case(seed)
+        Rs = oracle.process_paf(pk, hu, pu, mode=mode, sort="std")
+        Rt = oracle.process_paf(pk, hu, pu, mode=mode, sort="total")
+        ref.process_paf(pk, hu, pu)
+        assert ref.humans_as_tuples() == Rs.humans_as_tuples()
+        assert (Rs.flags & 1) and (Rt.flags & 1) and len(Rs.humans_as_tuples()) > 0
+        assert max(len(c[0]) for c in Rs.cands) > 16
+        differ += int(Rs.humans_as_tuples() != Rt.humans_as_tuples())
+    assert differ >= 8
