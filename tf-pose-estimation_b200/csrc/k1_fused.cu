@@ -319,10 +319,12 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
     const int lx0 = 4 * (lane * CPL - 4);        // slot column of this lane's first pixel
     // low-res heat values of both cells in row r (zero outside the image: SAME zero padding, smoother.py:91)
     const float *Xc = p.X + (size_t)n * h * w * kNetC + c + (ptrdiff_t)cell0 * kNetC;
+    // r * w * 57 fits 32 bits: h <= 2047 and w <= 4095 (the upsampled map is capped at 8191 x 16383, tfpd_create)
+    const int rowstride = w * kNetC;
     auto hv2 = [&](int r) -> float2 {
         float2 v = make_float2(0.0f, 0.0f);
         if (r >= 0 && r < h) {
-            const float *row = Xc + (size_t)r * w * kNetC;
+            const float *row = Xc + r * rowstride;
             if (cin0) v.x = __ldg(row);
             if (cin1) v.y = __ldg(row + kNetC);
         }
@@ -424,16 +426,29 @@ __device__ void blur_role(const K1Params &p, const Item &it, float *pslots, int 
             }
             pm &= ownmask;
             if (is_part && hot > thr_lo) {
-                // a pixel above the heat threshold that lost its 3x3 max by a hair: near-tie (loser side)
-                uint32_t nm = 0;
+                // a pixel above the heat threshold that lost its 3x3 max by a hair: near-tie (loser side).  In minimal
+                // mode every row that reaches this point has hot > thr_lo somewhere in the warp, so the exact test below
+                // ran on every live row (15 % of the kernel's instructions, ncu r02i) for an event that is almost never
+                // there.  Screen first, one FMA and one compare per pixel: the exact condition (m - prev) <= 2e-5*|m|
+                // implies prev >= m - 3e-5*|m| (the 1e-5*|m| of slack is two orders of magnitude above the roundings of
+                // either side), so a lane whose screen stays clear cannot have a near-tie; the exact test decides.
+                bool cand = false;
 #pragma unroll
                 for (int i = 0; i < NPX; ++i) {
                     const float m = fmaxf(fmaxf(v[i], v[i + 1]), v[i + 2]);
-                    const bool nr = (prev[i] > thr_lo) & (prev[i] != m) & ((m - prev[i]) <= 2e-5f * fabsf(m));
-                    nm |= nr ? (1u << i) : 0u;
+                    cand |= (prev[i] != m) & (prev[i] >= fmaf(-3e-5f, fabsf(m), m));
                 }
-                nm &= ownmask;
-                if (nm) atomicAdd(&p.counters[n].near_ties, __popc(nm));
+                if (cand) {
+                    uint32_t nm = 0;
+#pragma unroll
+                    for (int i = 0; i < NPX; ++i) {
+                        const float m = fmaxf(fmaxf(v[i], v[i + 1]), v[i + 2]);
+                        const bool nr = (prev[i] > thr_lo) & (prev[i] != m) & ((m - prev[i]) <= 2e-5f * fabsf(m));
+                        nm |= nr ? (1u << i) : 0u;
+                    }
+                    nm &= ownmask;
+                    if (nm) atomicAdd(&p.counters[n].near_ties, __popc(nm));
+                }
             }
 
             float *slot = nullptr;
