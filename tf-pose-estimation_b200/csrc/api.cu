@@ -796,11 +796,14 @@ static int enqueue_decode(tfpd_ctx *ctx, const Workspace &ws, const float *net_o
         p.thresh = ctx->cfg.thresh_heat;
         p.min_band = ctx->k1_min_band;
         if (p.min_band <= 0) {
-            // automatic: the largest band of 16 / 8 / 4 low-res rows that still gives ~6 waves of CTAs (three CTAs per
-            // band, four resident per SM).  Measured (profiles/r02g_k1_ab.log, 64 frames): 46x54 maps 4 rows (52.5 us
-            // against 53.8 / 59.2 at 8 / 16), 92x164 maps 16 rows (129.5 us against 154.0 at 4): larger bands re-read
-            // fewer window rows, smaller ones fill the last wave.
-            const long long enough = 6LL * 4 * ctx->sm_count;
+            // automatic: the largest band of 16 / 8 / 4 low-res rows that still gives ~1.9 waves of CTAs (three CTAs per
+            // band, four resident per SM).  Larger bands cost less SM time in total (fewer halo rows and window
+            // prologues), smaller ones balance the last wave.  Measured on whole steps (profiles/r02s_band_sweep.log, 64
+            // frames, band 4 | 8 | 16): 46x54 maps serial 118.0 | 119.3 | 124.9 us, four contexts in flight 60.9 | 57.1 |
+            // 56.5; 46x82 serial 142.6 | 140.0 | 142.5, in flight 89.4 | 79.2 | 73.6; 92x164 serial 219 | 196 | 195, in
+            // flight 159 | 132 | 126.  Round 2 first asked for ~6 waves (K1 timed alone: 50.0 | 51.5 | 54.9 us), which
+            // left 5-18 % of the pipelined rate on the table for 1-3 % of the serial step.
+            const long long enough = 19LL * 4 * ctx->sm_count / 10;
             p.min_band = 4;
             for (int cand = 16; cand >= 8; cand /= 2)
                 if ((long long)N * p.nchunks * ((h + cand - 1) / cand) * (kParts / 6) >= enough) {
