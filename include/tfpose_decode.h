@@ -176,6 +176,28 @@ TFPD_API int tfpd_process_paf(tfpd_ctx *ctx, int p1, int p2, int p3, const float
 TFPD_API int tfpd_process_paf_device(tfpd_ctx *ctx, int p1, int p2, int p3, const float *peaks, int h1, int h2,
                             int h3, const float *heatmap, int f1, int f2, int f3, const float *pafmap,
                             void *stream);
+/* Peak table without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Needs no tfpd_ctx; calls no cudaMalloc / cudaFree / allocating library routine.
+ *
+ * Computes what tfpd_process_paf_device + tfpd_fetch_peaks compute (the reference's scan PEAKS(y,x,part) >
+ * thresh_heat over part < 18 in (part, y, x) order, score = HEAT(y,x,part): pafprocess.cpp:22-44) on the CURRENT
+ * device, asynchronously on `stream`:
+ *   peaks, heatmap : DEVICE float32 [H,W,19]           H <= 8191, W <= 16383
+ *   part, x, y     : DEVICE int32 [cap]                score : DEVICE float32 [cap]
+ *   count          : DEVICE int32 [2] = { entries written (<= cap), peaks found }; found > cap means the table
+ *                    overflowed and holds an arbitrary subset of `cap` peaks, in order
+ *   err, err_len   : optional HOST buffer that receives the message of a non-zero return
+ * Its scratch (append counter + unordered records) is a static __device__ array of TFPD_NOALLOC_SCRATCH_BYTES
+ * that every GPU loading the library holds until the process exits; cap > TFPD_NOALLOC_MAX_PEAKS is rejected with
+ * TFPD_ERR_CAPACITY.  All calls on a device SHARE that array: calls that overlap on the GPU (different streams or
+ * threads) race -- keep them on one stream or order them with events. */
+#define TFPD_NOALLOC_MAX_PEAKS 4096
+#define TFPD_NOALLOC_SCRATCH_BYTES (256 + 8 * TFPD_NOALLOC_MAX_PEAKS) /* 33,024 bytes per GPU */
+TFPD_API int tfpd_peak_table_noalloc(const float *peaks, const float *heatmap, int H, int W, float thresh_heat,
+                            int cap, int32_t *part, int32_t *x, int32_t *y, float *score, int32_t *count,
+                            void *stream, char *err, size_t err_len);
+
 /* getters of pafprocess.h:54-59 (frame 0 of the last call).  Unlike the reference they are
  * bounds-checked: out-of-range arguments return -1 / 0.0f and set the error string. */
 TFPD_API int tfpd_get_num_humans(tfpd_ctx *ctx);

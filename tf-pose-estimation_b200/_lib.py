@@ -72,6 +72,7 @@ SIGNATURES = {
     "tfpd_fetch_connections": (_I, [_P, _I, _I, _P, _P, _P, _P, C.POINTER(_I)]),
     "tfpd_process_paf": (_I, [_P, _I, _I, _I, _P, _I, _I, _I, _P, _I, _I, _I, _P]),
     "tfpd_process_paf_device": (_I, [_P, _I, _I, _I, _P, _I, _I, _I, _P, _I, _I, _I, _P, _P]),
+    "tfpd_peak_table_noalloc": (_I, [_P, _P, _I, _I, C.c_float, _I, _P, _P, _P, _P, _P, _P, C.c_char_p, C.c_size_t]),
     "tfpd_get_num_humans": (_I, [_P]),
     "tfpd_get_part_cid": (_I, [_P, _I, _I]),
     "tfpd_get_score": (C.c_float, [_P, _I]),

@@ -27,7 +27,7 @@ grep -n "membership" "$OUT/cpu_gcc_warnings_pafprocess.log" | head -5
 ( cd "$ROOT/tf-pose-estimation_b200/csrc" && nvcc -gencode arch=compute_100a,code=sm_100a -O1 -g -std=c++17 -lineinfo \
     -Xcompiler -fPIC -Xcompiler -fvisibility=hidden -Xcompiler -fsanitize=address -Xcompiler -fsanitize=undefined -Xcompiler -fno-omit-frame-pointer \
     -I../../include -shared -o "$ROOT/tools/ab/libtfpose_decode_asan.so" \
-    api.cu k1_fused.cu k_generic.cu k_peaks.cu k2_limbs.cu k3_assemble.cu k_draw.cu k_preproc.cu \
+    api.cu k1_fused.cu k_generic.cu k_peaks.cu k2_limbs.cu k3_assemble.cu k_draw.cu k_preproc.cu k_noalloc.cu \
     -Xlinker -lasan -Xlinker -lubsan ) > "$OUT/cpu_build_asan_lib.log" 2>&1 || { tail -5 "$OUT/cpu_build_asan_lib.log"; exit 1; }
 set +x
 PRE="$(gcc -print-file-name=libasan.so):$(gcc -print-file-name=libubsan.so)"
