@@ -273,7 +273,7 @@ TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, s
  *                  blurred value there can come within reach of the heat threshold or of a near-tie test.  Exact:
  *                  same tables, same near-tie counts; 0 computes every row.  Dense mode always computes every row.
  *   "k1_min_band"  minimal mode: low-res rows per CTA of the fused map kernel; 0 (default) = automatic, the largest of
- *                  16 / 8 / 4 that still gives about six waves of CTAs.  In minimal mode the kernel
+ *                  16 / 8 / 4 that still gives about two waves of CTAs (what whole pipelined steps prefer).  In minimal mode the kernel
  *                  runs three small CTAs (6 warps = 6 part channels each, four CTAs per SM) per band of rows of a
  *                  frame.  Smaller bands balance better, larger ones re-read fewer window rows.  Same results.
  *                  ("k1_ctas" applies to dense mode only.)
