@@ -131,7 +131,7 @@ def decoder(cuda):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("path", [0, 1, 2, 3])       # automatic / tiled / one thread per output pixel / strip
+@pytest.mark.parametrize("path", [0, 1, 2, 3])       # automatic (staged strip, else strip) / tiled / one thread per output pixel / strip
 def test_resize_cubic_matches_oracle_and_golden(decoder, path):
     decoder.set_option("resize_path", path)
     try:
@@ -147,6 +147,40 @@ def test_resize_cubic_matches_oracle_and_golden(decoder, path):
         decoder.set_option("resize_path", 0)
     g = golden_image(5, 50, 61, 1)[:, :, 0]
     assert decoder.resize_cubic(g, (43, 37)).shape == (37, 43)         # 2-D in, 2-D out like cv2
+
+
+@pytest.mark.gpu
+def test_resize_cubic_staged_form_on_odd_shapes(decoder):
+    """The automatic path takes the shared-memory staged strip kernel whenever the source rows are 4-byte aligned:
+    row tails that take the fixed-point cast (dst_w * cn not a multiple of 8), up- and down-scaling in either
+    direction, 1 / 2 / 3 / 4 channels, windows that run over every image border, tiles narrower than a CTA and
+    strips shorter than 32 rows -- against the CPU oracle (pinned on cv2) and against the plain strip kernel."""
+    import torch
+    shapes = [(37, 64, 1, 91, 53), (120, 160, 3, 431, 97), (480, 640, 3, 433, 367), (97, 128, 2, 45, 200),
+              (64, 48, 4, 47, 31), (300, 400, 3, 100, 77), (33, 20, 3, 5, 7), (5, 4, 3, 300, 40), (2, 4, 1, 1, 1),
+              (61, 256, 3, 256, 61), (200, 1024, 3, 700, 33)]
+    for i, (sh, sw, cn, dw, dh) in enumerate(shapes):
+        assert (sw * cn) % 4 == 0
+        img = golden_image(100 + i, sh, sw, cn)
+        want = PO.resize_cubic_u8(img, dw, dh)
+        decoder.set_option("resize_path", 0)
+        got = decoder.resize_cubic(img, (dw, dh))
+        decoder.set_option("resize_path", 3)
+        plain = decoder.resize_cubic(img, (dw, dh))
+        decoder.set_option("resize_path", 0)
+        got = got.reshape(want.shape)
+        assert np.array_equal(got, want), (sh, sw, cn, dw, dh, int(np.abs(got.astype(int) - want.astype(int)).max()))
+        assert np.array_equal(plain.reshape(want.shape), want)
+    # a batch on the device, extremes that overshoot on both sides
+    rng = np.random.default_rng(9)
+    imgs = rng.integers(0, 256, (5, 240, 320, 3), dtype=np.uint8)
+    imgs[1, ::2] = 0
+    imgs[1, 1::2] = 255
+    imgs[2, :, ::2] = 255
+    imgs[2, :, 1::2] = 0
+    out = decoder.resize_cubic(torch.from_numpy(imgs).cuda(), (217, 163)).cpu().numpy()
+    for i in range(len(imgs)):
+        assert np.array_equal(out[i], PO.resize_cubic_u8(imgs[i], 217, 163)), i
 
 
 @pytest.mark.gpu

@@ -57,7 +57,7 @@ struct tfpd_ctx {
     DevBuf poly_buf;                    // per-phase smoother weights of the power-of-two path, for factor poly_log2f
     int poly_log2f = -1, poly_T = 0;
     DevBuf draw_ids, draw_centers, draw_counts, draw_img;  // draw_humans scratch (lazily sized)
-    int resize_path = 0;                // 0 auto (= 3), 1 tiled, 2 one thread per output pixel, 3 strip
+    int resize_path = 0;                // 0 auto (staged strip where it applies, else 3), 1 tiled, 2 one thread per output pixel, 3 strip
     DevBuf pre_src, pre_dst;            // host-pointer calls of the image pre-processing (lazily sized)
     DevBuf in_buf, dense_buf, gen_buf;  // lazily sized: host-call input, dense outputs, generic-path scratch
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};

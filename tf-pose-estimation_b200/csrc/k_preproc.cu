@@ -8,8 +8,8 @@
 // round-half-even) except for the last (dst_w*cn) % 8 elements of a row, which take the fixed-point cast of the
 // scalar tail of OpenCV's 128-bit SIMD loop.
 //
-// Three forms with identical arithmetic (option "resize_path"): one thread per output pixel (the plain statement),
-// the strip form (default) and a shared-memory tiled form that measured slower; the tests force each.
+// Four forms with identical arithmetic (option "resize_path"): one thread per output pixel (the plain statement),
+// the strip form, its shared-memory staged version (default) and a tiled form that measured slower; the tests force each.
 #include "tfpd_internal.cuh"
 
 namespace tfpd {
@@ -193,6 +193,323 @@ __global__ void __launch_bounds__(128) k_resize_cubic_u8_strip(const unsigned ch
     }
 }
 
+// Staged strip form (the default where the source rows are 4-byte aligned): the strip form's arithmetic with a
+// third of its instructions.
+//  * The source window of a CTA (the rows its strip reads x the columns its output columns read, out-of-image
+//    columns replicated) is staged once in shared memory with 128-bit loads: a thread's 4 tap columns x CN channels
+//    are then 4*CN CONTIGUOUS bytes at a fixed offset of every row, fetched as CN+1 aligned words (the strip form
+//    issues 4*CN byte loads with 64-bit address arithmetic each) and realigned with funnel shifts.
+//  * byte permutes gather a channel's four taps into one register and two dp2a (s16 coefficient pairs x u8 taps)
+//    make its exact integer sum; the accumulator starts at the bit pattern of 1.5*2^23, so the sum arrives as the
+//    float's bits and one FADD finishes the exact int->float conversion.
+//  * The window of four source rows is a register ring rotated by unrolling (no moves): the outer loop walks SOURCE
+//    rows and emits every output row whose fourth tap row was just computed.
+//  * The vertical pass runs channel pairs on packed FP32 (mul.rn.f32x2 / add.rn.f32x2: the same separately rounded
+//    multiplies and adds), clamps in float and rounds with the magic constant: the low byte is the pixel.
+// Same bytes as the other forms (tests force each).
+constexpr int kStagedPx = 2;             // output columns per thread: x and x + blockDim.x
+template <int CN>
+struct HRow {                            // horizontal sums of one source row: CN channels of both columns, in pairs
+    float2 p[CN * kStagedPx / 2];
+};
+
+__device__ __forceinline__ float2 pk_mul(float2 a, float2 b) {
+    unsigned long long ra = *reinterpret_cast<unsigned long long *>(&a), rb = *reinterpret_cast<unsigned long long *>(&b), rd;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(rd) : "l"(ra), "l"(rb));
+    return *reinterpret_cast<float2 *>(&rd);
+}
+// a + b as fma(a, one, b) with one == 1.0f passed in at RUN time: ptxas contracts mul.rn.f32x2 feeding add.rn.f32x2
+// into one FFMA2 (observed with CUDA 12.9 even under --fmad=false, .rn notwithstanding), which would round the product
+// and the sum once instead of twice.  A product feeding the MULTIPLICAND of an fma with an opaque multiplier cannot be
+// contracted, and a * 1.0 + b rounds exactly like a + b.
+__device__ __forceinline__ float2 pk_add(float2 a, float2 one, float2 b) {
+    unsigned long long ra = *reinterpret_cast<unsigned long long *>(&a), ro = *reinterpret_cast<unsigned long long *>(&one),
+                       rb = *reinterpret_cast<unsigned long long *>(&b), rd;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(rd) : "l"(ra), "l"(ro), "l"(rb));
+    return *reinterpret_cast<float2 *>(&rd);
+}
+__device__ __forceinline__ int dp2a_lo_su(unsigned a, unsigned b, int c) {     // c + s16(a.lo)*u8(b.0) + s16(a.hi)*u8(b.1)
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi_su(unsigned a, unsigned b, int c) {     // c + s16(a.lo)*u8(b.2) + s16(a.hi)*u8(b.3)
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+// saturate_cast<uchar>(cvRound(v)) in one instruction (F2IP.U8.F32): round half even, clamped to 0..255
+__device__ __forceinline__ unsigned f2u8_rn_sat(float v) {
+    unsigned r;
+    asm("cvt.rni.u8.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return r;
+}
+
+// the four taps of channel C (bytes C, CN+C, 2CN+C, 3CN+C of the realigned tap bytes A[]) in one register
+template <int CN, int C>
+__device__ __forceinline__ unsigned gather_taps(const unsigned (&A)[CN]) {
+    constexpr int i0 = C, i1 = CN + C, i2 = 2 * CN + C, i3 = 3 * CN + C;
+    if constexpr (CN == 1) {
+        return A[0];
+    } else if constexpr (CN == 2) {
+        return __byte_perm(A[0], A[1], i0 | (i1 << 4) | (i2 << 8) | (i3 << 12));
+    } else if constexpr (CN == 3) {
+        // taps below byte 8 come from (A0, A1); the rest from A2
+        constexpr unsigned s1 = (unsigned)(i0 | (i1 << 4) | ((i2 < 8 ? i2 : 0) << 8));
+        const unsigned P = __byte_perm(A[0], A[1], s1);
+        constexpr unsigned s2 = 0u | (1u << 4) | ((i2 < 8 ? 2u : (unsigned)(4 + i2 - 8)) << 8) | ((unsigned)(4 + i3 - 8) << 12);
+        return __byte_perm(P, A[2], s2);
+    } else {
+        const unsigned lo = __byte_perm(A[0], A[1], (i0 & 3) | ((4 + (i1 & 3)) << 4));
+        const unsigned hi = __byte_perm(A[2], A[3], (i2 & 3) | ((4 + (i3 & 3)) << 4));
+        return __byte_perm(lo, hi, 0x5410);
+    }
+}
+
+// shared-memory loads through explicit 32-bit shared addresses: with generic pointers the compiler rebuilt the shared
+// window base (S2UR SR_CgaCtaId, ULEA ...) in front of every group of accesses of the hot loop (ncu r02z: a quarter of
+// its instructions were uniform-datapath bookkeeping).  "memory" keeps them behind the barrier that ends the staging.
+template <int OFF>
+__device__ __forceinline__ unsigned lds_u32(unsigned addr) {
+    unsigned v;
+    asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(OFF) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 lds_f4(unsigned addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ int4 lds_i4(unsigned addr) {
+    int4 v;
+    asm volatile("ld.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+
+constexpr int kStagePad = 16;            // bytes in front of a staged row: room for replicated left border columns
+template <int TY>
+constexpr int kStagedHeader = 36 * TY;   // bytes in front of the staged rows (TY = 16, 32: a multiple of 16)
+
+// TAIL: dw*CN is not a multiple of 8, the last elements of a row take the fixed-point cast (kept out of the common
+// variant altogether: the compiler hoists the tail's float->int conversions out of their branch)
+template <int CN, int TY, bool TAIL>
+__global__ void __launch_bounds__(256) k_resize_cubic_u8_staged(const unsigned char *__restrict__ src,
+                                                                 unsigned char *__restrict__ dst, int sh, int sw, int dh,
+                                                                 int dw, double scale_x, double scale_y, int stride,
+                                                                 int max_rows, float one) {
+    constexpr int PX = kStagedPx, VC = CN * PX, NP = VC / 2;
+    // dynamic shared memory: ylast[TY] | ybf[TY] | ybi[TY] | the staged rows [max_rows][stride]
+    extern __shared__ __align__(16) unsigned char st_dyn[];
+    int *ylast = reinterpret_cast<int *>(st_dyn);                    // source row (unclamped) of an output row's fourth tap
+    float4 *ybf = reinterpret_cast<float4 *>(st_dyn + 4 * TY);       // its coefficients / 2^22 as floats (vertical pass)
+    int4 *ybi = reinterpret_cast<int4 *>(st_dyn + 20 * TY);          // and as integers (fixed-point tail of a row)
+    unsigned char *st_rows = st_dyn + kStagedHeader<TY>;
+    __shared__ int s_win[2];             // unclamped first / last source column of the CTA
+    const int tid = threadIdx.x, T = blockDim.x;
+    const int x0 = blockIdx.x * (PX * T), tw = min(PX * T, dw - x0);
+    const int y0 = blockIdx.y * TY, n = blockIdx.z;
+    const int th = min(TY, dh - y0);
+    const float sc = 1.0f / (2048.0f * 2048.0f);
+    if (tid < th) {
+        const CubicTap t = cubic_tap(y0 + tid, scale_y);
+        ylast[tid] = t.ofs + 2;
+        ybf[tid] = make_float4((float)t.c[0] * sc, (float)t.c[1] * sc, (float)t.c[2] * sc, (float)t.c[3] * sc);
+        if (TAIL) ybi[tid] = make_int4(t.c[0], t.c[1], t.c[2], t.c[3]);
+    }
+    // this thread's columns: x0 + tid and x0 + tid + T (taps of an out-of-range column are those of the last column)
+    int xs[PX], ta[PX];                   // column, staged byte offset of its first tap byte (set below)
+    unsigned c01[PX], c23[PX];
+#pragma unroll
+    for (int j = 0; j < PX; ++j) {
+        xs[j] = x0 + tid + j * T;
+        const CubicTap tx = cubic_tap(min(xs[j], dw - 1), scale_x);
+        ta[j] = (tx.ofs - 1) * CN;
+        c01[j] = ((unsigned)tx.c[0] & 0xffffu) | ((unsigned)tx.c[1] << 16);
+        c23[j] = ((unsigned)tx.c[2] & 0xffffu) | ((unsigned)tx.c[3] << 16);
+        if (tid + j * T == 0) s_win[0] = tx.ofs - 1;
+        if (tid + j * T == tw - 1) s_win[1] = tx.ofs + 2;
+    }
+    __syncthreads();
+    const int wl = s_win[0], wr = s_win[1];
+    const int u_first = ylast[0] - 3, u_last = ylast[th - 1];
+    const int nrows = u_last - u_first + 1;                     // staged row r <-> source row clamp(u_first + r)
+    const int pitch = sw * CN;
+    // staged byte s of a row <-> source byte s - kStagePad + g0 of that row (g0: 16-byte aligned), columns clamped
+    const int g0 = (max(wl, 0) * CN) & ~15;
+    const int s_end = (wr + 1) * CN - g0 + kStagePad;          // one past the last byte any thread reads
+    const int units = (s_end + 4 + 15) >> 4;                    // + the extra word of the realigning loads
+    if (nrows > max_rows || units * 16 > stride) __trap();      // the host sized the buffer from the same scales
+    const unsigned char *img = src + (size_t)n * sh * (size_t)pitch;
+    const bool al16 = ((reinterpret_cast<uintptr_t>(img) | (unsigned)pitch) & 15) == 0;
+    // units [un_a, un_b) lie wholly inside the source row: 128-bit loads when the rows are 16-byte aligned
+    const int un_a = g0 >= kStagePad ? 0 : (kStagePad - g0) >> 4;
+    const int un_b = al16 ? max(un_a, min(units, ((pitch - g0 + kStagePad) >> 4))) : un_a;
+    const int nb_l = max(0, -wl) * CN, nb_r = max(0, wr - (sw - 1)) * CN;
+    // warp = staged row (strided); out-of-image rows are copies of the first / last row (the vertical taps clamp)
+    for (int r = tid >> 5; r < nrows; r += (T >> 5)) {
+        const unsigned char *row = img + (size_t)max(0, min(sh - 1, u_first + r)) * pitch;
+        unsigned char *srow = st_rows + (size_t)r * stride;
+        const int lane = tid & 31;
+        // whole units, four loads in flight per lane
+        for (int un0 = un_a + lane; un0 < un_b; un0 += 128) {
+            uint4 v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (un0 + 32 * k < un_b) v[k] = __ldg(reinterpret_cast<const uint4 *>(row + (un0 + 32 * k) * 16 - kStagePad + g0));
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (un0 + 32 * k < un_b) *reinterpret_cast<uint4 *>(srow + (un0 + 32 * k) * 16) = v[k];
+        }
+        // the units that straddle or lie outside the row (all of them when the rows are only 4-byte aligned): words
+        // inside the row are loaded (rows are 4-byte aligned: host check), the rest is zero
+        for (int e = lane; e < units - (un_b - un_a); e += 32) {
+            const int un = e < un_a ? e : e + (un_b - un_a);
+            const int g = un * 16 - kStagePad + g0;
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if (g >= 0 && g + 4 <= pitch) v.x = __ldg(reinterpret_cast<const unsigned *>(row + g));
+            if (g + 4 >= 0 && g + 8 <= pitch) v.y = __ldg(reinterpret_cast<const unsigned *>(row + g + 4));
+            if (g + 8 >= 0 && g + 12 <= pitch) v.z = __ldg(reinterpret_cast<const unsigned *>(row + g + 8));
+            if (g + 12 >= 0 && g + 16 <= pitch) v.w = __ldg(reinterpret_cast<const unsigned *>(row + g + 12));
+            *reinterpret_cast<uint4 *>(srow + un * 16) = v;
+        }
+        // the replicated border columns a window can reach (at most two on either side)
+        if (nb_l + nb_r > 0) {
+            __syncwarp();
+            for (int i = lane; i < nb_l + nb_r; i += 32) {
+                if (i < nb_l) {           // byte i of the columns wl .. -1: channel i % CN of column 0
+                    srow[wl * CN + i - g0 + kStagePad] = __ldg(row + i % CN);
+                } else {                  // byte j of the columns sw .. wr: channel j % CN of column sw-1
+                    const int j = i - nb_l;
+                    srow[sw * CN + j - g0 + kStagePad] = __ldg(row + (sw - 1) * CN + j % CN);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (xs[0] >= dw) return;
+    const bool valid1 = xs[PX - 1] < dw;
+
+    // one 32-bit shared base, made opaque so that it stays in a register (the compiler otherwise rebuilds it from
+    // SR_CgaCtaId at every use)
+    unsigned sbase = (unsigned)__cvta_generic_to_shared(st_dyn);
+    asm volatile("" : "+r"(sbase));
+    const unsigned a_ylast = sbase, a_ybf = sbase + 4u * TY, a_ybi = sbase + 20u * TY;
+    // a column's tap bytes: 4*CN contiguous bytes from staged byte a of every row, fetched as CN+1 aligned words
+    unsigned tp32[PX], shift[PX];
+#pragma unroll
+    for (int j = 0; j < PX; ++j) {
+        const int a = ta[j] - g0 + kStagePad;
+        tp32[j] = sbase + (unsigned)kStagedHeader<TY> + (unsigned)(a & ~3);
+        shift[j] = (unsigned)(a & 3) * 8u;
+    }
+    const int kMagicI = 0x4B400000;
+    const float kMagicF = 12582912.0f;
+
+    auto fetch = [&](unsigned roff, unsigned (&wv)[PX][CN + 1]) {
+#pragma unroll
+        for (int j = 0; j < PX; ++j) {
+            const unsigned q = tp32[j] + roff;
+            wv[j][0] = lds_u32<0>(q);
+            wv[j][1] = lds_u32<4>(q);
+            if (CN >= 2) wv[j][CN >= 2 ? 2 : 0] = lds_u32<8>(q);
+            if (CN >= 3) wv[j][CN >= 3 ? 3 : 0] = lds_u32<12>(q);
+            if (CN >= 4) wv[j][CN >= 4 ? 4 : 0] = lds_u32<16>(q);
+        }
+    };
+    // exact integer sums of the fetched row: byte permutes gather a channel's taps, two dp2a sum them on top of the
+    // bits of 1.5*2^23, one FADD finishes the int->float conversion
+    auto reduce = [&](const unsigned (&wv)[PX][CN + 1], HRow<CN> &R) {
+        float hf[VC];
+#pragma unroll
+        for (int j = 0; j < PX; ++j) {
+            unsigned A[CN];
+#pragma unroll
+            for (int k = 0; k < CN; ++k) A[k] = __funnelshift_r(wv[j][k], wv[j][k + 1], shift[j]);
+#pragma unroll
+            for (int c = 0; c < CN; ++c) {
+                unsigned Tp;
+                if (c == 0) Tp = gather_taps<CN, 0>(A);
+                else if (c == 1) Tp = gather_taps<CN, (CN > 1 ? 1 : 0)>(A);
+                else if (c == 2) Tp = gather_taps<CN, (CN > 2 ? 2 : 0)>(A);
+                else Tp = gather_taps<CN, (CN > 3 ? 3 : 0)>(A);
+                hf[j * CN + c] = __fadd_rn(__int_as_float(dp2a_hi_su(c23[j], Tp, dp2a_lo_su(c01[j], Tp, kMagicI))), -kMagicF);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < NP; ++k) R.p[k] = make_float2(hf[2 * k], hf[2 * k + 1]);
+    };
+
+    const int simd_end = (dw * CN) & ~7;
+    unsigned char *q0 = dst + (((size_t)n * dh + y0) * dw + xs[0]) * CN;       // column 0's pixel of the next output row
+    const size_t opitch = (size_t)dw * CN;
+    const int qstep = T * CN;                                                   // to column 1's pixel
+    const float2 one2 = make_float2(one, one);
+    auto emit = [&](int yl, const HRow<CN> &R0, const HRow<CN> &R1, const HRow<CN> &R2, const HRow<CN> &R3) {
+        const float4 b = lds_f4(a_ybf + 16u * (unsigned)yl);
+        float res[VC];
+#pragma unroll
+        for (int k = 0; k < NP; ++k) {
+            float2 acc = pk_mul(R3.p[k], make_float2(b.w, b.w));
+            acc = pk_add(pk_mul(R2.p[k], make_float2(b.z, b.z)), one2, acc);
+            acc = pk_add(pk_mul(R1.p[k], make_float2(b.y, b.y)), one2, acc);
+            acc = pk_add(pk_mul(R0.p[k], make_float2(b.x, b.x)), one2, acc);
+            res[2 * k] = acc.x;
+            res[2 * k + 1] = acc.y;
+        }
+        unsigned out[VC];
+#pragma unroll
+        for (int v = 0; v < VC; ++v) out[v] = f2u8_rn_sat(res[v]);
+        if (TAIL) {
+            const int4 bi = lds_i4(a_ybi + 16u * (unsigned)yl);
+#pragma unroll
+            for (int v = 0; v < VC; ++v) {
+                if (xs[v / CN] * CN + v % CN >= simd_end) {     // the horizontal sums are exact integers below 2^22
+                    const float h0 = (v & 1) ? R0.p[v / 2].y : R0.p[v / 2].x, h1 = (v & 1) ? R1.p[v / 2].y : R1.p[v / 2].x,
+                                h2 = (v & 1) ? R2.p[v / 2].y : R2.p[v / 2].x, h3 = (v & 1) ? R3.p[v / 2].y : R3.p[v / 2].x;
+                    const int t = ((int)h0 * bi.x + (int)h1 * bi.y + (int)h2 * bi.z + (int)h3 * bi.w + (1 << 21)) >> 22;
+                    out[v] = (unsigned)max(0, min(255, t));
+                }
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < CN; ++c) q0[c] = (unsigned char)out[c];
+        if (valid1) {
+#pragma unroll
+            for (int c = 0; c < CN; ++c) q0[qstep + c] = (unsigned char)out[CN + c];
+        }
+        q0 += opitch;
+    };
+
+    HRow<CN> Ra, Rb, Rc, Rd;
+    int yl = 0, u = u_first;
+    int next_last = ylast[0];                   // source row that completes the window of output row yl
+    unsigned roff = 0;                          // staged row of u
+    unsigned wv[PX][CN + 1];
+    fetch(roff, wv);
+    // one source row per step: its sums go to S3 (the words of the NEXT row are requested before anything else uses
+    // them), then every output row whose fourth tap row this is gets emitted
+#define TFPD_STAGED_STEP(S0, S1, S2, S3)                                              \
+    {                                                                                  \
+        reduce(wv, S3);                                                                \
+        if (u < u_last) roff += (unsigned)stride;                                      \
+        fetch(roff, wv);                                                               \
+        while (next_last == u) {                                                       \
+            emit(yl, S0, S1, S2, S3);                                                  \
+            ++yl;                                                                      \
+            next_last = yl < th ? (int)lds_u32<0>(a_ylast + 4u * (unsigned)yl) : 0x7fffffff; \
+        }                                                                              \
+        if (u == u_last) break;                                                        \
+        ++u;                                                                           \
+    }
+    for (;;) {
+        TFPD_STAGED_STEP(Ra, Rb, Rc, Rd)
+        TFPD_STAGED_STEP(Rb, Rc, Rd, Ra)
+        TFPD_STAGED_STEP(Rc, Rd, Ra, Rb)
+        TFPD_STAGED_STEP(Rd, Ra, Rb, Rc)
+    }
+#undef TFPD_STAGED_STEP
+}
+
 // Tiled form: one CTA = TY output rows x tile_w output columns.  The coefficient tables of the tile are computed once
 // (not per pixel), the horizontal pass runs once per SOURCE row the tile touches (TY*scale + 3 rows instead of 4 per
 // output row) into shared memory as exact int32, the vertical pass reads it back.  Same arithmetic as above.
@@ -309,6 +626,55 @@ int launch_resize_cubic_u8(const unsigned char *src, unsigned char *dst, int N, 
     const bool tiled = path == 1;      // measured slower than the per-pixel kernel (0.17-0.28 ms against 0.15 per 64 frames)
     const bool strip = path == 0 || path == 3;
     if (tiled && smem > 200 * 1024) return -1;
+    // staged strip form: needs 4-byte aligned source rows (its staging loads are words) and a window that fits in
+    // shared memory; otherwise the plain strip form
+    if (path == 0) {
+        static const int ty_env = getenv("TFPD_RESIZE_TY") ? atoi(getenv("TFPD_RESIZE_TY")) : 0;
+        static const int th_env = getenv("TFPD_RESIZE_THREADS") ? atoi(getenv("TFPD_RESIZE_THREADS")) : 0;
+        const int ty = ty_env == 32 ? 32 : 16;
+        // CTA width: a thread computes columns x and x + threads; the multiple of 32 in 64..256 that leaves the fewest
+        // idle column slots over dw columns (the widest such)
+        int threads = 128;
+        long long best = -1;
+        for (int t = 64; t <= 256; t += 32) {
+            const long long tile = (long long)kStagedPx * t, padded = (dw + tile - 1) / tile * tile;
+            if (best < 0 || padded < best || (padded == best && t > threads)) best = padded, threads = t;
+        }
+        if (th_env >= 32 && th_env <= 256 && th_env % 32 == 0) threads = th_env;
+        const int wcols = (int)ceil((kStagedPx * threads - 1) * scale_x) + 6;
+        const int stride = (wcols * cn + 15 + kStagePad + 4 + 15) / 16 * 16;
+        const int rows = (int)ceil((ty - 1) * scale_y) + 6;
+        const size_t st_smem = (size_t)stride * rows + 36 * (size_t)ty;
+        const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (size_t)sw * cn) & 3) == 0;
+        if (aligned && st_smem <= 96 * 1024 && scale_x < 64.0 && scale_y < 64.0) {
+            const dim3 grid((dw + kStagedPx * threads - 1) / (kStagedPx * threads), (dh + ty - 1) / ty, N);
+#define TFPD_STAGED_CASE_T(CN, TY, TAIL)                                                                               \
+    {                                                                                                                  \
+        if (st_smem > 48 * 1024 &&                                                                                     \
+            cudaFuncSetAttribute(k_resize_cubic_u8_staged<CN, TY, TAIL>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                 (int)st_smem) != cudaSuccess)                                                        \
+            return -1;                                                                                                 \
+        k_resize_cubic_u8_staged<CN, TY, TAIL><<<grid, threads, st_smem, s>>>(src, dst, sh, sw, dh, dw, scale_x,      \
+                                                                              scale_y, stride, rows, 1.0f);            \
+    }
+#define TFPD_STAGED_CASE(CN, TY)                                                                                       \
+    if ((dw * CN) & 7) TFPD_STAGED_CASE_T(CN, TY, true) else TFPD_STAGED_CASE_T(CN, TY, false)
+            switch (cn * 100 + ty) {
+                case 116: TFPD_STAGED_CASE(1, 16) break;
+                case 132: TFPD_STAGED_CASE(1, 32) break;
+                case 216: TFPD_STAGED_CASE(2, 16) break;
+                case 232: TFPD_STAGED_CASE(2, 32) break;
+                case 316: TFPD_STAGED_CASE(3, 16) break;
+                case 332: TFPD_STAGED_CASE(3, 32) break;
+                case 416: TFPD_STAGED_CASE(4, 16) break;
+                case 432: TFPD_STAGED_CASE(4, 32) break;
+                default: return -1;
+            }
+#undef TFPD_STAGED_CASE
+#undef TFPD_STAGED_CASE_T
+            return cudaGetLastError() == cudaSuccess ? 1 : -1;
+        }
+    }
 #define TFPD_RESIZE_CASE(CN)                                                                                           \
     case CN:                                                                                                           \
         if (tiled) {                                                                                                   \

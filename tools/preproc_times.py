@@ -35,7 +35,7 @@ def main():
         return d.resize_cubic(srcs[i[0] % 8], (432, 368))
 
     by = n * (sh * sw * 3 + 368 * 432 * 3)
-    for path, name in ((3, "strip"), (1, "tiled"), (2, "per-pixel")):
+    for path, name in ((0, "staged strip (automatic)"), (3, "strip"), (1, "tiled"), (2, "per-pixel")):
         d.set_option("resize_path", path)
         ms = timed(resize)
         print("resize_cubic %s %dx%dx3 -> 368x432x3, batch %d: %.3f ms, %.0f frames/s, %.0f GB/s algorithmic" %
