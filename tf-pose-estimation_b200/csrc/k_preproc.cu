@@ -345,46 +345,50 @@ __global__ void __launch_bounds__(256) k_resize_cubic_u8_staged(const unsigned c
     const int un_a = g0 >= kStagePad ? 0 : (kStagePad - g0) >> 4;
     const int un_b = al16 ? max(un_a, min(units, ((pitch - g0 + kStagePad) >> 4))) : un_a;
     const int nb_l = max(0, -wl) * CN, nb_r = max(0, wr - (sw - 1)) * CN;
-    // warp = staged row (strided); out-of-image rows are copies of the first / last row (the vertical taps clamp)
+    // Staging.  Out-of-image rows are copies of the first / last row (the vertical taps clamp).  Everything is issued
+    // before anything is waited for: one memory round trip for the CTA instead of one per row and pass (ncu r03b:
+    // long-scoreboard and barrier waits of the staging phase were a third of the warps' time).
+    //  (1) whole units as 16-byte asynchronous copies, warp = row (strided), lane = unit (strided);
+    const unsigned st32 = (unsigned)__cvta_generic_to_shared(st_rows);
     for (int r = tid >> 5; r < nrows; r += (T >> 5)) {
+        const unsigned char *row = img + (size_t)max(0, min(sh - 1, u_first + r)) * pitch + (g0 - kStagePad);
+        const unsigned srow = st32 + (unsigned)r * (unsigned)stride;
+        for (int un = un_a + (tid & 31); un < un_b; un += 32)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(srow + 16u * (unsigned)un), "l"(row + 16 * un) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    //  (2) the units that straddle or lie outside the row (all of them when the rows are only 4-byte aligned), flat
+    //      over (row, unit): words inside the row are loaded (rows are 4-byte aligned: host check), the rest is zero;
+    const int n_edge = units - (un_b - un_a);
+    for (int idx = tid; idx < nrows * n_edge; idx += T) {
+        const int r = idx / n_edge, e = idx - r * n_edge;
+        const int un = e < un_a ? e : e + (un_b - un_a);
         const unsigned char *row = img + (size_t)max(0, min(sh - 1, u_first + r)) * pitch;
-        unsigned char *srow = st_rows + (size_t)r * stride;
-        const int lane = tid & 31;
-        // whole units, four loads in flight per lane
-        for (int un0 = un_a + lane; un0 < un_b; un0 += 128) {
-            uint4 v[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (un0 + 32 * k < un_b) v[k] = __ldg(reinterpret_cast<const uint4 *>(row + (un0 + 32 * k) * 16 - kStagePad + g0));
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (un0 + 32 * k < un_b) *reinterpret_cast<uint4 *>(srow + (un0 + 32 * k) * 16) = v[k];
-        }
-        // the units that straddle or lie outside the row (all of them when the rows are only 4-byte aligned): words
-        // inside the row are loaded (rows are 4-byte aligned: host check), the rest is zero
-        for (int e = lane; e < units - (un_b - un_a); e += 32) {
-            const int un = e < un_a ? e : e + (un_b - un_a);
-            const int g = un * 16 - kStagePad + g0;
-            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-            if (g >= 0 && g + 4 <= pitch) v.x = __ldg(reinterpret_cast<const unsigned *>(row + g));
-            if (g + 4 >= 0 && g + 8 <= pitch) v.y = __ldg(reinterpret_cast<const unsigned *>(row + g + 4));
-            if (g + 8 >= 0 && g + 12 <= pitch) v.z = __ldg(reinterpret_cast<const unsigned *>(row + g + 8));
-            if (g + 12 >= 0 && g + 16 <= pitch) v.w = __ldg(reinterpret_cast<const unsigned *>(row + g + 12));
-            *reinterpret_cast<uint4 *>(srow + un * 16) = v;
-        }
-        // the replicated border columns a window can reach (at most two on either side)
-        if (nb_l + nb_r > 0) {
-            __syncwarp();
-            for (int i = lane; i < nb_l + nb_r; i += 32) {
-                if (i < nb_l) {           // byte i of the columns wl .. -1: channel i % CN of column 0
-                    srow[wl * CN + i - g0 + kStagePad] = __ldg(row + i % CN);
-                } else {                  // byte j of the columns sw .. wr: channel j % CN of column sw-1
-                    const int j = i - nb_l;
-                    srow[sw * CN + j - g0 + kStagePad] = __ldg(row + (sw - 1) * CN + j % CN);
-                }
+        const int g = un * 16 - kStagePad + g0;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (g >= 0 && g + 4 <= pitch) v.x = __ldg(reinterpret_cast<const unsigned *>(row + g));
+        if (g + 4 >= 0 && g + 8 <= pitch) v.y = __ldg(reinterpret_cast<const unsigned *>(row + g + 4));
+        if (g + 8 >= 0 && g + 12 <= pitch) v.z = __ldg(reinterpret_cast<const unsigned *>(row + g + 8));
+        if (g + 12 >= 0 && g + 16 <= pitch) v.w = __ldg(reinterpret_cast<const unsigned *>(row + g + 12));
+        *reinterpret_cast<uint4 *>(st_rows + (size_t)r * stride + un * 16) = v;
+    }
+    //  (3) the replicated border columns a window can reach (at most two on either side), after the units they lie in.
+    if (nb_l + nb_r > 0) {
+        __syncthreads();
+        const int nb = nb_l + nb_r;
+        for (int idx = tid; idx < nrows * nb; idx += T) {
+            const int r = idx / nb, i = idx - r * nb;
+            const unsigned char *row = img + (size_t)max(0, min(sh - 1, u_first + r)) * pitch;
+            unsigned char *srow = st_rows + (size_t)r * stride;
+            if (i < nb_l) {           // byte i of the columns wl .. -1: channel i % CN of column 0
+                srow[wl * CN + i - g0 + kStagePad] = __ldg(row + i % CN);
+            } else {                  // byte j of the columns sw .. wr: channel j % CN of column sw-1
+                const int j = i - nb_l;
+                srow[sw * CN + j - g0 + kStagePad] = __ldg(row + (sw - 1) * CN + j % CN);
             }
         }
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
     if (xs[0] >= dw) return;
     const bool valid1 = xs[PX - 1] < dw;

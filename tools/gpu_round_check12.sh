@@ -3,7 +3,7 @@
 P=${1:-r02z}
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_preproc.py -m gpu -x -q 2>&1 | tail -4
-for ty in 16 32; do for th in 0 128 160; do echo "== TY $ty threads $th"; TFPD_RESIZE_TY=$ty TFPD_RESIZE_THREADS=$th timeout 300 python tools/preproc_times.py 2>&1 | grep -E "staged|resize_cubic strip" | tee -a gpurun_out/${P}_preproc_times.log; done; done
+for ty in 16; do for th in 0 128; do echo "== TY $ty threads $th"; TFPD_RESIZE_TY=$ty TFPD_RESIZE_THREADS=$th timeout 300 python tools/preproc_times.py 2>&1 | grep -E "staged|resize_cubic strip" | tee -a gpurun_out/${P}_preproc_times.log; done; done
 timeout 300 python tools/preproc_times.py 64 720 1280 2>&1 | grep -E "resize_cubic (staged|strip)" | tee -a gpurun_out/${P}_preproc_times.log
 python tools/ncu_preproc.py 0 > /dev/null 2>&1 || { echo "target fails"; exit 1; }
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_resize_cubic_u8 --launch-skip 1 --launch-count 1 -f \
