@@ -286,79 +286,104 @@ __device__ __forceinline__ int4 lds_i4(unsigned addr) {
     return v;
 }
 
+// TMA bulk load global -> shared with an mbarrier counting the bytes (16-byte aligned source, destination and size)
+__device__ __forceinline__ void st_mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void st_mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void st_mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n .reg .pred p;\n WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra DONE_%=;\n"
+        " bra WAIT_%=;\n DONE_%=:\n}\n" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void st_bulk_load(unsigned sdst, const void *gsrc, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(sdst),
+                 "l"(gsrc), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
 constexpr int kStagePad = 16;            // bytes in front of a staged row: room for replicated left border columns
-template <int TY>
-constexpr int kStagedHeader = 36 * TY;   // bytes in front of the staged rows (TY = 16, 32: a multiple of 16)
+constexpr int kStagedMaxTy = 32;         // most output rows per CTA (the strip height is a launch parameter)
+constexpr int kStagedHeader = 36 * kStagedMaxTy;   // bytes in front of the staged rows
 
 // TAIL: dw*CN is not a multiple of 8, the last elements of a row take the fixed-point cast (kept out of the common
 // variant altogether: the compiler hoists the tail's float->int conversions out of their branch)
-template <int CN, int TY, bool TAIL>
+template <int CN, bool TAIL>
 __global__ void __launch_bounds__(256) k_resize_cubic_u8_staged(const unsigned char *__restrict__ src,
                                                                  unsigned char *__restrict__ dst, int sh, int sw, int dh,
                                                                  int dw, double scale_x, double scale_y, int stride,
-                                                                 int max_rows, float one) {
+                                                                 int max_rows, float one, int TY) {
     constexpr int PX = kStagedPx, VC = CN * PX, NP = VC / 2;
-    // dynamic shared memory: ylast[TY] | ybf[TY] | ybi[TY] | the staged rows [max_rows][stride]
+    // dynamic shared memory: ylast[32] | ybf[32] | ybi[32] | the staged rows [max_rows][stride]   (TY <= 32 output rows)
     extern __shared__ __align__(16) unsigned char st_dyn[];
     int *ylast = reinterpret_cast<int *>(st_dyn);                    // source row (unclamped) of an output row's fourth tap
-    float4 *ybf = reinterpret_cast<float4 *>(st_dyn + 4 * TY);       // its coefficients / 2^22 as floats (vertical pass)
-    int4 *ybi = reinterpret_cast<int4 *>(st_dyn + 20 * TY);          // and as integers (fixed-point tail of a row)
-    unsigned char *st_rows = st_dyn + kStagedHeader<TY>;
-    __shared__ int s_win[2];             // unclamped first / last source column of the CTA
+    float4 *ybf = reinterpret_cast<float4 *>(st_dyn + 4 * kStagedMaxTy);       // its coefficients / 2^22 as floats (vertical pass)
+    int4 *ybi = reinterpret_cast<int4 *>(st_dyn + 20 * kStagedMaxTy);          // and as integers (fixed-point tail of a row)
+    unsigned char *st_rows = st_dyn + kStagedHeader;
+    __shared__ __align__(8) unsigned long long s_bar;      // mbarrier of the staging copies
     const int tid = threadIdx.x, T = blockDim.x;
+    const unsigned bar32 = (unsigned)__cvta_generic_to_shared(&s_bar);
     const int x0 = blockIdx.x * (PX * T), tw = min(PX * T, dw - x0);
     const int y0 = blockIdx.y * TY, n = blockIdx.z;
     const int th = min(TY, dh - y0);
-    const float sc = 1.0f / (2048.0f * 2048.0f);
-    if (tid < th) {
-        const CubicTap t = cubic_tap(y0 + tid, scale_y);
-        ylast[tid] = t.ofs + 2;
-        ybf[tid] = make_float4((float)t.c[0] * sc, (float)t.c[1] * sc, (float)t.c[2] * sc, (float)t.c[3] * sc);
-        if (TAIL) ybi[tid] = make_int4(t.c[0], t.c[1], t.c[2], t.c[3]);
-    }
-    // this thread's columns: x0 + tid and x0 + tid + T (taps of an out-of-range column are those of the last column)
-    int xs[PX], ta[PX];                   // column, staged byte offset of its first tap byte (set below)
-    unsigned c01[PX], c23[PX];
-#pragma unroll
-    for (int j = 0; j < PX; ++j) {
-        xs[j] = x0 + tid + j * T;
-        const CubicTap tx = cubic_tap(min(xs[j], dw - 1), scale_x);
-        ta[j] = (tx.ofs - 1) * CN;
-        c01[j] = ((unsigned)tx.c[0] & 0xffffu) | ((unsigned)tx.c[1] << 16);
-        c23[j] = ((unsigned)tx.c[2] & 0xffffu) | ((unsigned)tx.c[3] << 16);
-        if (tid + j * T == 0) s_win[0] = tx.ofs - 1;
-        if (tid + j * T == tw - 1) s_win[1] = tx.ofs + 2;
-    }
-    __syncthreads();
-    const int wl = s_win[0], wr = s_win[1];
-    const int u_first = ylast[0] - 3, u_last = ylast[th - 1];
-    const int nrows = u_last - u_first + 1;                     // staged row r <-> source row clamp(u_first + r)
     const int pitch = sw * CN;
-    // staged byte s of a row <-> source byte s - kStagePad + g0 of that row (g0: 16-byte aligned), columns clamped
-    const int g0 = (max(wl, 0) * CN) & ~15;
-    const int s_end = (wr + 1) * CN - g0 + kStagePad;          // one past the last byte any thread reads
-    const int units = (s_end + 4 + 15) >> 4;                    // + the extra word of the realigning loads
-    if (nrows > max_rows || units * 16 > stride) __trap();      // the host sized the buffer from the same scales
     const unsigned char *img = src + (size_t)n * sh * (size_t)pitch;
     const bool al16 = ((reinterpret_cast<uintptr_t>(img) | (unsigned)pitch) & 15) == 0;
-    // units [un_a, un_b) lie wholly inside the source row: 128-bit loads when the rows are 16-byte aligned
-    const int un_a = g0 >= kStagePad ? 0 : (kStagePad - g0) >> 4;
-    const int un_b = al16 ? max(un_a, min(units, ((pitch - g0 + kStagePad) >> 4))) : un_a;
-    const int nb_l = max(0, -wl) * CN, nb_r = max(0, wr - (sw - 1)) * CN;
-    // Staging.  Out-of-image rows are copies of the first / last row (the vertical taps clamp).  Everything is issued
-    // before anything is waited for: one memory round trip for the CTA instead of one per row and pass (ncu r03b:
-    // long-scoreboard and barrier waits of the staging phase were a third of the warps' time).
-    //  (1) whole units as 16-byte asynchronous copies, warp = row (strided), lane = unit (strided);
     const unsigned st32 = (unsigned)__cvta_generic_to_shared(st_rows);
-    for (int r = tid >> 5; r < nrows; r += (T >> 5)) {
-        const unsigned char *row = img + (size_t)max(0, min(sh - 1, u_first + r)) * pitch + (g0 - kStagePad);
-        const unsigned srow = st32 + (unsigned)r * (unsigned)stride;
-        for (int un = un_a + (tid & 31); un < un_b; un += 32)
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(srow + 16u * (unsigned)un), "l"(row + 16 * un) : "memory");
+    // What the CTA stages, from its first / last source column (wl, wr) and row (u_first, u_last), all unclamped:
+    // staged row r <-> source row clamp(u_first + r); staged byte s of a row <-> source byte s - kStagePad + g0 of that
+    // row (g0: 16-byte aligned), columns clamped; units [un_a, un_b) of 16 bytes lie wholly inside the source row.
+    struct Ext {
+        int wl, wr, u_first, u_last, nrows, g0, units, un_a, un_b;
+    };
+    auto extents = [&](int wl, int wr, int u_first, int u_last) {
+        Ext e;
+        e.wl = wl, e.wr = wr, e.u_first = u_first, e.u_last = u_last;
+        e.nrows = u_last - u_first + 1;
+        e.g0 = (max(wl, 0) * CN) & ~15;
+        const int s_end = (wr + 1) * CN - e.g0 + kStagePad;     // one past the last byte any thread reads
+        e.units = (s_end + 4 + 15) >> 4;                         // + the extra word of the realigning loads
+        e.un_a = e.g0 >= kStagePad ? 0 : (kStagePad - e.g0) >> 4;
+        e.un_b = al16 ? max(e.un_a, min(e.units, ((pitch - e.g0 + kStagePad) >> 4))) : e.un_a;
+        return e;
+    };
+    // Staging.  Every warp finds the extents for itself (four taps on four lanes, shuffled: no barrier in front of the
+    // staging); warp 0 then issues the whole units of every row as ONE bulk copy (TMA) per row, lane = row (strided),
+    // and everything else -- the edge units, the header, every thread's own column taps (float64 arithmetic) -- is
+    // computed while the copies are in flight.  Out-of-image rows are copies of the first / last row (the vertical
+    // taps clamp).  One barrier at the end.
+    Ext ex;
+    {
+        const int l = tid & 31;
+        const int d = l == 0 ? x0 : l == 1 ? x0 + tw - 1 : l == 2 ? y0 : y0 + th - 1;
+        const CubicTap t = cubic_tap(d, l < 2 ? scale_x : scale_y);
+        const int v = t.ofs + ((l & 1) ? 2 : -1);
+        ex = extents(__shfl_sync(0xffffffffu, v, 0), __shfl_sync(0xffffffffu, v, 1), __shfl_sync(0xffffffffu, v, 2),
+                     __shfl_sync(0xffffffffu, v, 3));
     }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    //  (2) the units that straddle or lie outside the row (all of them when the rows are only 4-byte aligned), flat
-    //      over (row, unit): words inside the row are loaded (rows are 4-byte aligned: host check), the rest is zero;
+    const int wl = ex.wl, wr = ex.wr, u_first = ex.u_first, u_last = ex.u_last, nrows = ex.nrows, g0 = ex.g0, units = ex.units,
+              un_a = ex.un_a, un_b = ex.un_b;
+    if (nrows > max_rows || units * 16 > stride) __trap();      // the host sized the buffer from the same scales
+    const unsigned row_bytes = (unsigned)(un_b - un_a) * 16u;
+    if (tid < 32) {
+        if (tid == 0) {
+            st_mbar_init(bar32, 1);
+            if (row_bytes != 0u) st_mbar_expect_tx(bar32, row_bytes * (unsigned)nrows);
+        }
+        __syncwarp();
+        if (row_bytes != 0u)
+            for (int r = tid; r < nrows; r += 32)
+                st_bulk_load(st32 + (unsigned)r * (unsigned)stride + 16u * (unsigned)un_a,
+                             img + (size_t)max(0, min(sh - 1, u_first + r)) * pitch + (g0 - kStagePad) + 16 * un_a, row_bytes, bar32);
+    }
+    // The units that straddle or lie outside the source row (all of them when the rows are only 4-byte aligned), flat
+    // over (row, unit): words inside the row are loaded (rows are 4-byte aligned: host check), the rest is zero; the
+    // replicated border columns are patched in below, after a barrier.  (Filling them here, byte by byte, in the same
+    // pass measured slower: 39 -> 46 us, the few threads with such units keep the whole CTA at the barrier.)
     const int n_edge = units - (un_b - un_a);
     for (int idx = tid; idx < nrows * n_edge; idx += T) {
         const int r = idx / n_edge, e = idx - r * n_edge;
@@ -372,7 +397,28 @@ __global__ void __launch_bounds__(256) k_resize_cubic_u8_staged(const unsigned c
         if (g + 12 >= 0 && g + 16 <= pitch) v.w = __ldg(reinterpret_cast<const unsigned *>(row + g + 12));
         *reinterpret_cast<uint4 *>(st_rows + (size_t)r * stride + un * 16) = v;
     }
-    //  (3) the replicated border columns a window can reach (at most two on either side), after the units they lie in.
+    // header: the row taps of the strip, by the last threads of the CTA (warp 0 has the copies to issue)
+    const float sc = 1.0f / (2048.0f * 2048.0f);
+    if (T - 1 - tid < th) {
+        const int i = T - 1 - tid;
+        const CubicTap t = cubic_tap(y0 + i, scale_y);
+        ylast[i] = t.ofs + 2;
+        ybf[i] = make_float4((float)t.c[0] * sc, (float)t.c[1] * sc, (float)t.c[2] * sc, (float)t.c[3] * sc);
+        if (TAIL) ybi[i] = make_int4(t.c[0], t.c[1], t.c[2], t.c[3]);
+    }
+    // this thread's columns: x0 + tid and x0 + tid + T (taps of an out-of-range column are those of the last column)
+    int xs[PX], ta[PX];                   // column, source byte offset of its first tap byte
+    unsigned c01[PX], c23[PX];
+#pragma unroll
+    for (int j = 0; j < PX; ++j) {
+        xs[j] = x0 + tid + j * T;
+        const CubicTap tx = cubic_tap(min(xs[j], dw - 1), scale_x);
+        ta[j] = (tx.ofs - 1) * CN;
+        c01[j] = ((unsigned)tx.c[0] & 0xffffu) | ((unsigned)tx.c[1] << 16);
+        c23[j] = ((unsigned)tx.c[2] & 0xffffu) | ((unsigned)tx.c[3] << 16);
+    }
+    // the replicated border columns a window can reach (at most two on either side), after the units they lie in
+    const int nb_l = max(0, -wl) * CN, nb_r = max(0, wr - (sw - 1)) * CN;
     if (nb_l + nb_r > 0) {
         __syncthreads();
         const int nb = nb_l + nb_r;
@@ -388,8 +434,8 @@ __global__ void __launch_bounds__(256) k_resize_cubic_u8_staged(const unsigned c
             }
         }
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
+    __syncthreads();              // staged bytes and header written; the mbarrier (initialised by thread 0) may be waited on
+    if (row_bytes != 0u) st_mbar_wait(bar32, 0u);
     if (xs[0] >= dw) return;
     const bool valid1 = xs[PX - 1] < dw;
 
@@ -397,13 +443,13 @@ __global__ void __launch_bounds__(256) k_resize_cubic_u8_staged(const unsigned c
     // SR_CgaCtaId at every use)
     unsigned sbase = (unsigned)__cvta_generic_to_shared(st_dyn);
     asm volatile("" : "+r"(sbase));
-    const unsigned a_ylast = sbase, a_ybf = sbase + 4u * TY, a_ybi = sbase + 20u * TY;
+    const unsigned a_ylast = sbase, a_ybf = sbase + 4u * kStagedMaxTy, a_ybi = sbase + 20u * kStagedMaxTy;
     // a column's tap bytes: 4*CN contiguous bytes from staged byte a of every row, fetched as CN+1 aligned words
     unsigned tp32[PX], shift[PX];
 #pragma unroll
     for (int j = 0; j < PX; ++j) {
         const int a = ta[j] - g0 + kStagePad;
-        tp32[j] = sbase + (unsigned)kStagedHeader<TY> + (unsigned)(a & ~3);
+        tp32[j] = sbase + (unsigned)kStagedHeader + (unsigned)(a & ~3);
         shift[j] = (unsigned)(a & 3) * 8u;
     }
     const int kMagicI = 0x4B400000;
@@ -630,48 +676,68 @@ int launch_resize_cubic_u8(const unsigned char *src, unsigned char *dst, int N, 
     const bool tiled = path == 1;      // measured slower than the per-pixel kernel (0.17-0.28 ms against 0.15 per 64 frames)
     const bool strip = path == 0 || path == 3;
     if (tiled && smem > 200 * 1024) return -1;
-    // staged strip form: needs 4-byte aligned source rows (its staging loads are words) and a window that fits in
+    // staged strip form: needs 4-byte aligned source rows (its edge loads are words) and a window that fits in
     // shared memory; otherwise the plain strip form
-    if (path == 0) {
+    if (path == 0 && ((reinterpret_cast<uintptr_t>(src) | (size_t)sw * cn) & 3) == 0 && scale_x < 64.0 && scale_y < 64.0) {
         static const int ty_env = getenv("TFPD_RESIZE_TY") ? atoi(getenv("TFPD_RESIZE_TY")) : 0;
         static const int th_env = getenv("TFPD_RESIZE_THREADS") ? atoi(getenv("TFPD_RESIZE_THREADS")) : 0;
-        const int ty = ty_env == 32 ? 32 : 16;
-        // CTA width: a thread computes columns x and x + threads; the multiple of 32 in 64..256 that leaves the fewest
-        // idle column slots over dw columns (the widest such)
-        int threads = 128;
-        long long best = -1;
+        static int sm_of_dev[64] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        int &sms = sm_of_dev[dev & 63];
+        if (sms == 0 && cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms = 148;
+        // CTA width t (a thread computes columns x and x + t) and strip height ty, by a model of the kernel's time:
+        // waves of CTAs x the work of one CTA x the CTAs that share an SM.  Per thread a source row costs ~56
+        // instructions, an output row ~41 (ncu r03c); taller strips re-do fewer source rows, shorter ones leave a
+        // fuller last wave when there are only one or two.
+        int threads = 0, ty = 0, stride = 0, rows = 0;
+        double best = 0.0;
         for (int t = 64; t <= 256; t += 32) {
-            const long long tile = (long long)kStagedPx * t, padded = (dw + tile - 1) / tile * tile;
-            if (best < 0 || padded < best || (padded == best && t > threads)) best = padded, threads = t;
+            if (th_env >= 32 && th_env <= 256 && th_env % 32 == 0 && t != th_env) continue;
+            const int xt = (dw + kStagedPx * t - 1) / (kStagedPx * t);
+            const int wcols = (int)ceil((kStagedPx * t - 1) * scale_x) + 6;
+            const int st = (wcols * cn + 15 + kStagePad + 4 + 15) / 16 * 16;
+            for (int y = 4; y <= kStagedMaxTy; ++y) {
+                if (ty_env >= 4 && ty_env <= kStagedMaxTy && y != ty_env) continue;
+                const int rw = (int)ceil((y - 1) * scale_y) + 6;
+                const size_t sm_bytes = (size_t)st * rw + kStagedHeader;
+                if (sm_bytes > 96 * 1024) continue;
+                int per_sm = (int)((227 * 1024) / (sm_bytes + 1024));
+                per_sm = per_sm < 2048 / t ? per_sm : 2048 / t;          // resident threads
+                per_sm = per_sm < 65536 / (t * 64) ? per_sm : 65536 / (t * 64);   // 64 registers per thread
+                if (per_sm < 1) continue;
+                const double ctas = (double)xt * ((dh + y - 1) / y) * N;
+                // whole waves only where there are few of them (small batches: 16 frames ran 25 % faster on strips
+                // that fill exactly one wave); with several waves the measured time follows the total work
+                // (64 frames: 16-row strips 39 us, 14-row strips at 2.92 waves 41 us)
+                const double wv_exact = ctas / ((double)sms * per_sm), waves = wv_exact < 2.0 ? ceil(wv_exact) : wv_exact;
+                const double work = ((y - 1) * scale_y + 4.0) * 56.0 + y * 41.0 + 250.0;
+                // idle lanes of the last column tile and few resident warps (latency no longer hidden) cost time too
+                const double lanes = (double)xt * kStagedPx * t / dw;
+                const double warps = per_sm * (t / 32.0);
+                const double cost = waves * work * per_sm * t * lanes * (warps < 24.0 ? 24.0 / warps : 1.0);
+                if (threads == 0 || cost < best) best = cost, threads = t, ty = y, stride = st, rows = rw;
+            }
         }
-        if (th_env >= 32 && th_env <= 256 && th_env % 32 == 0) threads = th_env;
-        const int wcols = (int)ceil((kStagedPx * threads - 1) * scale_x) + 6;
-        const int stride = (wcols * cn + 15 + kStagePad + 4 + 15) / 16 * 16;
-        const int rows = (int)ceil((ty - 1) * scale_y) + 6;
-        const size_t st_smem = (size_t)stride * rows + 36 * (size_t)ty;
-        const bool aligned = ((reinterpret_cast<uintptr_t>(src) | (size_t)sw * cn) & 3) == 0;
-        if (aligned && st_smem <= 96 * 1024 && scale_x < 64.0 && scale_y < 64.0) {
+        if (threads != 0) {
+            const size_t st_smem = (size_t)stride * rows + kStagedHeader;
             const dim3 grid((dw + kStagedPx * threads - 1) / (kStagedPx * threads), (dh + ty - 1) / ty, N);
-#define TFPD_STAGED_CASE_T(CN, TY, TAIL)                                                                               \
+#define TFPD_STAGED_CASE_T(CN, TAIL)                                                                                   \
     {                                                                                                                  \
         if (st_smem > 48 * 1024 &&                                                                                     \
-            cudaFuncSetAttribute(k_resize_cubic_u8_staged<CN, TY, TAIL>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+            cudaFuncSetAttribute(k_resize_cubic_u8_staged<CN, TAIL>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
                                  (int)st_smem) != cudaSuccess)                                                        \
             return -1;                                                                                                 \
-        k_resize_cubic_u8_staged<CN, TY, TAIL><<<grid, threads, st_smem, s>>>(src, dst, sh, sw, dh, dw, scale_x,      \
-                                                                              scale_y, stride, rows, 1.0f);            \
+        k_resize_cubic_u8_staged<CN, TAIL><<<grid, threads, st_smem, s>>>(src, dst, sh, sw, dh, dw, scale_x, scale_y,  \
+                                                                          stride, rows, 1.0f, ty);                     \
     }
-#define TFPD_STAGED_CASE(CN, TY)                                                                                       \
-    if ((dw * CN) & 7) TFPD_STAGED_CASE_T(CN, TY, true) else TFPD_STAGED_CASE_T(CN, TY, false)
-            switch (cn * 100 + ty) {
-                case 116: TFPD_STAGED_CASE(1, 16) break;
-                case 132: TFPD_STAGED_CASE(1, 32) break;
-                case 216: TFPD_STAGED_CASE(2, 16) break;
-                case 232: TFPD_STAGED_CASE(2, 32) break;
-                case 316: TFPD_STAGED_CASE(3, 16) break;
-                case 332: TFPD_STAGED_CASE(3, 32) break;
-                case 416: TFPD_STAGED_CASE(4, 16) break;
-                case 432: TFPD_STAGED_CASE(4, 32) break;
+#define TFPD_STAGED_CASE(CN)                                                                                           \
+    if ((dw * CN) & 7) TFPD_STAGED_CASE_T(CN, true) else TFPD_STAGED_CASE_T(CN, false)
+            switch (cn) {
+                case 1: TFPD_STAGED_CASE(1) break;
+                case 2: TFPD_STAGED_CASE(2) break;
+                case 3: TFPD_STAGED_CASE(3) break;
+                case 4: TFPD_STAGED_CASE(4) break;
                 default: return -1;
             }
 #undef TFPD_STAGED_CASE
