@@ -286,10 +286,13 @@ TFPD_API int tfpd_quantize_img(tfpd_ctx *ctx, const float *src, int on_device, s
  *   "pow2_path"    kernels for power-of-two upsample factors other than the x4 fast path (2, 8, 16): 1 automatic
  *                  (default), 0 the general kernels, 2 fused, 3 fused with a separate horizontal pass, 4 unfused
  *                  polyphase passes.  All give the same maps up to the order of additions; for tests and tuning.
- *   "resize_path"  kernel of tfpd_resize_cubic_u8: 0 automatic (default: the strip form), 1 tiled (horizontal pass
- *                  once per source row of a 16-row tile, in shared memory; measured slower), 2 one thread per
- *                  output pixel, 3 strip (a thread marches down 16 output rows of a column with a register window
- *                  of four source rows' horizontal sums).  Same bytes every way.  */
+ *   "resize_path"  kernel of tfpd_resize_cubic_u8: 0 automatic (default: the staged strip form -- the source window of
+ *                  a strip staged in shared memory by TMA, word loads + byte permutes + dp2a for the horizontal
+ *                  sums, packed FP32 for the vertical pass, two columns per thread -- where the source rows are
+ *                  4-byte aligned and the window fits, else the strip form), 1 tiled (horizontal pass once per
+ *                  source row of a 16-row tile, in shared memory; measured slower), 2 one thread per output pixel,
+ *                  3 strip (a thread marches down 16 output rows of a column with a register window of four
+ *                  source rows' horizontal sums).  Same bytes every way.  */
 TFPD_API int tfpd_set_option(tfpd_ctx *ctx, const char *name, int value);
 
 /* Introspection used by the tests and the bench. */

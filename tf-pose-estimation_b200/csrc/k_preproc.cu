@@ -193,20 +193,32 @@ __global__ void __launch_bounds__(128) k_resize_cubic_u8_strip(const unsigned ch
     }
 }
 
-// Staged strip form (the default where the source rows are 4-byte aligned): the strip form's arithmetic with a
-// third of its instructions.
-//  * The source window of a CTA (the rows its strip reads x the columns its output columns read, out-of-image
-//    columns replicated) is staged once in shared memory with 128-bit loads: a thread's 4 tap columns x CN channels
-//    are then 4*CN CONTIGUOUS bytes at a fixed offset of every row, fetched as CN+1 aligned words (the strip form
-//    issues 4*CN byte loads with 64-bit address arithmetic each) and realigned with funnel shifts.
-//  * byte permutes gather a channel's four taps into one register and two dp2a (s16 coefficient pairs x u8 taps)
+// Staged strip form (the default where the source rows are 4-byte aligned): the strip form's arithmetic in about half
+// its instructions (64 frames 640x480x3 -> 432x368x3: 53.8 M -> 28 M warp instructions, 76 -> 39 us; ncu r02y / r03h).
+//  * The source window of a CTA (the rows its strip reads x the columns its output columns read; out-of-image columns
+//    and rows replicated) is staged in shared memory: one TMA bulk copy per row for the whole 16-byte units, issued by
+//    warp 0 before anything else, word loads for the few units at the row ends, byte stores for the border columns.
+//    A thread's 4 tap columns x CN channels are then 4*CN CONTIGUOUS bytes at a fixed offset of every staged row,
+//    fetched as CN+1 aligned words (the strip form issues 4*CN byte loads with 64-bit address arithmetic each) and
+//    realigned with funnel shifts.
+//  * Byte permutes gather a channel's four taps into one register and two dp2a (s16 coefficient pairs x u8 taps)
 //    make its exact integer sum; the accumulator starts at the bit pattern of 1.5*2^23, so the sum arrives as the
 //    float's bits and one FADD finishes the exact int->float conversion.
+//  * A thread computes TWO output columns (x and x + blockDim.x): the per-row bookkeeping is shared and the 2*CN
+//    channel values always pair up for the packed vertical pass.
 //  * The window of four source rows is a register ring rotated by unrolling (no moves): the outer loop walks SOURCE
 //    rows and emits every output row whose fourth tap row was just computed.
-//  * The vertical pass runs channel pairs on packed FP32 (mul.rn.f32x2 / add.rn.f32x2: the same separately rounded
-//    multiplies and adds), clamps in float and rounds with the magic constant: the low byte is the pixel.
-// Same bytes as the other forms (tests force each).
+//  * The vertical pass runs on packed FP32 (FMUL2 + an FFMA2 by 1.0: the same separately rounded multiplies and
+//    adds, see pk_add); saturate_cast<uchar>(cvRound()) is one F2IP.U8.F32.
+//  * Strip height and CTA width are chosen per launch (launch_resize_cubic_u8): whole waves for small batches, as
+//    little total work as fits four CTAs per SM otherwise.
+// Same bytes as the other forms (tests force each).  What is left (ncu r03h): 74 % of the issue slots busy on ~28 M
+// instructions that are the formulation's own (per two columns and source row: 8 word loads, 6 funnel shifts,
+// 12 permutes, 12 dp2a, 6 FADD; per output row 21 packed FP32, 6 F2IP, 6 byte stores).  TRIED, NOT KEPT (profiles/
+// r03i_*): a producer / consumer ring version (one extra warp staging 8-row chunks through full / empty mbarriers,
+// consumers walking 41-row segments so that a source row's sums are computed once: 1.05 passes over the source
+// instead of 1.49) removed the staging waits and measured the same 39 us (its per-row chunk bookkeeping ate the
+// gain); 720p sources gained 7 %.
 constexpr int kStagedPx = 2;             // output columns per thread: x and x + blockDim.x
 template <int CN>
 struct HRow {                            // horizontal sums of one source row: CN channels of both columns, in pairs
