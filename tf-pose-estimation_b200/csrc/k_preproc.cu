@@ -736,10 +736,13 @@ int launch_resize_cubic_u8(const unsigned char *src, unsigned char *dst, int N, 
             const dim3 grid((dw + kStagedPx * threads - 1) / (kStagedPx * threads), (dh + ty - 1) / ty, N);
 #define TFPD_STAGED_CASE_T(CN, TAIL)                                                                                   \
     {                                                                                                                  \
-        if (st_smem > 48 * 1024 &&                                                                                     \
-            cudaFuncSetAttribute(k_resize_cubic_u8_staged<CN, TAIL>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
-                                 (int)st_smem) != cudaSuccess)                                                        \
-            return -1;                                                                                                 \
+        static size_t attr_set[64] = {}; /* largest size allowed so far, per device (function attributes are) */     \
+        if (st_smem > 48 * 1024 && st_smem > attr_set[dev & 63]) {                                                     \
+            if (cudaFuncSetAttribute(k_resize_cubic_u8_staged<CN, TAIL>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                     (int)st_smem) != cudaSuccess)                                                    \
+                return -1;                                                                                             \
+            attr_set[dev & 63] = st_smem;                                                                              \
+        }                                                                                                              \
         k_resize_cubic_u8_staged<CN, TAIL><<<grid, threads, st_smem, s>>>(src, dst, sh, sw, dh, dw, scale_x, scale_y,  \
                                                                           stride, rows, 1.0f, ty);                     \
     }
