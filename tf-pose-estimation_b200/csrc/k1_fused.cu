@@ -45,7 +45,10 @@ constexpr int kThreads = kBlurThreads + kCopyThreads;   // 640 -> 96 registers p
 #endif
 constexpr int kMinWarps = TFPD_MIN_WARPS;
 constexpr int kMinThreads = kMinWarps * 32;
-constexpr int kMinCtasPerSm = 24 / kMinWarps;
+#ifndef TFPD_MIN_SM_WARPS
+#define TFPD_MIN_SM_WARPS 24                // minimal-mode warps per SM the kernel is compiled for (24 -> 74 registers)
+#endif
+constexpr int kMinCtasPerSm = TFPD_MIN_SM_WARPS / kMinWarps;
 // a warp pass owns at most 32*CPL-8 = 56 cells (see launch_k1_fused_f4: chunk_cells <= 56)
 constexpr int NPX = 4 * CPL;                // output pixels per lane per row
 
